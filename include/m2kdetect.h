@@ -1,0 +1,233 @@
+/*
+ * libm2kdetect -- B200-native source detection for move2kube (C ABI).
+ *
+ * This is the drop-in boundary for ONE path of the reference: the source-detection pass of
+ * `move2kube plan`.  A Go binding (cgo) would declare exactly these
+ * entry points; the stub is shown in INTEGRATION.md.  Plain C types only, no callbacks.
+ *
+ * Reference interfaces replaced (file:line under the reference tree):
+ *   Any2KubeTranslator.GetServiceOptions        internal/source/any2kube.go:43-105
+ *   Any2KubeTranslator.getIgnorePaths           internal/source/any2kube.go:151-181
+ *   common.GetFilesByName / GetFilesByExt       internal/common/utils.go:85-120 / 47-82
+ *   common.IsStringPresent (strings.EqualFold)  internal/common/utils.go:308-315
+ *   Containerizers.InitContainerizers /
+ *     GetContainerizationOptions                internal/containerizer/containerizer.go:56-76
+ *   DockerfileContainerizer.GetTargetOptions    internal/containerizer/dockerfilecontainerizer.go:62-83
+ *   S2IContainerizer.GetTargetOptions           internal/containerizer/s2icontainerizer.go:63-84
+ *   the 18 detect scripts                       internal/assets/{dockerfiles,s2i}/<lang>/m2k*detect.sh
+ *   isDockerFile / getDockerfileServices walk   internal/source/dockerfile2kube.go:117-170
+ *
+ * Error convention: every call returns M2K_OK (0) or a negative m2k_status; the message is
+ * kept per context (m2k_last_error) or, when no context exists, per thread
+ * (m2k_global_error).  There is no CPU fallback: without a usable CUDA device every compute
+ * entry point fails with M2K_ERR_CUDA.
+ *
+ * Threading: a context is used by one thread at a time (the reference path is
+ * single-goroutine).  Calls set the CUDA device themselves.
+ */
+#ifndef M2KDETECT_H
+#define M2KDETECT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M2K_ABI_VERSION 1
+#define M2K_NONE 0xFFFFFFFFu
+
+typedef enum m2k_status {
+  M2K_OK = 0,
+  M2K_ERR_ARG = -1,         /* bad argument */
+  M2K_ERR_CUDA = -2,        /* CUDA runtime error or no device */
+  M2K_ERR_IO = -3,          /* root missing / unreadable (GetFilesByName error path) */
+  M2K_ERR_NOMEM = -4,
+  M2K_ERR_UNSUPPORTED = -5, /* input the packed representation cannot express exactly
+                               (e.g. a file name containing a newline) */
+  M2K_ERR_LIMIT = -6        /* a stated size limit was exceeded */
+} m2k_status;
+
+/* ---- entry types: low nibble = lstat type, high nibble = type after following symlinks ---- */
+enum { M2K_T_ERR = 0, M2K_T_REG = 1, M2K_T_DIR = 2, M2K_T_LNK = 3, M2K_T_OTHER = 4 };
+
+/* ---- /bin/sh flavour of the python detect scripts ---- */
+enum { M2K_SH_BASH = 0, M2K_SH_DASH = 1 };
+
+/* ---- per-entry / per-directory name features (bit numbers) ----
+ * F_* : [ -f D/name ]   -- entry exists with that exact basename and is a regular file after
+ *                          following symlinks (detect scripts' `[ -f ... ]`)
+ * R_* : find -name "*.ext" -- entry of ANY type whose basename ends in ".ext"
+ * WAR_OK: first non-dot entry "*.war" of the directory (byte order, LC_ALL=C) exists ([ -e ]) */
+enum {
+  M2K_F_PIPFILE = 0, M2K_F_BUILD_XML = 1, M2K_F_BUILD_GRADLE = 2, M2K_F_POM_XML = 3,
+  M2K_F_PACKAGE_JSON = 4, M2K_F_REQUIREMENTS = 5, M2K_F_SETUP_PY = 6, M2K_F_ENVIRONMENT_YML = 7,
+  M2K_F_GEMFILE = 8, M2K_F_GO_MOD = 9,
+  M2K_R_GO = 10, M2K_R_PHP = 11, M2K_R_JAVA = 12,
+  M2K_N_WAR = 13,        /* entry: non-dot name ending ".war"; directory: WAR_OK */
+  M2K_N_IGNOREFILE = 14, /* non-directory named ".m2kignore"          (utils.go:85-120) */
+  M2K_N_USER_DF = 15,    /* non-directory named "m2kdfdetect.sh"      (dockerfilecontainerizer.go:50-59) */
+  M2K_N_USER_S2I = 16,   /* non-directory named "m2ks2idetect.sh"     (s2icontainerizer.go:51-60) */
+  M2K_N_YAML = 17,       /* non-directory whose filepath.Ext is .yml/.yaml (GetFilesByExt callers) */
+  M2K_C_MAIN_PY = 18,    /* content: a file whose name ends "py" contains "__main__" */
+  M2K_C_DOCKERFILE = 19  /* content: a file isDockerFile() accepts */
+};
+
+/* ---- containerizer option bits in dir_opts (= TargetOptions order) ---- */
+enum {
+  M2K_DF_DJANGO = 0, M2K_DF_GOLANG = 1, M2K_DF_WAR_JBOSS = 2, M2K_DF_WAR_LIBERTY = 3,
+  M2K_DF_WAR_TOMCAT = 4, M2K_DF_JAVAANT = 5, M2K_DF_JAVAGRADLE = 6, M2K_DF_JAVAMAVEN = 7,
+  M2K_DF_NODEJS = 8, M2K_DF_PHP = 9, M2K_DF_PYTHON = 10, M2K_DF_RUBY = 11,
+  M2K_S2I_GOLANG = 12, M2K_S2I_JAVA = 13, M2K_S2I_NODEJS = 14, M2K_S2I_PHP = 15,
+  M2K_S2I_PYTHON = 16, M2K_S2I_RUBY = 17,
+  M2K_N_OPTS = 18
+};
+#define M2K_DF_MASK 0x00000FFFu
+#define M2K_S2I_MASK 0x0003F000u
+
+/* ---- per-file content flags ---- */
+enum {
+  M2K_FILE_HAS_MAIN = 1,    /* bytes contain "__main__"              (python detect scripts :21/:22) */
+  M2K_FILE_LONG_LINE = 2,   /* some line >= 65536 bytes (bufio.Scanner ErrTooLong) */
+  M2K_FILE_FROM_FIRST = 4,  /* first non-ARG instruction is FROM and matches dockerfile2kube.go:131 */
+  M2K_FILE_DOCKERFILE = 8   /* isDockerFile() == true                (dockerfile2kube.go:117-144) */
+};
+
+/* ---- what the walk did with a directory (any2kube.go:58-98) ---- */
+enum {
+  M2K_DIR_NOT_VISITED = 0,        /* hidden below a pruned directory */
+  M2K_DIR_PRECONTAINERIZED = 1,   /* :66-68  SkipDir */
+  M2K_DIR_IGNORED_PRUNE = 2,      /* :69-72  SkipDir */
+  M2K_DIR_IGNORED_DESCEND = 3,    /* :73     */
+  M2K_DIR_NOMATCH_PRUNE = 4,      /* :78-80  SkipDir */
+  M2K_DIR_NOMATCH_DESCEND = 5,    /* :81     */
+  M2K_DIR_SERVICE = 6,            /* :83-97  services emitted, SkipDir */
+  M2K_DIR_WALK_ERROR = 7          /* :59-62  ReadDir failed: warned, not detected */
+};
+
+/* ---- the packed tree: struct-of-arrays in (pinned) host memory -------------------------
+ * Directories are numbered in DFS pre-order with children in byte order (filepath.Walk's
+ * order), so a subtree is the id range [d, dir_end[d]).  Entries (files, directories,
+ * symlinks, other) are sorted by (directory id, name).  Files that carry content -- entries
+ * whose type after following symlinks is REG -- are numbered in entry order; each file's
+ * bytes start 16-byte aligned in `bytes`, zero padded, and at least 16 zero bytes follow
+ * the last file.  `bytes` may be NULL when the content lives only on the device
+ * (synthetic trees filled by m2k_synth_fill_device). */
+typedef struct m2k_tree {
+  uint32_t n_dirs, n_entries, n_files, max_depth;
+  uint64_t n_bytes;      /* size of the bytes blob including padding */
+  uint64_t n_name_bytes; /* size of the names blob */
+  uint64_t content_bytes;/* sum of file_len: the algorithmic bytes of one scan */
+  const char* root_path; /* as given by the caller (not cleaned), NUL terminated */
+  uint32_t* dir_parent;      /* [n_dirs]   parent directory id, root: M2K_NONE */
+  uint32_t* dir_end;         /* [n_dirs]   one past the last directory id of the subtree */
+  uint32_t* dir_entry;       /* [n_dirs]   this directory's entry index, root: M2K_NONE */
+  uint32_t* dir_first_entry; /* [n_dirs+1] entries of d are [dir_first_entry[d], dir_first_entry[d+1]) */
+  uint32_t* dir_depth;       /* [n_dirs]   root = 0 */
+  uint8_t* dir_flags;        /* [n_dirs]   bit0: ReadDir failed */
+  uint32_t* entry_dir;       /* [n_entries] containing directory id (non-decreasing) */
+  uint32_t* entry_name_off;  /* [n_entries+1] offsets into names */
+  uint8_t* entry_type;       /* [n_entries] lstat type | followed type << 4 */
+  uint32_t* entry_child;     /* [n_entries] directory id (DIR), file id (content), else M2K_NONE */
+  uint8_t* names;            /* [n_name_bytes] basenames, not NUL terminated */
+  uint32_t* file_entry;      /* [n_files] */
+  uint64_t* file_off;        /* [n_files] offset into bytes, multiple of 16 */
+  uint64_t* file_len;        /* [n_files] */
+  uint8_t* bytes;            /* [n_bytes] or NULL */
+  void* owner;               /* library bookkeeping */
+} m2k_tree;
+
+/* ---- results (host memory, owned by the library, freed with m2k_result_free) ---- */
+typedef struct m2k_result {
+  uint32_t n_dirs, n_files, n_services, n_candidates_verified;
+  uint32_t* dir_opts;      /* [n_dirs] built-in option bits (M2K_DF_*, M2K_S2I_*) for EVERY directory */
+  uint32_t* dir_direct;    /* [n_dirs] features of the directory's own entries */
+  uint32_t* dir_subtree;   /* [n_dirs] OR of dir_direct over the subtree (R_* predicates, content bits) */
+  uint8_t* dir_state;      /* [n_dirs] M2K_DIR_* */
+  uint8_t* dir_ignore;     /* [n_dirs] bit0 in ignoreDirectories, bit1 in ignoreContents, bit2 preContainerized */
+  uint32_t* dir_main_file; /* [n_dirs] lowest file id under the directory with M2K_C_MAIN_PY, else M2K_NONE */
+  uint8_t* file_flags;     /* [n_files] M2K_FILE_* */
+  uint32_t* service_dirs;  /* [n_services] directory ids with state SERVICE, walk order */
+  uint32_t n_ignore_dirs, n_ignore_contents;
+  char** ignore_dirs;      /* cleaned paths, any2kube.go:175-176 */
+  char** ignore_contents;  /* any2kube.go:170-173 */
+  /* timing of the last run, milliseconds (CUDA events / host clock) */
+  float ms_h2d, ms_kernels, ms_scan_kernel, ms_d2h, ms_host_ignore, ms_total;
+  uint32_t n_kernel_launches;
+  uint32_t _pad;
+} m2k_result;
+
+typedef struct m2k_detect_params {
+  uint32_t sh_flavor;          /* M2K_SH_BASH (canonical) or M2K_SH_DASH */
+  uint32_t n_pre;              /* preContainerizedSourcePaths, any2kube.go:47-54 */
+  const char* const* pre_paths;
+  uint32_t skip_content;       /* 1: names only (no byte scan): a11/a12 bits stay 0 */
+  uint32_t _pad;
+} m2k_detect_params;
+
+typedef struct m2k_ctx m2k_ctx;       /* one CUDA device, its stream and scratch */
+typedef struct m2k_devtree m2k_devtree; /* a tree (or a shard of its files) resident in HBM */
+
+/* -- lifecycle -- */
+int m2k_abi_version(void);
+const char* m2k_global_error(void);
+int m2k_ctx_create(int device, m2k_ctx** out);
+void m2k_ctx_destroy(m2k_ctx* ctx);
+const char* m2k_last_error(const m2k_ctx* ctx);
+int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes, char* name, size_t name_cap);
+
+/* -- host packer: ONE filesystem walk replaces the reference's 4-11 walks
+ *    (utils.go:85-120 x3 per Any2Kube call, any2kube.go:58, dockerfile2kube.go:154) -- */
+int m2k_pack_tree(m2k_ctx* ctx, const char* root_path, int read_content, m2k_tree** out);
+void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree);
+
+/* -- synthetic trees of BASELINE.md section 4 (configs B, C, D), deterministic in `seed` -- */
+typedef struct m2k_synth_params {
+  uint64_t seed;
+  uint32_t n_files, n_dirs, max_depth, n_ignore_files;
+  uint64_t total_bytes;   /* target content size */
+  uint32_t n_huge;        /* config D: number of multi-GiB files */
+  uint32_t _pad;
+  uint64_t huge_bytes;    /* size of each */
+  uint32_t tiny_min, tiny_max; /* config D: tiny file size range (0,0 = log-normal sizes) */
+} m2k_synth_params;
+int m2k_synth_tree(m2k_ctx* ctx, const m2k_synth_params* p, int host_bytes, m2k_tree** out);
+/* bytes of file ids [file_begin, file_end) generated on the host into dst (file_off relative to
+ * file_off[file_begin]); the SAME generator the device fill uses */
+int m2k_synth_fill_host(const m2k_tree* tree, uint64_t seed, uint32_t file_begin, uint32_t file_end,
+                        uint8_t* dst, int n_threads);
+
+/* -- whole path, host buffers in, host results out (H2D + kernels + D2H): the call a plugin makes -- */
+int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_params* params, m2k_result** out);
+void m2k_result_free(m2k_result* r);
+
+/* -- staged form (bench, multi-GPU): a shard = file ids [file_begin, file_end) -- */
+int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out);
+int m2k_synth_fill_device(m2k_ctx* ctx, m2k_devtree* dt, uint64_t seed);
+/* phase A: name features + byte scan + Dockerfile check over the resident shard */
+int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
+/* per-directory partial arrays a multi-GPU run gathers (device pointers, n_dirs uint32 each):
+ * content mask (OR-reducible) and lowest main-file id (MIN-reducible) */
+int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t** d_dir_content, uint32_t** d_dir_main, uint32_t* n_dirs);
+/* OR / MIN `n_ranks` gathered partial arrays (device memory, rank-major) into this shard's own */
+int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks);
+/* phase C: subtree OR, predicate combine, ignore join, prune; copies results to the host */
+int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params, m2k_result** out);
+void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt);
+/* device time of the byte-scan kernel alone in the last m2k_scan, and launches issued so far */
+int m2k_scan_kernel_ms(m2k_ctx* ctx, float* ms);
+uint64_t m2k_launch_count(const m2k_ctx* ctx);
+void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
+
+/* -- host-side path helpers the mirror needs (Go stdlib semantics) -- */
+int m2k_path_clean(const char* path, char* out, size_t cap);              /* filepath.Clean */
+int m2k_equal_fold(const char* a, size_t na, const char* b, size_t nb);   /* strings.EqualFold */
+/* filepath.Walk-order listing of non-directory entries selected by feature bit (GetFilesByName /
+ * GetFilesByExt replacement): writes entry indices, returns count */
+int m2k_list_entries(const m2k_tree* tree, uint32_t feature_bit, const uint32_t* entry_feat, uint32_t* out, uint32_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M2KDETECT_H */
