@@ -140,7 +140,7 @@ typedef struct m2k_tree {
 
 /* ---- results (host memory, owned by the library, freed with m2k_result_free) ---- */
 typedef struct m2k_result {
-  uint32_t n_dirs, n_files, n_services, n_candidates_verified;
+  uint32_t n_dirs, n_files, n_services, n_entries;
   uint32_t* dir_opts;      /* [n_dirs] built-in option bits (M2K_DF_*, M2K_S2I_*) for EVERY directory */
   uint32_t* dir_direct;    /* [n_dirs] features of the directory's own entries */
   uint32_t* dir_subtree;   /* [n_dirs] OR of dir_direct over the subtree (R_* predicates, content bits) */
@@ -149,6 +149,7 @@ typedef struct m2k_result {
   uint32_t* dir_main_file; /* [n_dirs] lowest file id under the directory with M2K_C_MAIN_PY, else M2K_NONE */
   uint8_t* file_flags;     /* [n_files] M2K_FILE_* */
   uint32_t* service_dirs;  /* [n_services] directory ids with state SERVICE, walk order */
+  uint32_t* entry_feat;    /* [n_entries] name-feature bits of every entry (M2K_F_*, M2K_R_*, M2K_N_*) */
   uint32_t n_ignore_dirs, n_ignore_contents;
   char** ignore_dirs;      /* cleaned paths, any2kube.go:175-176 */
   char** ignore_contents;  /* any2kube.go:170-173 */

@@ -45,9 +45,9 @@ class Tree(C.Structure):
 class Result(C.Structure):
     _fields_ = [
         ("n_dirs", C.c_uint32), ("n_files", C.c_uint32), ("n_services", C.c_uint32),
-        ("n_candidates_verified", C.c_uint32),
+        ("n_entries", C.c_uint32),
         ("dir_opts", u32p), ("dir_direct", u32p), ("dir_subtree", u32p), ("dir_state", u8p),
-        ("dir_ignore", u8p), ("dir_main_file", u32p), ("file_flags", u8p), ("service_dirs", u32p),
+        ("dir_ignore", u8p), ("dir_main_file", u32p), ("file_flags", u8p), ("service_dirs", u32p), ("entry_feat", u32p),
         ("n_ignore_dirs", C.c_uint32), ("n_ignore_contents", C.c_uint32),
         ("ignore_dirs", C.POINTER(C.c_char_p)), ("ignore_contents", C.POINTER(C.c_char_p)),
         ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_scan_kernel", C.c_float),

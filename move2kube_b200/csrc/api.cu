@@ -1,0 +1,573 @@
+// C ABI of libm2kdetect (include/m2kdetect.h): contexts, uploads, the kernel pipeline, results.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <chrono>
+#include <unordered_map>
+
+#include "casefold_table.h"
+#include "gostr.h"
+#include "m2k_internal.h"
+
+using namespace m2k;
+
+struct m2k_ctx { Ctx c; };
+struct m2k_devtree { DevTree t; float ms_h2d = 0.f; };
+
+static thread_local std::string g_err;
+
+static int fail(Ctx* c, int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                                              \
+  do {                                                                                                        \
+    cudaError_t e_ = (call);                                                                                  \
+    if (e_ != cudaSuccess) return fail(C, M2K_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+static double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ---- name signature table -------------------------------------------------------------------
+static NameSig make_sig(const char* pat, uint32_t kind, uint32_t feature, uint32_t need) {
+  NameSig g;
+  memset(&g, 0, sizeof g);
+  size_t n = strlen(pat);
+  g.len = (uint32_t)n; g.kind = kind; g.feature = feature; g.need = need;
+  for (size_t i = 0; i < n && i < 16; i++) {
+    uint64_t ch = (uint8_t)pat[n - 1 - i];
+    if (i < 8) { g.lo |= ch << (8 * i); g.mask_lo |= 0xFFull << (8 * i); }
+    else { g.hi |= ch << (8 * (i - 8)); g.mask_hi |= 0xFFull << (8 * (i - 8)); }
+  }
+  return g;
+}
+
+static std::vector<NameSig> default_sigs() {
+  std::vector<NameSig> s;
+  // [ -f D/name ]  (exact name, regular file after following symlinks)
+  s.push_back(make_sig("Pipfile", 0, M2K_F_PIPFILE, 1));
+  s.push_back(make_sig("build.xml", 0, M2K_F_BUILD_XML, 1));
+  s.push_back(make_sig("build.gradle", 0, M2K_F_BUILD_GRADLE, 1));
+  s.push_back(make_sig("pom.xml", 0, M2K_F_POM_XML, 1));
+  s.push_back(make_sig("package.json", 0, M2K_F_PACKAGE_JSON, 1));
+  s.push_back(make_sig("requirements.txt", 0, M2K_F_REQUIREMENTS, 1));
+  s.push_back(make_sig("setup.py", 0, M2K_F_SETUP_PY, 1));
+  s.push_back(make_sig("environment.yml", 0, M2K_F_ENVIRONMENT_YML, 1));
+  s.push_back(make_sig("Gemfile", 0, M2K_F_GEMFILE, 1));
+  s.push_back(make_sig("go.mod", 0, M2K_F_GO_MOD, 1));
+  // find -name "*.ext"  (any entry type, dotfiles included)
+  s.push_back(make_sig(".go", 1, M2K_R_GO, 0));
+  s.push_back(make_sig(".php", 1, M2K_R_PHP, 0));
+  s.push_back(make_sig(".java", 1, M2K_R_JAVA, 0));
+  // "$1/"*.war  (shell glob: no dotfiles)
+  s.push_back(make_sig(".war", 1, M2K_N_WAR, 3));
+  // GetFilesByName targets (non-directories)
+  s.push_back(make_sig(".m2kignore", 0, M2K_N_IGNOREFILE, 2));
+  s.push_back(make_sig("m2kdfdetect.sh", 0, M2K_N_USER_DF, 2));
+  s.push_back(make_sig("m2ks2idetect.sh", 0, M2K_N_USER_S2I, 2));
+  // GetFilesByExt(.yml, .yaml) (non-directories)
+  s.push_back(make_sig(".yml", 1, M2K_N_YAML, 2));
+  s.push_back(make_sig(".yaml", 1, M2K_N_YAML, 2));
+  return s;
+}
+
+// ---- lifecycle ------------------------------------------------------------------------------
+extern "C" int m2k_abi_version(void) { return M2K_ABI_VERSION; }
+extern "C" const char* m2k_global_error(void) { return g_err.c_str(); }
+extern "C" const char* m2k_last_error(const m2k_ctx* ctx) { return ctx ? ctx->c.err.c_str() : g_err.c_str(); }
+
+extern "C" int m2k_ctx_create(int device, m2k_ctx** out) {
+  if (!out) return fail(nullptr, M2K_ERR_ARG, "m2k_ctx_create: out is NULL");
+  *out = nullptr;
+  Ctx* C = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(nullptr, M2K_ERR_CUDA, "no CUDA device (%s): libm2kdetect has no CPU path", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= n) return fail(nullptr, M2K_ERR_ARG, "device %d out of range (0..%d)", device, n - 1);
+  m2k_ctx* ctx = new m2k_ctx();
+  C = &ctx->c;
+  C->device = device;
+  auto bail = [&](int rc) { std::string keep = C->err; delete ctx; g_err = keep; return rc; };
+#define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(C, M2K_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(M2K_ERR_CUDA); } } while (0)
+  CUX(cudaSetDevice(device));
+  CUX(cudaStreamCreateWithFlags(&C->stream, cudaStreamNonBlocking));
+  for (auto& ev : C->ev) CUX(cudaEventCreate(&ev));
+  CUX(cudaDeviceGetAttribute(&C->sm_count, cudaDevAttrMultiProcessorCount, device));
+  CUX(cudaMalloc(&C->d_fold_from, sizeof(m2k_casefold_from)));
+  CUX(cudaMalloc(&C->d_fold_to, sizeof(m2k_casefold_to)));
+  CUX(cudaMemcpy(C->d_fold_from, m2k_casefold_from, sizeof(m2k_casefold_from), cudaMemcpyHostToDevice));
+  CUX(cudaMemcpy(C->d_fold_to, m2k_casefold_to, sizeof(m2k_casefold_to), cudaMemcpyHostToDevice));
+  std::vector<NameSig> sigs = default_sigs();
+  C->n_sigs = (int)sigs.size();
+  CUX(cudaMalloc(&C->d_sigs, sizeof(NameSig) * sigs.size()));
+  CUX(cudaMemcpy(C->d_sigs, sigs.data(), sizeof(NameSig) * sigs.size(), cudaMemcpyHostToDevice));
+#undef CUX
+  *out = ctx;
+  return M2K_OK;
+}
+
+extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
+  if (!ctx) return;
+  Ctx* C = &ctx->c;
+  cudaSetDevice(C->device);
+  if (C->stream) cudaStreamSynchronize(C->stream);
+  cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
+  for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
+  if (C->stream) cudaStreamDestroy(C->stream);
+  delete ctx;
+}
+
+extern "C" int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes, char* name, size_t name_cap) {
+  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+  Ctx* C = &ctx->c;
+  cudaDeviceProp p;
+  CU(cudaGetDeviceProperties(&p, C->device));
+  if (sm_count) *sm_count = p.multiProcessorCount;
+  if (hbm_bytes) *hbm_bytes = p.totalGlobalMem;
+  if (name && name_cap) { strncpy(name, p.name, name_cap - 1); name[name_cap - 1] = 0; }
+  return M2K_OK;
+}
+
+extern "C" void* m2k_stream(m2k_ctx* ctx) { return ctx ? (void*)ctx->c.stream : nullptr; }
+extern "C" uint64_t m2k_launch_count(const m2k_ctx* ctx) { return ctx ? ctx->c.launches : 0; }
+extern "C" int m2k_scan_kernel_ms(m2k_ctx* ctx, float* ms) {
+  if (!ctx || !ms) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  *ms = ctx->c.last_scan_ms;
+  return M2K_OK;
+}
+
+// ---- host trees -----------------------------------------------------------------------------
+extern "C" int m2k_pack_tree(m2k_ctx* ctx, const char* root_path, int read_content, m2k_tree** out) {
+  if (!root_path || !out) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_pack_tree: NULL argument");
+  if (ctx) cudaSetDevice(ctx->c.device);
+  std::string err;
+  int rc = pack_tree_impl(ctx != nullptr, root_path, read_content, out, &err);
+  if (rc != M2K_OK) return fail(ctx ? &ctx->c : nullptr, rc, "%s", err.c_str());
+  return rc;
+}
+
+extern "C" int m2k_synth_tree(m2k_ctx* ctx, const m2k_synth_params* p, int host_bytes, m2k_tree** out) {
+  if (!p || !out) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_synth_tree: NULL argument");
+  if (ctx) cudaSetDevice(ctx->c.device);
+  std::string err;
+  int rc = synth_tree_impl(ctx != nullptr, p, host_bytes, out, &err);
+  if (rc != M2K_OK) return fail(ctx ? &ctx->c : nullptr, rc, "%s", err.c_str());
+  return rc;
+}
+
+extern "C" int m2k_synth_fill_host(const m2k_tree* tree, uint64_t seed, uint32_t file_begin, uint32_t file_end, uint8_t* dst,
+                                   int n_threads) {
+  if (!tree || !dst || file_begin > file_end || file_end > tree->n_files) return fail(nullptr, M2K_ERR_ARG, "m2k_synth_fill_host: bad argument");
+  const TreeOwner* o = static_cast<const TreeOwner*>(tree->owner);
+  if (!o || !o->synthetic) return fail(nullptr, M2K_ERR_ARG, "not a synthetic tree");
+  if (seed != o->synth_seed) return fail(nullptr, M2K_ERR_ARG, "seed differs from the tree's seed");
+  synth_fill_host(tree, file_begin, file_end, dst, n_threads);
+  return M2K_OK;
+}
+
+extern "C" void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree) {
+  if (ctx) cudaSetDevice(ctx->c.device);
+  tree_release(tree);
+}
+
+// ---- device trees ---------------------------------------------------------------------------
+static void devtree_release(DevTree* t) {
+  void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->level_dirs, t->dir_flags, t->entry_dir, t->entry_name_off,
+                  t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
+                  t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
+                  t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
+                  t->dir_descend, t->file_flags};
+  for (void* p : ptrs) if (p) cudaFree(p);
+}
+
+extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
+  if (!dt) return;
+  if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); }
+  devtree_release(&dt->t);
+  delete dt;
+}
+
+template <typename T>
+static cudaError_t dev_alloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
+
+extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out) {
+  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+  Ctx* C = &ctx->c;
+  if (!tree || !out || file_begin > file_end || file_end > tree->n_files) return fail(C, M2K_ERR_ARG, "m2k_upload: bad argument");
+  *out = nullptr;
+  CU(cudaSetDevice(C->device));
+  m2k_devtree* dt = new m2k_devtree();
+  DevTree* t = &dt->t;
+  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); delete d; } } } guard{dt};
+  t->host = tree;
+  t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
+  t->file_begin = file_begin; t->file_end = file_end;
+  const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files, ns = file_end - file_begin;
+  // levels (host): directories grouped by depth for the bottom-up / top-down sweeps
+  std::vector<uint32_t> level_dirs(nd ? nd : 1);
+  t->level_off.assign((size_t)t->max_depth + 2, 0);
+  for (uint32_t d = 0; d < nd; d++) t->level_off[tree->dir_depth[d] + 1]++;
+  for (size_t L = 1; L < t->level_off.size(); L++) t->level_off[L] += t->level_off[L - 1];
+  {
+    std::vector<uint32_t> cur(t->level_off.begin(), t->level_off.end() - 1);
+    for (uint32_t d = 0; d < nd; d++) level_dirs[cur[tree->dir_depth[d]]++] = d;
+  }
+  // chunk prefix over the shard
+  std::vector<uint32_t> chunk_first((size_t)ns + 1);
+  uint64_t nchunks = 0, content = 0;
+  for (uint32_t i = 0; i < ns; i++) {
+    chunk_first[i] = (uint32_t)nchunks;
+    uint64_t len = tree->file_len[file_begin + i];
+    nchunks += (len + kChunkBytes - 1) / kChunkBytes;
+    content += len;
+  }
+  chunk_first[ns] = (uint32_t)nchunks;
+  if (nchunks > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard has too many 64 KiB chunks (%llu)", (unsigned long long)nchunks);
+  t->n_chunks = (uint32_t)nchunks;
+  t->shard_content = content;
+  t->shard_byte0 = ns ? tree->file_off[file_begin] : 0;
+  uint64_t shard_end = ns ? (tree->file_off[file_end - 1] + ((tree->file_len[file_end - 1] + 15) & ~15ull)) : 0;
+  t->shard_bytes = shard_end - t->shard_byte0 + 16;
+
+  CU(dev_alloc(&t->dir_parent, nd)); CU(dev_alloc(&t->dir_entry, nd)); CU(dev_alloc(&t->dir_depth, nd));
+  CU(dev_alloc(&t->level_dirs, nd)); CU(dev_alloc(&t->dir_flags, nd));
+  CU(dev_alloc(&t->entry_dir, ne)); CU(dev_alloc(&t->entry_name_off, (size_t)ne + 1)); CU(dev_alloc(&t->entry_child, ne));
+  CU(dev_alloc(&t->entry_type, ne)); CU(dev_alloc(&t->names, (size_t)tree->n_name_bytes));
+  CU(dev_alloc(&t->file_entry, nf)); CU(dev_alloc(&t->file_off, nf)); CU(dev_alloc(&t->file_len, nf));
+  CU(dev_alloc(&t->chunk_first, (size_t)ns + 1));
+  CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
+  CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne));
+  CU(dev_alloc(&t->dir_direct, nd)); CU(dev_alloc(&t->dir_first_war, nd)); CU(dev_alloc(&t->dir_content, nd));
+  CU(dev_alloc(&t->dir_main, nd)); CU(dev_alloc(&t->dir_subtree, nd)); CU(dev_alloc(&t->dir_main_sub, nd));
+  CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_hash, nd)); CU(dev_alloc(&t->dir_ignore, nd));
+  CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd)); CU(dev_alloc(&t->file_flags, nf));
+
+  cudaStream_t s = C->stream;
+  CU(cudaEventRecord(C->ev[0], s));
+  auto H2D = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess; };
+  CU(H2D(t->dir_parent, tree->dir_parent, 4ull * nd)); CU(H2D(t->dir_entry, tree->dir_entry, 4ull * nd));
+  CU(H2D(t->dir_depth, tree->dir_depth, 4ull * nd)); CU(H2D(t->dir_flags, tree->dir_flags, nd));
+  CU(H2D(t->level_dirs, level_dirs.data(), 4ull * nd));
+  CU(H2D(t->entry_dir, tree->entry_dir, 4ull * ne)); CU(H2D(t->entry_name_off, tree->entry_name_off, 4ull * ((size_t)ne + 1)));
+  CU(H2D(t->entry_child, tree->entry_child, 4ull * ne)); CU(H2D(t->entry_type, tree->entry_type, ne));
+  CU(H2D(t->names, tree->names, tree->n_name_bytes));
+  CU(H2D(t->file_entry, tree->file_entry, 4ull * nf)); CU(H2D(t->file_off, tree->file_off, 8ull * nf));
+  CU(H2D(t->file_len, tree->file_len, 8ull * nf));
+  CU(H2D(t->chunk_first, chunk_first.data(), 4ull * ((size_t)ns + 1)));
+  if (tree->bytes && t->shard_bytes > 16) CU(H2D(t->bytes, tree->bytes + t->shard_byte0, t->shard_bytes - 16));
+  CU(cudaMemsetAsync(t->bytes + (t->shard_bytes - 16), 0, 16, s));
+  CU(cudaEventRecord(C->ev[1], s));
+  CU(cudaStreamSynchronize(s));  // level_dirs / chunk_first are stack-owned host vectors
+  CU(cudaEventElapsedTime(&dt->ms_h2d, C->ev[0], C->ev[1]));
+  guard.keep = true;
+  *out = dt;
+  return M2K_OK;
+}
+
+extern "C" int m2k_synth_fill_device(m2k_ctx* ctx, m2k_devtree* dt, uint64_t seed) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  const TreeOwner* o = static_cast<const TreeOwner*>(t->host->owner);
+  if (!o || !o->synthetic) return fail(C, M2K_ERR_ARG, "m2k_synth_fill_device: not a synthetic tree");
+  if (seed != o->synth_seed) return fail(C, M2K_ERR_ARG, "seed differs from the tree's seed");
+  CU(cudaSetDevice(C->device));
+  if (!t->synth_class) {
+    CU(dev_alloc(&t->synth_class, t->n_files)); CU(dev_alloc(&t->synth_inject, t->n_files));
+    CU(cudaMemcpyAsync(t->synth_class, o->synth_class.data(), t->n_files, cudaMemcpyHostToDevice, C->stream));
+    CU(cudaMemcpyAsync(t->synth_inject, o->synth_inject.data(), 8ull * t->n_files, cudaMemcpyHostToDevice, C->stream));
+  }
+  launch_synth_fill(C, t, seed);
+  CU(cudaGetLastError());
+  for (size_t k = 0; k < o->literal_file.size(); k++) {
+    uint32_t f = o->literal_file[k];
+    if (f < t->file_begin || f >= t->file_end) continue;
+    uint64_t off = t->host->file_off[f] - t->shard_byte0;
+    uint64_t padded = (t->host->file_len[f] + 15) & ~15ull;
+    CU(cudaMemsetAsync(t->bytes + off, 0, padded, C->stream));
+    CU(cudaMemcpyAsync(t->bytes + off, o->literal_data[k].data(), o->literal_data[k].size(), cudaMemcpyHostToDevice, C->stream));
+  }
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+// ---- phase A --------------------------------------------------------------------------------
+extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  CU(cudaSetDevice(C->device));
+  cudaStream_t s = C->stream;
+  const bool content = !(params && params->skip_content);
+  CU(cudaMemsetAsync(t->dir_direct, 0, 4ull * t->n_dirs, s));
+  CU(cudaMemsetAsync(t->dir_first_war, 0xFF, 4ull * t->n_dirs, s));
+  CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
+  CU(cudaMemsetAsync(t->dir_main, 0xFF, 4ull * t->n_dirs, s));
+  CU(cudaMemsetAsync(t->file_flags, 0, t->n_files, s));
+  launch_name_features(C, t);
+  if (content) {
+    CU(cudaEventRecord(C->ev[2], s));
+    launch_scan_bytes(C, t, t->chunk_rec);
+    CU(cudaEventRecord(C->ev[3], s));
+    launch_file_combine(C, t, t->chunk_rec);
+    launch_dockerfile(C, t);
+  }
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(s));
+  if (content) CU(cudaEventElapsedTime(&C->last_scan_ms, C->ev[2], C->ev[3]));
+  t->scanned = true;
+  return M2K_OK;
+}
+
+extern "C" int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t** d_dir_content, uint32_t** d_dir_main, uint32_t* n_dirs) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  if (d_dir_content) *d_dir_content = dt->t.dir_content;
+  if (d_dir_main) *d_dir_main = dt->t.dir_main;
+  if (n_dirs) *n_dirs = dt->t.n_dirs;
+  return M2K_OK;
+}
+
+extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks) {
+  if (!ctx || !dt || !d_all_content || !d_all_main || !n_ranks) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  launch_merge_partials(C, &dt->t, d_all_content, d_all_main, n_ranks);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+// ---- phase C --------------------------------------------------------------------------------
+namespace {
+
+// entries in filepath.Walk order: climb to the common directory, then compare entry indices there
+bool walk_before(const m2k_tree* t, uint32_t a, uint32_t b) {
+  if (a == b) return false;
+  // chains of (entry) from the entry up to the root's children
+  auto chain = [&](uint32_t e, std::vector<uint32_t>* out) {
+    out->clear();
+    for (;;) {
+      out->push_back(e);
+      uint32_t d = t->entry_dir[e];
+      if (d == 0) break;
+      e = t->dir_entry[d];
+    }
+    std::reverse(out->begin(), out->end());
+  };
+  std::vector<uint32_t> ca, cb;
+  chain(a, &ca); chain(b, &cb);
+  size_t n = std::min(ca.size(), cb.size());
+  for (size_t i = 0; i < n; i++) if (ca[i] != cb[i]) return ca[i] < cb[i];
+  return ca.size() < cb.size();  // an ancestor directory comes before its contents
+}
+
+const uint8_t* host_file_bytes(const m2k_tree* t, uint32_t f, uint64_t* len) {
+  *len = t->file_len[f];
+  if (t->bytes) return t->bytes + t->file_off[f];
+  const TreeOwner* o = static_cast<const TreeOwner*>(t->owner);
+  if (o) for (size_t k = 0; k < o->literal_file.size(); k++)
+    if (o->literal_file[k] == f) return reinterpret_cast<const uint8_t*>(o->literal_data[k].data());
+  return nullptr;
+}
+
+char** dup_list(const std::vector<std::string>& v) {
+  char** out = static_cast<char**>(calloc(v.size() ? v.size() : 1, sizeof(char*)));
+  for (size_t i = 0; i < v.size(); i++) out[i] = strdup(v[i].c_str());
+  return out;
+}
+
+}  // namespace
+
+extern "C" void m2k_result_free(m2k_result* r) {
+  if (!r) return;
+  free(r->dir_opts); free(r->dir_direct); free(r->dir_subtree); free(r->dir_state); free(r->dir_ignore); free(r->dir_main_file);
+  free(r->file_flags); free(r->service_dirs); free(r->entry_feat);
+  for (uint32_t i = 0; i < r->n_ignore_dirs; i++) free(r->ignore_dirs[i]);
+  for (uint32_t i = 0; i < r->n_ignore_contents; i++) free(r->ignore_contents[i]);
+  free(r->ignore_dirs); free(r->ignore_contents);
+  free(r);
+}
+
+extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params, m2k_result** out) {
+  if (!ctx || !dt || !out) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  *out = nullptr;
+  if (!t->scanned) return fail(C, M2K_ERR_ARG, "m2k_finalize before m2k_scan");
+  CU(cudaSetDevice(C->device));
+  cudaStream_t s = C->stream;
+  const m2k_tree* tree = t->host;
+  const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
+  const uint32_t sh = params ? params->sh_flavor : M2K_SH_BASH;
+  m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
+  struct RG { m2k_result* r; bool keep = false; ~RG() { if (!keep) m2k_result_free(r); } } rg{r};
+  r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
+  auto HA = [&](size_t bytes) { return calloc(bytes ? bytes : 1, 1); };
+  r->dir_opts = (uint32_t*)HA(4ull * nd); r->dir_direct = (uint32_t*)HA(4ull * nd); r->dir_subtree = (uint32_t*)HA(4ull * nd);
+  r->dir_state = (uint8_t*)HA(nd); r->dir_ignore = (uint8_t*)HA(nd); r->dir_main_file = (uint32_t*)HA(4ull * nd);
+  r->file_flags = (uint8_t*)HA(nf); r->service_dirs = (uint32_t*)HA(4ull * nd); r->entry_feat = (uint32_t*)HA(4ull * ne);
+
+  // bottom-up and the predicate table do not depend on the ignore rules: queue them first
+  CU(cudaEventRecord(C->ev[4], s));
+  launch_subtree(C, t);
+  launch_combine_opts(C, t, sh);
+  CU(cudaMemcpyAsync(r->entry_feat, t->entry_feat, 4ull * ne, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+
+  // getIgnorePaths (any2kube.go:151-181): the .m2kignore files come from the name-feature bit
+  double h0 = now_ms();
+  std::vector<uint32_t> ign_entries;
+  for (uint32_t e = 0; e < ne; e++) if (r->entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
+  std::sort(ign_entries.begin(), ign_entries.end(), [&](uint32_t a, uint32_t b) { return walk_before(tree, a, b); });
+  std::vector<std::string> ign_dirs, ign_contents;
+  for (uint32_t e : ign_entries) {
+    uint32_t f = tree->entry_child[e];
+    if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
+    uint64_t len;
+    const uint8_t* data = host_file_bytes(tree, f, &len);
+    if (!data) {
+      if (len == 0) continue;
+      return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
+    }
+    std::string fpath = path_join(tree_dir_path(tree, tree->entry_dir[e]), ".m2kignore");
+    parse_ignore_file(fpath, data, len, &ign_dirs, &ign_contents);
+  }
+  // hash table over the case-folded entries; flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
+  const std::string root = tree->root_path ? tree->root_path : "";
+  uint8_t root_ignore = 0;
+  std::unordered_map<uint64_t, uint32_t> by_hash;
+  std::unordered_map<uint64_t, std::vector<std::pair<const std::string*, uint32_t>>> verify;
+  std::vector<std::string> pre;
+  for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
+  const uint64_t seed0 = 0xcbf29ce484222325ull;
+  auto add = [&](const std::string& sp, uint32_t flag) {
+    if (equal_fold(sp, root)) root_ignore |= (uint8_t)flag;
+    uint64_t key = hash_finish(hash_fold(seed0, sp));
+    by_hash[key] |= flag;
+    verify[key].push_back({&sp, flag});
+  };
+  for (const auto& x : ign_dirs) add(x, 1);
+  for (const auto& x : ign_contents) add(x, 2);
+  for (const auto& x : pre) add(x, 4);
+  std::vector<IgnoreSlot> table;
+  uint32_t table_mask = M2K_NONE;
+  IgnoreSlot* d_table = nullptr;
+  if (!by_hash.empty()) {
+    uint32_t cap = 16;
+    while (cap < by_hash.size() * 2) cap <<= 1;
+    table.assign(cap, IgnoreSlot{0, 0, 0});
+    table_mask = cap - 1;
+    for (const auto& kv : by_hash) {
+      uint32_t sidx = (uint32_t)kv.first & table_mask;
+      while (table[sidx].hash) sidx = (sidx + 1) & table_mask;
+      table[sidx].hash = kv.first; table[sidx].flags = kv.second;
+    }
+    CU(cudaMalloc(&d_table, sizeof(IgnoreSlot) * cap));
+    CU(cudaMemcpyAsync(d_table, table.data(), sizeof(IgnoreSlot) * cap, cudaMemcpyHostToDevice, s));
+  }
+  // hash state shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
+  std::string prefix1 = path_clean(root);
+  if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
+  uint64_t depth1_state = hash_fold(seed0, prefix1);
+  r->ms_host_ignore = (float)(now_ms() - h0);
+
+  launch_walk(C, t, d_table, table_mask, depth1_state, root_ignore);
+  CU(cudaEventRecord(C->ev[5], s));
+  CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_state, t->dir_state, nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_ignore, t->dir_ignore, nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, s));
+  CU(cudaEventRecord(C->ev[6], s));
+  cudaError_t werr = cudaStreamSynchronize(s);
+  if (d_table) cudaFree(d_table);
+  if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "walk kernels failed: %s", cudaGetErrorString(werr));
+  float ms_k = 0, ms_d = 0;
+  CU(cudaEventElapsedTime(&ms_k, C->ev[4], C->ev[5]));
+  CU(cudaEventElapsedTime(&ms_d, C->ev[5], C->ev[6]));
+  r->ms_kernels = ms_k; r->ms_d2h = ms_d;
+
+  // the hash join is exact only up to 64-bit collisions: confirm every hit with a real EqualFold
+  for (uint32_t d = 1; d < nd; d++) {
+    if (!r->dir_ignore[d]) continue;
+    std::string p = tree_dir_path(tree, d);
+    uint64_t key = hash_finish(hash_fold(seed0, p));
+    uint32_t exact = 0;
+    auto it = verify.find(key);
+    if (it != verify.end()) for (const auto& pr : it->second) if (equal_fold(*pr.first, p)) exact |= pr.second;
+    if (exact != r->dir_ignore[d])
+      return fail(C, M2K_ERR_UNSUPPORTED, "64-bit path-hash collision on directory %s: refusing to return inexact ignore decisions", p.c_str());
+  }
+  for (uint32_t d = 0; d < nd; d++) {
+    r->dir_direct[d] |= 0;  // direct name features; content bits are part of dir_subtree
+    if (r->dir_state[d] == M2K_DIR_SERVICE) r->service_dirs[r->n_services++] = d;
+  }
+  r->n_ignore_dirs = (uint32_t)ign_dirs.size(); r->ignore_dirs = dup_list(ign_dirs);
+  r->n_ignore_contents = (uint32_t)ign_contents.size(); r->ignore_contents = dup_list(ign_contents);
+  r->ms_h2d = dt->ms_h2d;
+  r->ms_scan_kernel = C->last_scan_ms;
+  r->n_kernel_launches = (uint32_t)C->launches;
+  rg.keep = true;
+  *out = r;
+  return M2K_OK;
+}
+
+// ---- the whole path: host buffers in, host results out ----------------------------------------
+extern "C" int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_params* params, m2k_result** out) {
+  if (!ctx || !tree || !out) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_detect: NULL argument");
+  *out = nullptr;
+  const bool content = !(params && params->skip_content);
+  if (content && !tree->bytes && tree->content_bytes) return fail(&ctx->c, M2K_ERR_ARG, "m2k_detect needs host bytes (tree->bytes is NULL); use the staged calls for device-filled trees");
+  double t0 = now_ms();
+  uint64_t l0 = ctx->c.launches;
+  m2k_devtree* dt = nullptr;
+  int rc = m2k_upload(ctx, tree, 0, content ? tree->n_files : 0, &dt);
+  if (rc != M2K_OK) return rc;
+  rc = m2k_scan(ctx, dt, params);
+  if (rc == M2K_OK) rc = m2k_finalize(ctx, dt, params, out);
+  m2k_devtree_free(ctx, dt);
+  if (rc == M2K_OK) {
+    (*out)->ms_total = (float)(now_ms() - t0);
+    (*out)->n_kernel_launches = (uint32_t)(ctx->c.launches - l0);
+  }
+  return rc;
+}
+
+// ---- host helpers exported for the mirror ----------------------------------------------------
+extern "C" int m2k_path_clean(const char* path, char* outbuf, size_t cap) {
+  if (!path || !outbuf || !cap) return M2K_ERR_ARG;
+  std::string c = path_clean(path);
+  if (c.size() + 1 > cap) return M2K_ERR_LIMIT;
+  memcpy(outbuf, c.c_str(), c.size() + 1);
+  return M2K_OK;
+}
+
+extern "C" int m2k_equal_fold(const char* a, size_t na, const char* b, size_t nb) {
+  return equal_fold(std::string(a ? a : "", a ? na : 0), std::string(b ? b : "", b ? nb : 0)) ? 1 : 0;
+}
+
+extern "C" int m2k_list_entries(const m2k_tree* tree, uint32_t feature_bit, const uint32_t* entry_feat, uint32_t* outv, uint32_t cap) {
+  if (!tree || !entry_feat || feature_bit > 31) return M2K_ERR_ARG;
+  std::vector<uint32_t> v;
+  for (uint32_t e = 0; e < tree->n_entries; e++) if (entry_feat[e] >> feature_bit & 1) v.push_back(e);
+  std::sort(v.begin(), v.end(), [&](uint32_t a, uint32_t b) { return walk_before(tree, a, b); });
+  for (size_t i = 0; i < v.size() && i < cap; i++) outv[i] = v[i];
+  return (int)v.size();
+}

@@ -1,0 +1,164 @@
+// Host-side path and .m2kignore handling with Go semantics.
+// Reference: internal/source/any2kube.go:151-181 (getIgnorePaths), internal/common/utils.go:308-315
+// (IsStringPresent / strings.EqualFold).  [external] path/filepath.Clean/Join/Dir, strings.TrimSpace and
+// bufio.Scanner follow the Go 1.15 standard library's documented behaviour.
+#include <string.h>
+
+#include <algorithm>
+
+#include "casefold_table.h"
+#include "gostr.h"
+#include "m2k_internal.h"
+
+namespace m2k {
+
+// filepath.Clean for Unix paths: lexical only.
+std::string path_clean(const std::string& p) {
+  if (p.empty()) return ".";
+  const bool rooted = p[0] == '/';
+  std::vector<std::string> parts;
+  size_t i = 0, n = p.size();
+  while (i < n) {
+    while (i < n && p[i] == '/') i++;
+    size_t j = i;
+    while (j < n && p[j] != '/') j++;
+    if (j > i) {
+      std::string comp = p.substr(i, j - i);
+      if (comp == ".") {
+      } else if (comp == "..") {
+        if (!parts.empty() && parts.back() != "..") parts.pop_back();
+        else if (!rooted) parts.push_back(comp);
+      } else {
+        parts.push_back(comp);
+      }
+    }
+    i = j;
+  }
+  std::string out = rooted ? "/" : "";
+  for (size_t k = 0; k < parts.size(); k++) {
+    if (k) out += '/';
+    out += parts[k];
+  }
+  return out.empty() ? "." : out;
+}
+
+// filepath.Join of two elements: empty elements are dropped, the result is cleaned.
+std::string path_join(const std::string& a, const std::string& b) {
+  if (a.empty() && b.empty()) return "";
+  if (a.empty()) return path_clean(b);
+  if (b.empty()) return path_clean(a);
+  return path_clean(a + "/" + b);
+}
+
+// filepath.Dir
+std::string path_dir(const std::string& p) {
+  size_t s = p.rfind('/');
+  return path_clean(s == std::string::npos ? std::string() : p.substr(0, s + 1));
+}
+
+bool equal_fold(const std::string& a, const std::string& b) {
+  const uint8_t* pa = reinterpret_cast<const uint8_t*>(a.data());
+  const uint8_t* pb = reinterpret_cast<const uint8_t*>(b.data());
+  size_t i = 0, j = 0;
+  while (i < a.size() && j < b.size()) {
+    uint32_t wa, wb;
+    uint32_t ra = fold_rune(decode_rune(pa + i, a.size() - i, &wa), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
+    uint32_t rb = fold_rune(decode_rune(pb + j, b.size() - j, &wb), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
+    if (ra != rb) return false;
+    i += wa;
+    j += wb;
+  }
+  return i == a.size() && j == b.size();
+}
+
+uint64_t hash_fold(uint64_t h, const std::string& s) {
+  return hash_fold_bytes(h, reinterpret_cast<const uint8_t*>(s.data()), s.size(), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
+}
+
+// strings.TrimSpace on [b, e)
+static void trim_space(const uint8_t*& b, const uint8_t*& e) {
+  while (b < e) {
+    uint32_t w;
+    if (!is_space_rune(decode_rune(b, (size_t)(e - b), &w))) break;
+    b += w;
+  }
+  while (e > b) {
+    // utf8.DecodeLastRune: back up over at most three continuation bytes
+    const uint8_t* s = e - 1;
+    uint32_t r, w = 1;
+    if (*s < 0x80) {
+      r = *s;
+    } else {
+      const uint8_t* lim = (e - b > 4) ? e - 4 : b;
+      while (s > lim && (*s & 0xC0) == 0x80) s--;
+      uint32_t ww;
+      r = decode_rune(s, (size_t)(e - s), &ww);
+      if (s + ww != e) { r = 0xFFFD; w = 1; } else w = ww;
+    }
+    if (!is_space_rune(r)) break;
+    e -= w;
+  }
+}
+
+// One .m2kignore file (any2kube.go:158-177): bufio.Scanner lines (64 KiB cap: a longer line ends
+// the scan silently), TrimSpace, a trailing '*' (one) marks "ignore contents", Join with the
+// file's directory.
+void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64_t len, std::vector<std::string>* ignore_dirs,
+                       std::vector<std::string>* ignore_contents) {
+  const std::string dir = path_dir(file_path);
+  uint64_t pos = 0;
+  while (pos < len) {
+    const uint8_t* nl = static_cast<const uint8_t*>(memchr(data + pos, '\n', len - pos));
+    uint64_t end = nl ? (uint64_t)(nl - data) : len;
+    if (end - pos >= kLongLine) break;
+    const uint8_t* b = data + pos;
+    const uint8_t* e = data + end;
+    if (e > b && e[-1] == '\r') e--;
+    trim_space(b, e);
+    std::string line(reinterpret_cast<const char*>(b), (size_t)(e - b));
+    if (!line.empty() && line.back() == '*') {
+      line.pop_back();
+      ignore_contents->push_back(path_join(dir, line));
+    } else {
+      ignore_dirs->push_back(path_join(dir, line));
+    }
+    pos = end + 1;
+  }
+}
+
+static std::string entry_name(const m2k_tree* t, uint32_t e) {
+  return std::string(reinterpret_cast<const char*>(t->names + t->entry_name_off[e]), t->entry_name_off[e + 1] - t->entry_name_off[e]);
+}
+
+// The path filepath.Walk reports for directory d: the root exactly as given, below it Join(parent, name).
+std::string tree_dir_path(const m2k_tree* t, uint32_t d) {
+  if (d == 0) return t->root_path ? t->root_path : "";
+  std::vector<uint32_t> chain;
+  for (uint32_t x = d; x != 0; x = t->dir_parent[x]) chain.push_back(x);
+  std::string p = t->root_path ? t->root_path : "";
+  for (size_t k = chain.size(); k-- > 0;) p = path_join(p, entry_name(t, t->dir_entry[chain[k]]));
+  return p;
+}
+
+// filepath.Walk order over all entries: a directory's entries in name order, descending into each
+// sub-directory right after its own entry.
+void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out) {
+  out->clear();
+  if (!t->n_dirs) return;
+  out->reserve(t->n_entries);
+  struct Frame { uint32_t e, end; };
+  std::vector<Frame> st;
+  st.push_back({t->dir_first_entry[0], t->dir_first_entry[1]});
+  while (!st.empty()) {
+    Frame& f = st.back();
+    if (f.e == f.end) { st.pop_back(); continue; }
+    uint32_t e = f.e++;
+    out->push_back(e);
+    if ((t->entry_type[e] & 0xF) == M2K_T_DIR) {
+      uint32_t d = t->entry_child[e];
+      if (!(t->dir_flags[d] & 1)) st.push_back({t->dir_first_entry[d], t->dir_first_entry[d + 1]});
+    }
+  }
+}
+
+}  // namespace m2k

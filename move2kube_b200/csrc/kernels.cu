@@ -1,0 +1,548 @@
+// sm_100a kernels of the source-detection path.  HBM-bound integer/byte work: the rules that
+// matter are coalesced 16-byte loads, enough bytes in flight per SM, and grids sized in multiples
+// of the SM count (DESIGN.md has the per-kernel rooflines).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "casefold_table.h"
+#include "dockerfile_dev.cuh"
+#include "gostr.h"
+#include "m2k_internal.h"
+#include "synth.h"
+
+namespace m2k {
+
+#define FULL 0xFFFFFFFFu
+
+// ---------------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+__global__ void k_fill_u32(uint32_t* p, uint32_t v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = v;
+}
+
+void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n) {
+  if (!n) return;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > c->sm_count * 8) blocks = c->sm_count * 8;
+  k_fill_u32<<<blocks, 256, 0, c->stream>>>(p, v, n);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 1: name features.  One thread per directory entry; the signature table (exact names,
+// suffixes) is staged in shared memory; a warp-level segmented OR (match_any + redux) folds the
+// entries of one directory before a single atomicOr per (warp, directory).
+// Replaces: [ -f D/name ] / find -name "*.ext" / "$1/"*.war of the 18 detect scripts
+// (internal/assets/*/m2k*detect.sh) and GetFilesByName's basename test (utils.go:108-113).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_name_features(
+    uint32_t n_entries, const uint32_t* __restrict__ entry_dir, const uint32_t* __restrict__ entry_name_off,
+    const uint8_t* __restrict__ entry_type, const uint8_t* __restrict__ names, const NameSig* __restrict__ sigs, int n_sigs,
+    uint32_t* __restrict__ entry_feat, uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_first_war) {
+  __shared__ NameSig s_sigs[kMaxNameSigs];
+  for (int i = threadIdx.x; i < n_sigs; i += blockDim.x) s_sigs[i] = sigs[i];
+  __syncthreads();
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  bool valid = e < n_entries;
+  uint32_t feat = 0, dir = M2K_NONE;
+  if (valid) {
+    dir = entry_dir[e];
+    uint32_t off = entry_name_off[e], len = entry_name_off[e + 1] - off;
+    uint32_t type = entry_type[e];
+    uint32_t lt = type & 0xF, ft = type >> 4;
+    // the last <=16 bytes of the name, right aligned: byte 0 of lo is the last character
+    uint64_t lo = 0, hi = 0;
+    uint32_t take = len < 16 ? len : 16;
+    for (uint32_t i = 0; i < take; i++) {
+      uint64_t ch = names[off + len - 1 - i];
+      if (i < 8) lo |= ch << (8 * i); else hi |= ch << (8 * (i - 8));
+    }
+    uint32_t first = len ? names[off] : 0;
+    if (lt != M2K_T_ERR) {
+      for (int s = 0; s < n_sigs; s++) {
+        const NameSig& g = s_sigs[s];
+        bool m = (g.kind == 0) ? (len == g.len) : (len >= g.len);
+        m = m && ((lo & g.mask_lo) == g.lo) && ((hi & g.mask_hi) == g.hi);
+        if (!m) continue;
+        if (g.need == 1 && ft != M2K_T_REG) continue;
+        if (g.need == 2 && lt == M2K_T_DIR) continue;
+        if (g.need == 3 && first == '.') continue;
+        feat |= 1u << g.feature;
+      }
+    }
+    entry_feat[e] = feat;
+    if (feat & (1u << M2K_N_WAR)) atomicMin(&dir_first_war[dir], e);  // entries are name-sorted inside a directory
+  }
+  // segmented OR over the lanes that share a directory
+  uint32_t peers = __match_any_sync(FULL, dir);
+  uint32_t dirfeat = feat & ~(1u << M2K_N_WAR);  // the war bit of a directory is decided from dir_first_war
+  uint32_t ored = __reduce_or_sync(peers, dirfeat);
+  if (valid && ored && (uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicOr(&dir_direct[dir], ored);
+}
+
+void launch_name_features(Ctx* c, DevTree* t) {
+  if (!t->n_entries) return;
+  uint32_t blocks = (t->n_entries + 255) / 256;
+  k_name_features<<<blocks, 256, 0, c->stream>>>(t->n_entries, t->entry_dir, t->entry_name_off, t->entry_type, t->names,
+                                                 c->d_sigs, c->n_sigs, t->entry_feat, t->dir_direct, t->dir_first_war);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 2: byte scan -- the HBM-roofline kernel.  One warp per 64 KiB chunk of one file; a warp
+// row is 32 lanes x 16 bytes = 512 contiguous bytes, 8 rows in flight per lane.
+//   * "__main__" (python detect scripts :21/:22): any occurrence fully contains one 4-byte ALIGNED
+//     word equal to "__ma", "_mai", "main" or "ain_", so the streaming test is four compares per
+//     word; the rare hit is confirmed bytewise from global memory (file bounds respected).
+//   * line length (bufio.Scanner's 64 KiB cap inside dockerparser.Parse, dockerfile2kube.go:124): per
+//     16-byte unit "has a newline" (SWAR), ballot per row, and a warp-uniform count of consecutive
+//     newline-free units.  Only lead/trail counts leave the chunk; k_file_combine stitches chunks
+//     and does the exact byte count for the (rare) runs of >= 4095 free units.
+// Algorithmic traffic: every content byte read once + 4 B written per 64 KiB.
+// ---------------------------------------------------------------------------------------------
+constexpr int kScanRows = 8;        // rows (512 B each) loaded before use
+constexpr int kScanThreads = 256;
+
+__device__ __forceinline__ uint32_t has_newline(uint4 v) {
+  const uint32_t nl = 0x0A0A0A0Au, ones = 0x01010101u;
+  uint32_t x0 = v.x ^ nl, x1 = v.y ^ nl, x2 = v.z ^ nl, x3 = v.w ^ nl;
+  uint32_t t = ((x0 - ones) & ~x0) | ((x1 - ones) & ~x1) | ((x2 - ones) & ~x2) | ((x3 - ones) & ~x3);
+  return t & 0x80808080u;
+}
+
+__device__ __forceinline__ bool main_word(uint32_t w) {
+  // little-endian words of "__ma" "_mai" "main" "ain_"
+  return w == 0x616D5F5Fu || w == 0x69616D5Fu || w == 0x6E69616Du || w == 0x5F6E6961u;
+}
+
+// exact check around an aligned word hit at file offset `pos`
+__device__ __noinline__ bool confirm_main(const uint8_t* file, uint64_t len, uint64_t pos) {
+  const char* pat = "__main__";
+  for (int back = 0; back <= 3; back++) {
+    if (pos < (uint64_t)back) break;
+    uint64_t s = pos - back;
+    if (s + 8 > len) continue;
+    bool ok = true;
+    for (int i = 0; i < 8; i++) ok = ok && file[s + i] == (uint8_t)pat[i];
+    if (ok) return true;
+  }
+  return false;
+}
+
+__global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
+    uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first,
+    const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, uint32_t file_begin,
+    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, uint32_t* __restrict__ chunk_rec) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t warps_per_block = kScanThreads / 32;
+  const uint32_t n_warps = gridDim.x * warps_per_block;
+  for (uint32_t item = blockIdx.x * warps_per_block + (threadIdx.x >> 5); item < n_chunks; item += n_warps) {
+    // which file: last f with chunk_first[f] <= item (empty files share their successor's value)
+    uint32_t lo = 0, hi = n_shard_files;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (chunk_first[mid] <= item) lo = mid; else hi = mid; }
+    const uint32_t f = file_begin + lo;
+    const uint64_t flen = file_len[f];
+    const uint64_t start = (uint64_t)(item - chunk_first[lo]) * kChunkBytes;
+    const uint8_t* fbase = bytes + (file_off[f] - shard_byte0);
+    const uint64_t range = flen - start < kChunkBytes ? flen - start : kChunkBytes;
+    const uint32_t n_units = (uint32_t)((range + 15) >> 4);
+    const uint4* src = reinterpret_cast<const uint4*>(fbase + start);
+    uint32_t q = 0, lead = M2K_NONE, found = 0;
+    for (uint32_t u0 = 0; u0 < n_units; u0 += 32 * kScanRows) {
+      uint4 v[kScanRows];
+#pragma unroll
+      for (int r = 0; r < kScanRows; r++) {
+        uint32_t u = u0 + r * 32 + lane;
+        v[r] = u < n_units ? ldg_stream(src + u) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int r = 0; r < kScanRows; r++) {
+        uint32_t ubase = u0 + r * 32;
+        if (ubase >= n_units) break;  // warp-uniform
+        uint32_t valid = n_units - ubase < 32 ? n_units - ubase : 32;
+        bool hit = main_word(v[r].x) || main_word(v[r].y) || main_word(v[r].z) || main_word(v[r].w);
+        uint32_t nlm = has_newline(v[r]);
+        uint32_t B = __ballot_sync(FULL, nlm != 0);
+        if (__any_sync(FULL, hit)) {
+          bool ok = false;
+          if (hit) {
+            uint64_t pos = start + (uint64_t)(ubase + lane) * 16;
+            if (main_word(v[r].x)) ok = ok || confirm_main(fbase, flen, pos);
+            if (main_word(v[r].y)) ok = ok || confirm_main(fbase, flen, pos + 4);
+            if (main_word(v[r].z)) ok = ok || confirm_main(fbase, flen, pos + 8);
+            if (main_word(v[r].w)) ok = ok || confirm_main(fbase, flen, pos + 12);
+          }
+          if (__any_sync(FULL, ok)) found = 1;
+        }
+        if (B == 0) q += valid;
+        else {
+          uint32_t firstl = __ffs(B) - 1, lastl = 31 - __clz(B);
+          if (lead == M2K_NONE) lead = q + firstl;
+          q = valid - 1 - lastl;
+        }
+      }
+    }
+    if (lead == M2K_NONE) lead = q;
+    if (lane == 0) chunk_rec[item] = rec_pack(lead, q, found);
+  }
+}
+
+void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec) {
+  if (!t->n_chunks) return;
+  uint32_t warps_per_block = kScanThreads / 32;
+  uint32_t want = (t->n_chunks + warps_per_block - 1) / warps_per_block;
+  uint32_t cap = (uint32_t)c->sm_count * 4 * 8;  // resident blocks x 8 waves of items per warp slot
+  uint32_t blocks = want < cap ? want : cap;
+  k_scan_bytes<<<blocks, kScanThreads, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
+                                                       t->file_len, t->file_begin, t->bytes, t->shard_byte0, chunk_rec);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 3: per-file combine of the chunk records (one warp per file).  Produces HAS_MAIN and
+// LONG_LINE, and the per-directory content partials for "__main__" in a file named *py.
+// ---------------------------------------------------------------------------------------------
+struct RunAcc {            // monoid over a span of 16-byte units
+  uint64_t units;          // units in the span
+  uint64_t lead, trail;    // newline-free units at both ends (== units when all free)
+  uint32_t longf;          // an exact check inside the span found a line >= 64 KiB
+};
+
+// exact length in bytes of the newline-free run that covers units [u0, u0 + nq) of the file
+__device__ bool run_is_long(const uint8_t* file, uint64_t len, uint64_t u0, uint64_t nq) {
+  uint64_t b = u0 * 16, e = (u0 + nq) * 16;
+  if (e > len) e = len;
+  while (b > 0 && file[b - 1] != '\n') b--;
+  while (e < len && file[e] != '\n') e++;
+  // bufio.Scanner drops nothing here: the '\r' of "\r\n" counts toward the token length
+  return e - b >= kLongLine;
+}
+
+__device__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b, const uint8_t* file, uint64_t len, uint64_t a_start_unit) {
+  if (a.units == 0) return b;
+  if (b.units == 0) return a;
+  RunAcc r;
+  r.units = a.units + b.units;
+  r.longf = a.longf | b.longf;
+  bool a_free = a.lead == a.units, b_free = b.lead == b.units;
+  r.lead = a_free ? a.units + b.lead : a.lead;
+  r.trail = b_free ? b.units + a.trail : b.trail;
+  if (!a_free && !b_free) {  // a run closed on both sides: decide it now
+    uint64_t mid = a.trail + b.lead;
+    if (mid >= kLongUnits && run_is_long(file, len, a_start_unit + a.units - a.trail, mid)) r.longf = 1;
+  }
+  return r;
+}
+
+__global__ void __launch_bounds__(256) k_file_combine(
+    uint32_t n_shard_files, uint32_t file_begin, const uint32_t* __restrict__ chunk_first, const uint32_t* __restrict__ chunk_rec,
+    const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, const uint8_t* __restrict__ bytes,
+    uint64_t shard_byte0, const uint32_t* __restrict__ file_entry, const uint32_t* __restrict__ entry_dir,
+    const uint32_t* __restrict__ entry_name_off, const uint8_t* __restrict__ names, uint8_t* __restrict__ file_flags,
+    uint32_t* __restrict__ dir_content, uint32_t* __restrict__ dir_main) {
+  uint32_t lane = threadIdx.x & 31;
+  uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n_shard_files) return;
+  uint32_t f = file_begin + w;
+  uint64_t len = file_len[f];
+  const uint8_t* file = bytes + (file_off[f] - shard_byte0);
+  uint32_t c0 = chunk_first[w], c1 = chunk_first[w + 1], nc = c1 - c0;
+  // each lane folds a contiguous slice of the records, then lane 0 folds the 32 partials
+  uint32_t per = (nc + 31) / 32;
+  uint32_t k0 = lane * per < nc ? lane * per : nc, k1 = (lane + 1) * per < nc ? (lane + 1) * per : nc;
+  RunAcc acc{0, 0, 0, 0};
+  uint32_t has_main = 0;
+  uint64_t total_units = (len + 15) >> 4;
+  uint64_t slice_start = (uint64_t)k0 * kUnitsPerChunk;
+  for (uint32_t k = k0; k < k1; k++) {
+    uint32_t rec = chunk_rec[c0 + k];
+    uint64_t ustart = (uint64_t)k * kUnitsPerChunk;
+    uint64_t nu = total_units - ustart < kUnitsPerChunk ? total_units - ustart : kUnitsPerChunk;
+    RunAcc b{nu, rec_lead(rec), rec_trail(rec), 0};
+    has_main |= rec_main(rec);
+    acc = acc_merge(acc, b, file, len, slice_start);
+  }
+  has_main = __any_sync(FULL, has_main);
+  RunAcc tot{0, 0, 0, 0};
+  uint64_t tot_start = 0;
+  for (int l = 0; l < 32; l++) {
+    RunAcc b;
+    b.units = __shfl_sync(FULL, acc.units, l);
+    b.lead = __shfl_sync(FULL, acc.lead, l);
+    b.trail = __shfl_sync(FULL, acc.trail, l);
+    b.longf = __shfl_sync(FULL, acc.longf, l);
+    if (lane == 0) tot = acc_merge(tot, b, file, len, tot_start);
+  }
+  if (lane == 0) {
+    uint32_t longf = tot.longf;
+    if (!longf && tot.units) {
+      bool all_free = tot.lead == tot.units;
+      // runs open toward the file start / end
+      if (tot.lead >= kLongUnits && run_is_long(file, len, 0, tot.lead)) longf = 1;
+      if (!all_free && tot.trail >= kLongUnits && run_is_long(file, len, tot.units - tot.trail, tot.trail)) longf = 1;
+    }
+    uint32_t flags = (has_main ? M2K_FILE_HAS_MAIN : 0) | (longf ? M2K_FILE_LONG_LINE : 0);
+    file_flags[f] = (uint8_t)flags;
+    if (has_main) {
+      uint32_t e = file_entry[f];
+      uint32_t off = entry_name_off[e], nl = entry_name_off[e + 1] - off;
+      if (nl >= 2 && names[off + nl - 2] == 'p' && names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
+        uint32_t d = entry_dir[e];
+        atomicOr(&dir_content[d], 1u << M2K_C_MAIN_PY);
+        atomicMin(&dir_main[d], f);
+      }
+    }
+  }
+}
+
+void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec) {
+  uint32_t nf = t->file_end - t->file_begin;
+  if (!nf) return;
+  uint32_t blocks = (nf + 7) / 8;
+  k_file_combine<<<blocks, 256, 0, c->stream>>>(nf, t->file_begin, t->chunk_first, chunk_rec, t->file_off, t->file_len, t->bytes,
+                                                t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
+                                                t->file_flags, t->dir_content, t->dir_main);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 4: isDockerFile, one thread per file (dockerfile_dev.cuh).  Nearly every file leaves after
+// a few bytes ("first instruction is not FROM"); real Dockerfiles are parsed to the end.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_dockerfile(
+    uint32_t n_shard_files, uint32_t file_begin, const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len,
+    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, const uint32_t* __restrict__ file_entry,
+    const uint32_t* __restrict__ entry_dir, uint8_t* __restrict__ file_flags, uint32_t* __restrict__ dir_content) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_shard_files) return;
+  uint32_t f = file_begin + i;
+  uint32_t flags = file_flags[f];
+  uint32_t bits = df::classify(bytes + (file_off[f] - shard_byte0), file_len[f], (flags & M2K_FILE_LONG_LINE) != 0);
+  if (bits) {
+    file_flags[f] = (uint8_t)(flags | bits);
+    if (bits & M2K_FILE_DOCKERFILE) atomicOr(&dir_content[entry_dir[file_entry[f]]], 1u << M2K_C_DOCKERFILE);
+  }
+}
+
+void launch_dockerfile(Ctx* c, DevTree* t) {
+  uint32_t nf = t->file_end - t->file_begin;
+  if (!nf) return;
+  k_dockerfile<<<(nf + 127) / 128, 128, 0, c->stream>>>(nf, t->file_begin, t->file_off, t->file_len, t->bytes, t->shard_byte0,
+                                                        t->file_entry, t->entry_dir, t->file_flags, t->dir_content);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 5: subtree OR / MIN, bottom-up one level per launch (find's recursion, done once for all
+// directories instead of once per visited directory).
+// ---------------------------------------------------------------------------------------------
+__global__ void k_subtree_init(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, const uint32_t* __restrict__ dir_content,
+                               const uint32_t* __restrict__ dir_main, uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs) return;
+  dir_subtree[d] = dir_direct[d] | dir_content[d];
+  dir_main_sub[d] = dir_main[d];
+}
+__global__ void k_subtree_level(const uint32_t* __restrict__ level_dirs, uint32_t n, const uint32_t* __restrict__ dir_parent,
+                                uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t d = level_dirs[i], p = dir_parent[d];
+  uint32_t s = dir_subtree[d];
+  if (s) atomicOr(&dir_subtree[p], s);
+  uint32_t m = dir_main_sub[d];
+  if (m != M2K_NONE) atomicMin(&dir_main_sub[p], m);
+}
+
+void launch_subtree(Ctx* c, DevTree* t) {
+  if (!t->n_dirs) return;
+  k_subtree_init<<<(t->n_dirs + 255) / 256, 256, 0, c->stream>>>(t->n_dirs, t->dir_direct, t->dir_content, t->dir_main,
+                                                                t->dir_subtree, t->dir_main_sub);
+  c->launches++;
+  for (uint32_t L = t->max_depth; L >= 1; L--) {
+    uint32_t a = t->level_off[L], b = t->level_off[L + 1];
+    if (b > a) {
+      k_subtree_level<<<(b - a + 255) / 256, 256, 0, c->stream>>>(t->level_dirs + a, b - a, t->dir_parent, t->dir_subtree, t->dir_main_sub);
+      c->launches++;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 6: the 18 built-in predicates per directory (SURVEY.md App. A truth table).
+// D = features of the directory's own entries, S = OR over the subtree.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_combine_opts(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, const uint32_t* __restrict__ dir_subtree,
+                               const uint32_t* __restrict__ dir_first_war, const uint8_t* __restrict__ entry_type,
+                               uint32_t sh_flavor, uint32_t* __restrict__ dir_opts) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs) return;
+  uint32_t D = dir_direct[d], S = dir_subtree[d];
+  auto F = [&](int b) { return (D >> b) & 1u; };
+  auto R = [&](int b) { return (S >> b) & 1u; };
+  uint32_t fw = dir_first_war[d];
+  uint32_t W = (fw != M2K_NONE && (entry_type[fw] >> 4) != M2K_T_ERR) ? 1u : 0u;  // [ -e first match ]
+  uint32_t py = (sh_flavor == M2K_SH_BASH) ? (F(M2K_F_REQUIREMENTS) | F(M2K_F_SETUP_PY) | F(M2K_F_ENVIRONMENT_YML) | F(M2K_F_PIPFILE)) : 0u;
+  uint32_t m = 0;
+  m |= F(M2K_F_PIPFILE) << M2K_DF_DJANGO;
+  m |= R(M2K_R_GO) << M2K_DF_GOLANG;
+  m |= (W << M2K_DF_WAR_JBOSS) | (W << M2K_DF_WAR_LIBERTY) | (W << M2K_DF_WAR_TOMCAT);
+  m |= F(M2K_F_BUILD_XML) << M2K_DF_JAVAANT;
+  m |= F(M2K_F_BUILD_GRADLE) << M2K_DF_JAVAGRADLE;
+  m |= F(M2K_F_POM_XML) << M2K_DF_JAVAMAVEN;
+  m |= F(M2K_F_PACKAGE_JSON) << M2K_DF_NODEJS;
+  m |= R(M2K_R_PHP) << M2K_DF_PHP;
+  m |= py << M2K_DF_PYTHON;
+  m |= F(M2K_F_GEMFILE) << M2K_DF_RUBY;
+  m |= (F(M2K_F_GO_MOD) | R(M2K_R_GO)) << M2K_S2I_GOLANG;
+  m |= ((1u ^ F(M2K_F_BUILD_GRADLE)) & (1u ^ F(M2K_F_BUILD_XML)) & (F(M2K_F_POM_XML) | R(M2K_R_JAVA))) << M2K_S2I_JAVA;
+  m |= F(M2K_F_PACKAGE_JSON) << M2K_S2I_NODEJS;
+  m |= R(M2K_R_PHP) << M2K_S2I_PHP;
+  m |= py << M2K_S2I_PYTHON;
+  m |= F(M2K_F_GEMFILE) << M2K_S2I_RUBY;
+  dir_opts[d] = m;
+}
+
+void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor) {
+  if (!t->n_dirs) return;
+  k_combine_opts<<<(t->n_dirs + 255) / 256, 256, 0, c->stream>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_first_war,
+                                                                t->entry_type, sh_flavor, t->dir_opts);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel 7: the walk (any2kube.go:58-98), top-down one level per launch.  Per directory: extend the
+// parent's case-folded path hash by "/name", probe the ignore table (hash join in place of
+// O(#dirs x #entries) EqualFold scans, utils.go:308-315), then apply the walk's rules given whether
+// the parent was visited and descended into.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_walk_level(const uint32_t* __restrict__ level_dirs, uint32_t n, uint32_t level,
+                             const uint32_t* __restrict__ dir_parent, const uint32_t* __restrict__ dir_entry,
+                             const uint8_t* __restrict__ dir_flags, const uint32_t* __restrict__ entry_name_off,
+                             const uint8_t* __restrict__ names, const uint32_t* __restrict__ fold_from,
+                             const uint32_t* __restrict__ fold_to, const IgnoreSlot* __restrict__ table, uint32_t table_mask,
+                             uint64_t depth1_state, uint8_t root_ignore, const uint32_t* __restrict__ dir_opts,
+                             uint64_t* __restrict__ dir_hash, uint8_t* __restrict__ dir_ignore, uint8_t* __restrict__ dir_state,
+                             uint8_t* __restrict__ dir_descend) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t d = level_dirs[i];
+  uint32_t ign = 0;
+  bool visited;
+  if (level == 0) {
+    ign = root_ignore;  // the root path is compared on the host exactly as given
+    visited = true;
+  } else {
+    uint32_t p = dir_parent[d];
+    uint64_t h = (level == 1) ? depth1_state : hash_step(dir_hash[p], '/');
+    uint32_t e = dir_entry[d];
+    uint32_t off = entry_name_off[e], len = entry_name_off[e + 1] - off;
+    h = hash_fold_bytes(h, names + off, len, fold_from, fold_to, M2K_CASEFOLD_N);
+    dir_hash[d] = h;
+    if (table_mask != M2K_NONE) {
+      uint64_t key = hash_finish(h);
+      for (uint32_t s = (uint32_t)key & table_mask;; s = (s + 1) & table_mask) {
+        uint64_t k = table[s].hash;
+        if (k == 0) break;
+        if (k == key) { ign = table[s].flags; break; }
+      }
+    }
+    visited = dir_state[p] != M2K_DIR_NOT_VISITED && dir_descend[p];
+  }
+  dir_ignore[d] = (uint8_t)ign;
+  uint32_t state, descend = 0;
+  if (!visited) state = M2K_DIR_NOT_VISITED;
+  else if (dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
+  else if (ign & 4) state = M2K_DIR_PRECONTAINERIZED;
+  else if (ign & 1) { if (ign & 2) state = M2K_DIR_IGNORED_PRUNE; else { state = M2K_DIR_IGNORED_DESCEND; descend = 1; } }
+  else if (dir_opts[d] == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
+  else state = M2K_DIR_SERVICE;
+  dir_state[d] = (uint8_t)state;
+  dir_descend[d] = (uint8_t)descend;
+}
+
+void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, uint64_t depth1_state, uint8_t root_ignore) {
+  for (uint32_t L = 0; L <= t->max_depth && t->n_dirs; L++) {
+    uint32_t a = t->level_off[L], b = t->level_off[L + 1];
+    if (b <= a) continue;
+    k_walk_level<<<(b - a + 127) / 128, 128, 0, c->stream>>>(t->level_dirs + a, b - a, L, t->dir_parent, t->dir_entry, t->dir_flags,
+                                                            t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to, table,
+                                                            table_mask, depth1_state, root_ignore, t->dir_opts, t->dir_hash,
+                                                            t->dir_ignore, t->dir_state, t->dir_descend);
+    c->launches++;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-GPU: fold the gathered per-directory partials (rank-major) into this rank's arrays
+// ---------------------------------------------------------------------------------------------
+__global__ void k_merge_partials(uint32_t n_dirs, uint32_t n_ranks, const uint32_t* __restrict__ all_content,
+                                 const uint32_t* __restrict__ all_main, uint32_t* __restrict__ dir_content, uint32_t* __restrict__ dir_main) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs) return;
+  uint32_t o = 0, m = M2K_NONE;
+  for (uint32_t r = 0; r < n_ranks; r++) {
+    o |= all_content[(size_t)r * n_dirs + d];
+    uint32_t v = all_main[(size_t)r * n_dirs + d];
+    m = v < m ? v : m;
+  }
+  dir_content[d] = o;
+  dir_main[d] = m;
+}
+
+void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, const uint32_t* all_main, uint32_t n_ranks) {
+  if (!t->n_dirs) return;
+  k_merge_partials<<<(t->n_dirs + 255) / 256, 256, 0, c->stream>>>(t->n_dirs, n_ranks, all_content, all_main, t->dir_content, t->dir_main);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// synthetic content, generated in place in HBM (same function as the host fill, synth.h)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_synth_fill(
+    uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first, const uint64_t* __restrict__ file_off,
+    const uint64_t* __restrict__ file_len, uint32_t file_begin, const uint8_t* __restrict__ synth_class,
+    const uint64_t* __restrict__ synth_inject, uint64_t seed, uint8_t* __restrict__ bytes, uint64_t shard_byte0) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t n_warps = gridDim.x * (blockDim.x / 32);
+  for (uint32_t item = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5); item < n_chunks; item += n_warps) {
+    uint32_t lo = 0, hi = n_shard_files;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (chunk_first[mid] <= item) lo = mid; else hi = mid; }
+    uint32_t f = file_begin + lo;
+    uint64_t flen = file_len[f];
+    uint64_t ublock0 = (uint64_t)(item - chunk_first[lo]) * kUnitsPerChunk;
+    uint64_t total_units = (flen + 15) >> 4;
+    uint32_t n_units = (uint32_t)(total_units - ublock0 < kUnitsPerChunk ? total_units - ublock0 : kUnitsPerChunk);
+    uint64_t key = synth_file_key(seed, f);
+    uint8_t cls = synth_class[f];
+    uint64_t inj = synth_inject[f];
+    uint4* dst = reinterpret_cast<uint4*>(bytes + (file_off[f] - shard_byte0)) + ublock0;
+    for (uint32_t u = lane; u < n_units; u += 32) {
+      union { uint8_t b[16]; uint4 v; } blk;
+      synth_block16(key, cls, flen, inj, ublock0 + u, blk.b);
+      dst[u] = blk.v;
+    }
+  }
+}
+
+void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed) {
+  if (!t->n_chunks) return;
+  uint32_t want = (t->n_chunks + 7) / 8;
+  uint32_t cap = (uint32_t)c->sm_count * 8 * 4;
+  k_synth_fill<<<want < cap ? want : cap, 256, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
+                                                                t->file_len, t->file_begin, t->synth_class, t->synth_inject, seed,
+                                                                t->bytes, t->shard_byte0);
+  c->launches++;
+}
+
+}  // namespace m2k

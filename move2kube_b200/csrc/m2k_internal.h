@@ -1,0 +1,135 @@
+// Internal declarations shared by the host code and the kernels of libm2kdetect.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/m2kdetect.h"
+
+namespace m2k {
+
+constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
+constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
+constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
+constexpr uint32_t kLongUnits = (kLongLine - 30 + 15) / 16;  // newline-free 16-byte units a long line must contain (4095)
+
+// per-chunk record written by the byte-scan kernel: scratch memory, 4 bytes per 64 KiB chunk
+//   bits  0..12  lead : newline-free 16-byte units at the start of the chunk (== units in chunk when none has a newline)
+//   bits 13..25  trail: newline-free 16-byte units at the end of the chunk
+//   bit  26      the chunk contains the start of a "__main__"
+__host__ __device__ inline uint32_t rec_pack(uint32_t lead, uint32_t trail, uint32_t has_main) { return lead | (trail << 13) | (has_main << 26); }
+__host__ __device__ inline uint32_t rec_lead(uint32_t r) { return r & 0x1FFF; }
+__host__ __device__ inline uint32_t rec_trail(uint32_t r) { return (r >> 13) & 0x1FFF; }
+__host__ __device__ inline uint32_t rec_main(uint32_t r) { return (r >> 26) & 1; }
+
+// name signature table staged into shared memory by the name-feature kernel
+struct NameSig {
+  uint64_t lo, hi;       // the last <=16 bytes of the pattern, right aligned (byte 0 of `lo` = last character)
+  uint64_t mask_lo, mask_hi;
+  uint32_t len;          // pattern length
+  uint32_t kind;         // 0 exact name, 1 suffix
+  uint32_t feature;      // bit to set (M2K_F_* / M2K_R_* / M2K_N_*)
+  uint32_t need;         // 0 any type; 1 followed type must be REG; 2 lstat type must not be DIR; 3 non-dot name (war glob)
+};
+constexpr int kMaxNameSigs = 32;
+
+struct IgnoreSlot { uint64_t hash; uint32_t flags; uint32_t _pad; };
+
+// a tree (metadata replicated) plus the bytes of file ids [file_begin, file_end) resident in HBM
+struct DevTree {
+  const m2k_tree* host = nullptr;
+  uint32_t n_dirs = 0, n_entries = 0, n_files = 0, max_depth = 0;
+  uint32_t file_begin = 0, file_end = 0;  // shard
+  uint64_t shard_bytes = 0;               // padded bytes resident
+  uint64_t shard_content = 0;             // sum of file_len over the shard
+  uint64_t shard_byte0 = 0;               // file_off[file_begin]
+  uint32_t n_chunks = 0;
+  // metadata
+  uint32_t *dir_parent = nullptr, *dir_entry = nullptr, *dir_depth = nullptr, *level_dirs = nullptr;
+  uint8_t* dir_flags = nullptr;
+  std::vector<uint32_t> level_off;        // host: dirs of depth L are level_dirs[level_off[L] .. level_off[L+1])
+  uint32_t *entry_dir = nullptr, *entry_name_off = nullptr, *entry_child = nullptr;
+  uint8_t *entry_type = nullptr, *names = nullptr;
+  uint32_t* file_entry = nullptr;
+  uint64_t *file_off = nullptr, *file_len = nullptr;  // [n_files] (all files; offsets are tree-global)
+  uint32_t* chunk_first = nullptr;        // [shard files + 1] prefix of ceil(len / kChunkBytes) over the shard
+  uint8_t* bytes = nullptr;               // shard bytes; byte 0 is tree offset shard_byte0
+  // synthetic content description (device copies), only for m2k_synth_fill_device
+  uint8_t* synth_class = nullptr;
+  uint64_t* synth_inject = nullptr;
+  // work buffers
+  uint32_t* chunk_rec = nullptr;          // [n_chunks] scratch
+  uint32_t* entry_feat = nullptr;         // [n_entries]
+  uint32_t* dir_direct = nullptr;         // [n_dirs]
+  uint32_t* dir_first_war = nullptr;      // [n_dirs]
+  uint32_t* dir_content = nullptr;        // [n_dirs] partial: content bits of this shard
+  uint32_t* dir_main = nullptr;           // [n_dirs] partial: lowest main-file id of this shard
+  uint32_t* dir_subtree = nullptr;        // [n_dirs]
+  uint32_t* dir_main_sub = nullptr;       // [n_dirs]
+  uint32_t* dir_opts = nullptr;           // [n_dirs]
+  uint64_t* dir_hash = nullptr;           // [n_dirs]
+  uint8_t* dir_ignore = nullptr;          // [n_dirs]
+  uint8_t* dir_state = nullptr;           // [n_dirs]
+  uint8_t* dir_descend = nullptr;         // [n_dirs]
+  uint8_t* file_flags = nullptr;          // [n_files] (only the shard's range is written)
+  bool scanned = false;
+};
+
+struct Ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+  int sm_count = 0;
+  uint64_t launches = 0;
+  float last_scan_ms = 0.f;
+  std::string err;
+  uint32_t *d_fold_from = nullptr, *d_fold_to = nullptr;
+  NameSig* d_sigs = nullptr;
+  int n_sigs = 0;
+};
+
+// ---- kernel launchers (kernels.cu) ----
+void launch_name_features(Ctx* c, DevTree* t);
+void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec);
+void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec);
+void launch_dockerfile(Ctx* c, DevTree* t);
+void launch_subtree(Ctx* c, DevTree* t);
+void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor);
+void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, uint64_t depth1_state,
+                 uint8_t root_ignore);
+void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, const uint32_t* all_main, uint32_t n_ranks);
+void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed);
+void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
+
+// ---- host helpers (hostpath.cc) ----
+std::string path_clean(const std::string& p);
+std::string path_join(const std::string& a, const std::string& b);
+std::string path_dir(const std::string& p);
+bool equal_fold(const std::string& a, const std::string& b);
+uint64_t hash_fold(uint64_t h, const std::string& s);
+void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64_t len,
+                       std::vector<std::string>* ignore_dirs, std::vector<std::string>* ignore_contents);
+std::string tree_dir_path(const m2k_tree* t, uint32_t d);
+void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out);  // filepath.Walk order of all entries
+
+// ---- tree ownership (packer.cc / synth.cc) ----
+struct TreeOwner {
+  bool pinned = false;
+  std::string root;
+  std::vector<uint8_t> synth_class;    // synthetic trees only
+  std::vector<uint64_t> synth_inject;
+  uint64_t synth_seed = 0;
+  bool synthetic = false;
+  // files whose bytes are literal rather than procedural (.m2kignore files of synthetic trees)
+  std::vector<uint32_t> literal_file;
+  std::vector<std::string> literal_data;
+};
+m2k_tree* tree_alloc(uint32_t n_dirs, uint32_t n_entries, uint32_t n_files, uint64_t n_name_bytes, uint64_t n_bytes,
+                     bool with_bytes, bool pinned, const char* root);
+void tree_release(m2k_tree* t);
+int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tree** out, std::string* err);
+int synth_tree_impl(bool pinned, const m2k_synth_params* p, int host_bytes, m2k_tree** out, std::string* err);
+void synth_fill_host(const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, uint8_t* dst, int n_threads);
+
+}  // namespace m2k

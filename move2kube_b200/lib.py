@@ -1,0 +1,228 @@
+"""ctypes binding of libm2kdetect.so (include/m2kdetect.h).
+
+The shared library is the product; this module only loads it and gives the calls Python
+signatures.  It fails loudly when the library is missing or a call fails: there is no CPU path.
+"""
+import ctypes as C
+import os
+
+from . import _abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libm2kdetect.so")
+
+_lib = None
+
+
+class M2KError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("libm2kdetect error %d: %s" % (code, message))
+        self.code = code
+        self.message = message
+
+
+# every symbol include/m2kdetect.h declares
+EXPORTS = [
+    "m2k_abi_version", "m2k_global_error", "m2k_ctx_create", "m2k_ctx_destroy", "m2k_last_error", "m2k_device_info",
+    "m2k_pack_tree", "m2k_tree_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
+    "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_finalize",
+    "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
+    "m2k_list_entries",
+]
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s is missing: build it with `python -m move2kube_b200.build` (nvcc, sm_100a). "
+                          "move2kube_b200 has no fallback implementation." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, TP, RP = C.c_void_p, C.POINTER(_abi.Tree), C.POINTER(_abi.Result)
+    PP = C.POINTER(_abi.DetectParams)
+    L.m2k_abi_version.restype = C.c_int
+    L.m2k_global_error.restype = C.c_char_p
+    L.m2k_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.m2k_ctx_destroy.argtypes = [vp]
+    L.m2k_ctx_destroy.restype = None
+    L.m2k_last_error.argtypes = [vp]
+    L.m2k_last_error.restype = C.c_char_p
+    L.m2k_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
+    L.m2k_pack_tree.argtypes = [vp, C.c_char_p, C.c_int, C.POINTER(TP)]
+    L.m2k_tree_free.argtypes = [vp, TP]
+    L.m2k_tree_free.restype = None
+    L.m2k_synth_tree.argtypes = [vp, C.POINTER(_abi.SynthParams), C.c_int, C.POINTER(TP)]
+    L.m2k_synth_fill_host.argtypes = [TP, C.c_uint64, C.c_uint32, C.c_uint32, vp, C.c_int]
+    L.m2k_detect.argtypes = [vp, TP, PP, C.POINTER(RP)]
+    L.m2k_result_free.argtypes = [RP]
+    L.m2k_result_free.restype = None
+    L.m2k_upload.argtypes = [vp, TP, C.c_uint32, C.c_uint32, C.POINTER(vp)]
+    L.m2k_synth_fill_device.argtypes = [vp, vp, C.c_uint64]
+    L.m2k_scan.argtypes = [vp, vp, PP]
+    L.m2k_partials.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(C.c_uint32)]
+    L.m2k_merge_partials.argtypes = [vp, vp, vp, vp, C.c_uint32]
+    L.m2k_finalize.argtypes = [vp, vp, PP, C.POINTER(RP)]
+    L.m2k_devtree_free.argtypes = [vp, vp]
+    L.m2k_devtree_free.restype = None
+    L.m2k_scan_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.m2k_launch_count.argtypes = [vp]
+    L.m2k_launch_count.restype = C.c_uint64
+    L.m2k_stream.argtypes = [vp]
+    L.m2k_stream.restype = vp
+    L.m2k_path_clean.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
+    L.m2k_equal_fold.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    L.m2k_list_entries.argtypes = [TP, C.c_uint32, _abi.u32p, _abi.u32p, C.c_uint32]
+    for name in EXPORTS:
+        fn = getattr(L, name)
+        if fn.restype is C.c_int and name not in ("m2k_abi_version", "m2k_equal_fold", "m2k_list_entries"):
+            pass
+    _lib = L
+    return L
+
+
+def _check(rc, ctx=None):
+    if rc != _abi.OK:
+        L = load()
+        msg = L.m2k_last_error(ctx) if ctx else L.m2k_global_error()
+        raise M2KError(rc, (msg or b"").decode("utf-8", "replace"))
+
+
+def make_params(flavor=_abi.SH_BASH, pre=(), skip_content=False):
+    """Returns (DetectParams, keepalive)."""
+    arr = (C.c_char_p * max(1, len(pre)))(*[bytes(p) for p in pre])
+    p = _abi.DetectParams(flavor, len(pre), arr, 1 if skip_content else 0, 0)
+    return p, arr
+
+
+class Context:
+    """One CUDA device (m2k_ctx).  Creating it without a GPU raises M2KError(M2K_ERR_CUDA)."""
+
+    def __init__(self, device=0):
+        self.L = load()
+        h = C.c_void_p()
+        _check(self.L.m2k_ctx_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.L.m2k_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def device_info(self):
+        sm, mem, name = C.c_int(), C.c_uint64(), C.create_string_buffer(256)
+        _check(self.L.m2k_device_info(self.h, C.byref(sm), C.byref(mem), name, 256), self.h)
+        return {"sm_count": sm.value, "hbm_bytes": mem.value, "name": name.value.decode()}
+
+    # -- host trees
+    def pack_tree(self, root: bytes, read_content=True):
+        tp = C.POINTER(_abi.Tree)()
+        _check(self.L.m2k_pack_tree(self.h, root, 1 if read_content else 0, C.byref(tp)), self.h)
+        return tp
+
+    def synth_tree(self, params: _abi.SynthParams, host_bytes: bool):
+        tp = C.POINTER(_abi.Tree)()
+        _check(self.L.m2k_synth_tree(self.h, C.byref(params), 1 if host_bytes else 0, C.byref(tp)), self.h)
+        return tp
+
+    def tree_free(self, tree):
+        self.L.m2k_tree_free(self.h, tree)
+
+    # -- whole path
+    def detect(self, tree, flavor=_abi.SH_BASH, pre=(), skip_content=False):
+        p, keep = make_params(flavor, pre, skip_content)
+        rp = C.POINTER(_abi.Result)()
+        _check(self.L.m2k_detect(self.h, tree, C.byref(p), C.byref(rp)), self.h)
+        return rp
+
+    def result_free(self, res):
+        self.L.m2k_result_free(res)
+
+    # -- staged
+    def upload(self, tree, file_begin=0, file_end=None):
+        if file_end is None:
+            file_end = tree.contents.n_files
+        h = C.c_void_p()
+        _check(self.L.m2k_upload(self.h, tree, file_begin, file_end, C.byref(h)), self.h)
+        return h
+
+    def synth_fill_device(self, dt, seed):
+        _check(self.L.m2k_synth_fill_device(self.h, dt, seed), self.h)
+
+    def scan(self, dt, flavor=_abi.SH_BASH, skip_content=False):
+        p, keep = make_params(flavor, (), skip_content)
+        _check(self.L.m2k_scan(self.h, dt, C.byref(p)), self.h)
+
+    def partials(self, dt):
+        a, b, n = C.c_void_p(), C.c_void_p(), C.c_uint32()
+        _check(self.L.m2k_partials(self.h, dt, C.byref(a), C.byref(b), C.byref(n)), self.h)
+        return a.value, b.value, n.value
+
+    def merge_partials(self, dt, all_content_ptr, all_main_ptr, n_ranks):
+        _check(self.L.m2k_merge_partials(self.h, dt, all_content_ptr, all_main_ptr, n_ranks), self.h)
+
+    def finalize(self, dt, flavor=_abi.SH_BASH, pre=()):
+        p, keep = make_params(flavor, pre, False)
+        rp = C.POINTER(_abi.Result)()
+        _check(self.L.m2k_finalize(self.h, dt, C.byref(p), C.byref(rp)), self.h)
+        return rp
+
+    def devtree_free(self, dt):
+        self.L.m2k_devtree_free(self.h, dt)
+
+    def scan_kernel_ms(self):
+        ms = C.c_float()
+        _check(self.L.m2k_scan_kernel_ms(self.h, C.byref(ms)), self.h)
+        return ms.value
+
+    def launch_count(self):
+        return int(self.L.m2k_launch_count(self.h))
+
+    def stream(self):
+        return self.L.m2k_stream(self.h)
+
+
+# -- calls that need no GPU (host logic of the boundary)
+def pack_tree_host(root: bytes, read_content=True):
+    L = load()
+    tp = C.POINTER(_abi.Tree)()
+    _check(L.m2k_pack_tree(None, root, 1 if read_content else 0, C.byref(tp)))
+    return tp
+
+
+def synth_tree_host(params: _abi.SynthParams, host_bytes=True):
+    L = load()
+    tp = C.POINTER(_abi.Tree)()
+    _check(L.m2k_synth_tree(None, C.byref(params), 1 if host_bytes else 0, C.byref(tp)))
+    return tp
+
+
+def tree_free_host(tree):
+    load().m2k_tree_free(None, tree)
+
+
+def path_clean(p: bytes) -> bytes:
+    buf = C.create_string_buffer(len(p) + 8)
+    _check(load().m2k_path_clean(p, buf, len(p) + 8))
+    return buf.value
+
+
+def equal_fold(a: bytes, b: bytes) -> bool:
+    return bool(load().m2k_equal_fold(a, len(a), b, len(b)))
+
+
+def list_entries(tree, feature_bit, entry_feat):
+    L = load()
+    n = tree.contents.n_entries
+    out = (C.c_uint32 * max(1, n))()
+    k = L.m2k_list_entries(tree, feature_bit, entry_feat, out, n)
+    if k < 0:
+        raise M2KError(k, "m2k_list_entries")
+    return list(out[0:k])

@@ -1,0 +1,88 @@
+"""The boundary data types of the path, mirrored from the reference's types/plan.
+
+Reference: types/plan/plan.go:80-93,108-117 (enum strings), :186-215 (Service), :217-230 (NewService).
+Only what Any2KubeTranslator.GetServiceOptions reads or writes is kept.
+"""
+from dataclasses import dataclass, field
+from typing import Dict, List
+
+# TranslationTypeValue / ContainerBuildTypeValue / SourceTypeValue strings (plan.go:80-117)
+Any2KubeTranslation = "Any2Kube"
+DockerFileContainerBuildTypeValue = "NewDockerfile"
+ReuseDockerFileContainerBuildTypeValue = "ReuseDockerfile"
+ReuseContainerBuildTypeValue = "Reuse"
+CNBContainerBuildTypeValue = "CNB"
+S2IContainerBuildTypeValue = "S2I"
+ManualContainerBuildTypeValue = "Manual"
+DirectorySourceTypeValue = "Directory"
+SourceDirectoryArtifactType = "SourceCode"
+SourceDirectoryBuildArtifactType = "SourceCode"
+
+
+@dataclass
+class Service:
+    """plantypes.Service (plan.go:202-215)."""
+    ServiceName: str = ""
+    Image: str = ""
+    TranslationType: str = ""
+    ContainerBuildType: str = ""
+    SourceTypes: List[str] = field(default_factory=list)
+    ContainerizationTargetOptions: List[str] = field(default_factory=list)
+    SourceArtifacts: Dict[str, List[str]] = field(default_factory=dict)
+    BuildArtifacts: Dict[str, List[str]] = field(default_factory=dict)
+    UpdateContainerBuildPipeline: bool = False
+    UpdateDeployPipeline: bool = False
+    ServiceRelPath: str = ""
+
+    def AddSourceType(self, st: str) -> bool:
+        if st not in self.SourceTypes:
+            self.SourceTypes.append(st)
+        return True
+
+
+def NewService(servicename: str, translationtype: str) -> Service:
+    """plan.go:217-230."""
+    return Service(ServiceName=servicename, Image=servicename + ":latest", TranslationType=translationtype,
+                   SourceTypes=[], ContainerizationTargetOptions=[], SourceArtifacts={}, BuildArtifacts={},
+                   UpdateDeployPipeline=False, ServiceRelPath="/" + servicename)
+
+
+@dataclass
+class Inputs:
+    RootDir: str = ""
+    Services: Dict[str, List[Service]] = field(default_factory=dict)
+
+
+@dataclass
+class Spec:
+    Inputs: "Inputs" = field(default_factory=Inputs)
+
+
+@dataclass
+class Plan:
+    """plantypes.Plan, as far as source detection looks at it (plan.go:133-160)."""
+    Name: str = "myproject"
+    Spec: "Spec" = field(default_factory=Spec)
+
+    def SetRootDir(self, path: str):
+        self.Spec.Inputs.RootDir = path
+
+    def AddServicesToPlan(self, services: List[Service]):
+        """plan.go:380-398 with merge rules :274-288 restricted to what this path produces:
+        same name + same build type + same source dirs merge, anything else is appended."""
+        for s in services:
+            lst = self.Spec.Inputs.Services.setdefault(s.ServiceName, [])
+            for old in lst:
+                if (old.ContainerBuildType == s.ContainerBuildType and old.TranslationType == s.TranslationType
+                        and old.SourceArtifacts.get(SourceDirectoryArtifactType) ==
+                        s.SourceArtifacts.get(SourceDirectoryArtifactType)):
+                    for o in s.ContainerizationTargetOptions:
+                        if o not in old.ContainerizationTargetOptions:
+                            old.ContainerizationTargetOptions.append(o)
+                    break
+            else:
+                lst.append(s)
+
+
+def NewPlan() -> Plan:
+    return Plan()

@@ -1,0 +1,247 @@
+"""GPU parity tests (pytest -m gpu): the CUDA path, called through the C ABI, against the golden
+fixtures and the CPU oracle on the same inputs.  Bit-exact: everything here is integer/byte work."""
+import ctypes as C
+import os
+
+import pytest
+
+import golden_check as gc
+import treespec
+from dockerfile_kats import KATS
+from move2kube_b200 import _abi, lib
+
+pytestmark = pytest.mark.gpu
+
+GOLDENS = gc.load_goldens()
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = lib.Context(0)
+    yield c
+    c.close()
+
+
+def compare_with_oracle(oracle, tree, res, ores, content=True):
+    """Every array the C ABI returns against the oracle's, for every directory and file."""
+    t, r, o = tree.contents, res.contents, ores.contents
+    nd, nf = t.n_dirs, t.n_files
+    assert (r.n_dirs, r.n_files) == (nd, nf)
+    assert r.dir_opts[0:nd] == o.dir_opts[0:nd]
+    assert r.dir_state[0:nd] == o.dir_state[0:nd]
+    assert r.service_dirs[0:r.n_services] == o.service_dirs[0:o.n_services]
+    # the oracle fills the ignore flags of visited directories only
+    for d in range(nd):
+        if o.dir_state[d] not in (_abi.DIR_NOT_VISITED, _abi.DIR_WALK_ERROR):
+            assert r.dir_ignore[d] == o.dir_ignore[d], d
+    assert [r.ignore_dirs[i] for i in range(r.n_ignore_dirs)] == [o.ignore_dirs[i] for i in range(o.n_ignore_dirs)]
+    assert [r.ignore_contents[i] for i in range(r.n_ignore_contents)] == \
+        [o.ignore_contents[i] for i in range(o.n_ignore_contents)]
+    if content:
+        assert r.file_flags[0:nf] == o.file_flags[0:nf]
+        assert r.dir_main_file[0:nd] == o.dir_main_file[0:nd]
+
+
+@pytest.mark.parametrize("spec", [g for g in GOLDENS if not g.get("nonexistent")], ids=lambda g: g["name"])
+@pytest.mark.parametrize("flavor", ["bash", "dash"])
+def test_golden_fixture(ctx, oracle, tmp_path, spec, flavor):
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / spec["name"])))
+    fl = _abi.SH_BASH if flavor == "bash" else _abi.SH_DASH
+    pre = [oracle.join(root, os.fsencode(p)) if p != "." else root for p in spec.get("pre", [])]
+    tree = ctx.pack_tree(root)
+    try:
+        res = ctx.detect(tree, fl, pre)
+        try:
+            assert res.contents.n_kernel_launches >= 5
+            if not gc.has_user_scripts(spec):
+                gc.check(spec, flavor, gc.TreeView(tree), res, root)
+            ores = oracle.detect(tree, fl, pre)
+            compare_with_oracle(oracle, tree, res, ores)
+            oracle.lib().m2ko_result_free(ores)
+        finally:
+            ctx.result_free(res)
+    finally:
+        ctx.tree_free(tree)
+
+
+def test_nonexistent_root_is_an_io_error(ctx, tmp_path):
+    with pytest.raises(lib.M2KError) as ei:
+        ctx.pack_tree(os.fsencode(str(tmp_path / "missing")))
+    assert ei.value.code == _abi.ERR_IO
+
+
+def test_dockerfile_known_answers(ctx, oracle, tmp_path):
+    root = tmp_path / "kats"
+    root.mkdir()
+    for i, (name, data, want) in enumerate(KATS):
+        (root / ("%03d_%s" % (i, name))).write_bytes(data)
+    broot = os.fsencode(str(root))
+    tree = ctx.pack_tree(broot)
+    res = ctx.detect(tree)
+    view = gc.TreeView(tree)
+    got = {}
+    for f in range(view.n_files):
+        got[os.fsdecode(view.file_rel[f])] = res.contents.file_flags[f]
+    for i, (name, data, want) in enumerate(KATS):
+        fl = got["%03d_%s" % (i, name)]
+        assert fl == oracle.file_flags(data), name
+        assert bool(fl & _abi.FILE_DOCKERFILE) == want, name
+    ctx.result_free(res)
+    ctx.tree_free(tree)
+
+
+def _adversarial_files():
+    """Content cases around the kernel's tiling: 16-byte units, 512-byte rows, 64 KiB chunks."""
+    out = {}
+    for pos in [0, 1, 2, 3, 5, 8, 9, 13, 15, 16, 505, 508, 511, 512, 4089, 65528, 65529, 65531, 65535, 65536, 131064, 131071]:
+        body = bytearray(b"x" * (pos + 8 + 40))
+        for k in range(60, len(body), 61):
+            body[k] = 0x0A
+        body[pos:pos + 8] = b"__main__"
+        out["main_at_%d.py" % pos] = bytes(body)
+        out["nomain_at_%d.py" % pos] = bytes(body[:pos + 7])  # cut one byte short
+    for pat in [b"__main_", b"_main__", b"__ma", b"main", b"ain_", b"_mai", b"__mainx__main_", b"__mai\nn__"]:
+        out["near_%d" % len(out)] = b"abc " * 7 + pat + b" tail\n"
+    out["exact8"] = b"__main__"
+    out["seven"] = b"__main_"
+    out["empty"] = b""
+    # line lengths around bufio.MaxScanTokenSize, at every alignment that matters
+    for lead in [0, 1, 15, 16, 17, 511, 65535, 65536, 65537]:
+        for ln in [65534, 65535, 65536, 65537]:
+            for tail in [b"", b"\n", b"\r\n", b"\nshort\n"]:
+                key = "line_%d_%d_%d" % (lead, ln, len(tail))
+                out[key] = (b"a" * lead + b"\n" if lead else b"") + b"b" * ln + tail
+    out["long_first_of_three_chunks"] = b"q" * 200000
+    out["long_between"] = b"short\n" * 100 + b"L" * 70000 + b"\n" + b"short\n" * 100
+    out["nl_every_unit"] = (b"123456789012345\n") * 9000
+    out["nl_sparse_ok"] = (b"z" * 65535 + b"\n") * 4
+    out["nl_sparse_bad"] = (b"z" * 65535 + b"\n") * 2 + b"z" * 65536 + b"\n" + b"z" * 100
+    return out
+
+
+def test_adversarial_content(ctx, oracle, tmp_path):
+    root = tmp_path / "adv"
+    root.mkdir()
+    files = _adversarial_files()
+    for name, data in files.items():
+        (root / name).write_bytes(data)
+    tree = ctx.pack_tree(os.fsencode(str(root)))
+    res = ctx.detect(tree)
+    view = gc.TreeView(tree)
+    bad = []
+    for f in range(view.n_files):
+        name = os.fsdecode(view.file_rel[f])
+        want = oracle.file_flags(files[name])
+        if res.contents.file_flags[f] != want:
+            bad.append((name, res.contents.file_flags[f], want))
+    assert not bad, bad[:10]
+    ctx.result_free(res)
+    ctx.tree_free(tree)
+
+
+def synth_params(seed, n_files, n_dirs, total, depth=6, n_ignore=6, **kw):
+    return _abi.SynthParams(seed=seed, n_files=n_files, n_dirs=n_dirs, max_depth=depth, n_ignore_files=n_ignore,
+                            total_bytes=total, n_huge=kw.get("n_huge", 0), huge_bytes=kw.get("huge_bytes", 0),
+                            tiny_min=kw.get("tiny_min", 0), tiny_max=kw.get("tiny_max", 0))
+
+
+@pytest.mark.parametrize("seed,n_files,n_dirs,total", [(7, 4000, 200, 16 << 20), (3, 1500, 120, 96 << 20)])
+def test_synthetic_tree_vs_oracle(ctx, oracle, seed, n_files, n_dirs, total):
+    tree = ctx.synth_tree(synth_params(seed, n_files, n_dirs, total), host_bytes=True)
+    try:
+        res = ctx.detect(tree)
+        ores = oracle.detect(tree, n_threads=8)
+        compare_with_oracle(oracle, tree, res, ores)
+        r = res.contents
+        assert r.n_services > 0
+        flags = r.file_flags[0:r.n_files]
+        assert any(x & _abi.FILE_DOCKERFILE for x in flags) and any(x & _abi.FILE_HAS_MAIN for x in flags)
+        oracle.lib().m2ko_result_free(ores)
+        ctx.result_free(res)
+    finally:
+        ctx.tree_free(tree)
+
+
+def test_device_fill_equals_host_fill_and_staged_equals_whole(ctx, oracle):
+    """m2k_synth_fill_device writes the bytes m2k_synth_fill_host writes, and upload/scan/finalize
+    returns what m2k_detect returns."""
+    p = synth_params(11, 3000, 150, 48 << 20)
+    host_tree = ctx.synth_tree(p, host_bytes=True)
+    dev_tree = ctx.synth_tree(p, host_bytes=False)
+    try:
+        whole = ctx.detect(host_tree)
+        dt = ctx.upload(dev_tree)
+        ctx.synth_fill_device(dt, 11)
+        ctx.scan(dt)
+        assert ctx.scan_kernel_ms() > 0
+        staged = ctx.finalize(dt)
+        a, b = whole.contents, staged.contents
+        nd, nf = a.n_dirs, a.n_files
+        for fld in ("dir_opts", "dir_subtree", "dir_main_file", "dir_state", "dir_ignore"):
+            assert getattr(a, fld)[0:nd] == getattr(b, fld)[0:nd], fld
+        assert a.file_flags[0:nf] == b.file_flags[0:nf]
+        assert a.service_dirs[0:a.n_services] == b.service_dirs[0:b.n_services]
+        ctx.devtree_free(dt)
+        ctx.result_free(staged)
+        ctx.result_free(whole)
+    finally:
+        ctx.tree_free(host_tree)
+        ctx.tree_free(dev_tree)
+
+
+def test_sharded_scan_merges_to_the_whole(ctx, oracle):
+    """Two shards of the files scanned separately (as two ranks would), partials merged with the
+    gather kernel, finalised: same answer as one pass.  Emulates the N>1 path on one GPU."""
+    import torch
+    p = synth_params(5, 2500, 140, 40 << 20)
+    tree = ctx.synth_tree(p, host_bytes=True)
+    try:
+        whole = ctx.detect(tree)
+        nf, nd = tree.contents.n_files, tree.contents.n_dirs
+        mid = nf // 2
+        parts = []
+        for a, b in ((0, mid), (mid, nf)):
+            dt = ctx.upload(tree, a, b)
+            ctx.scan(dt)
+            parts.append(dt)
+        allc = torch.empty((2, nd), dtype=torch.int32, device="cuda")
+        allm = torch.empty((2, nd), dtype=torch.int32, device="cuda")
+        cudart = torch.cuda.cudart()
+        for i, dt in enumerate(parts):
+            pc, pm, n = ctx.partials(dt)
+            assert n == nd
+            assert int(cudart.cudaMemcpy(allc[i].data_ptr(), pc, 4 * nd, 3)) == 0
+            assert int(cudart.cudaMemcpy(allm[i].data_ptr(), pm, 4 * nd, 3)) == 0
+        torch.cuda.synchronize()
+        flags = [0] * nf
+        results = []
+        for i, dt in enumerate(parts):
+            ctx.merge_partials(dt, allc.data_ptr(), allm.data_ptr(), 2)
+            results.append(ctx.finalize(dt))
+        w = whole.contents
+        for i, (a, b) in enumerate(((0, mid), (mid, nf))):
+            r = results[i].contents
+            assert r.dir_state[0:nd] == w.dir_state[0:nd]
+            assert r.dir_opts[0:nd] == w.dir_opts[0:nd]
+            assert r.dir_main_file[0:nd] == w.dir_main_file[0:nd]
+            assert r.dir_subtree[0:nd] == w.dir_subtree[0:nd]
+            assert r.file_flags[a:b] == w.file_flags[a:b]
+        for i, dt in enumerate(parts):
+            ctx.result_free(results[i])
+            ctx.devtree_free(dt)
+        ctx.result_free(whole)
+    finally:
+        ctx.tree_free(tree)
+
+
+def test_names_only_mode(ctx, oracle, tmp_path):
+    spec = next(g for g in GOLDENS if g["name"] == "nasty")
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / "nasty")))
+    tree = ctx.pack_tree(root, read_content=False)
+    res = ctx.detect(tree, skip_content=True)
+    gc_spec = dict(spec)
+    gc_spec["expect"] = {"bash": dict(spec["expect"]["bash"], main_script={})}
+    gc.check(gc_spec, "bash", gc.TreeView(tree), res, root)
+    assert not any(res.contents.file_flags[0:res.contents.n_files])
+    ctx.result_free(res)
+    ctx.tree_free(tree)

@@ -1,0 +1,160 @@
+"""CPU tests of the boundary's host logic: the C ABI library loads and exports what the header
+declares, the product packer agrees with the oracle's independent walk, synthetic trees are
+well formed and deterministic, path helpers follow Go.  No compute entry point is called."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import golden_check as gc
+import treespec
+from move2kube_b200 import _abi, lib
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDENS = gc.load_goldens()
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(REPO, "include", "m2kdetect.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(m2k_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    L = lib.load()
+    missing = [n for n in sorted(declared) if not hasattr(L, n)]
+    assert not missing, "declared in include/m2kdetect.h but not exported: %s" % missing
+    assert set(lib.EXPORTS) == declared
+    assert L.m2k_abi_version() == 1
+
+
+def test_no_gpu_means_a_loud_error_not_a_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(lib.M2KError) as ei:
+        lib.Context(0)
+    assert ei.value.code == _abi.ERR_CUDA
+    assert "no CPU path" in ei.value.message
+
+
+def _tree_arrays(tp):
+    t = tp.contents
+    nd, ne, nf = t.n_dirs, t.n_entries, t.n_files
+    d = {
+        "n": (nd, ne, nf, t.max_depth, t.content_bytes),
+        "dir_parent": t.dir_parent[0:nd], "dir_end": t.dir_end[0:nd], "dir_entry": t.dir_entry[0:nd],
+        "dir_first_entry": t.dir_first_entry[0:nd + 1], "dir_depth": t.dir_depth[0:nd], "dir_flags": t.dir_flags[0:nd],
+        "entry_dir": t.entry_dir[0:ne], "entry_name_off": t.entry_name_off[0:ne + 1], "entry_type": t.entry_type[0:ne],
+        "entry_child": t.entry_child[0:ne], "names": bytes(bytearray(t.names[0:t.n_name_bytes])),
+        "file_entry": t.file_entry[0:nf], "file_off": t.file_off[0:nf], "file_len": t.file_len[0:nf],
+    }
+    if t.bytes:
+        d["bytes"] = bytes(bytearray(t.bytes[0:t.n_bytes]))
+    return d
+
+
+@pytest.mark.parametrize("spec", [g for g in GOLDENS if not g.get("nonexistent")], ids=lambda g: g["name"])
+def test_packer_matches_the_oracle_walk(oracle, tmp_path, spec):
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / spec["name"])))
+    rc, otree = oracle.pack_fs(root)
+    assert rc == 0
+    ptree = lib.pack_tree_host(root)
+    try:
+        a, b = _tree_arrays(otree), _tree_arrays(ptree)
+        for k in a:
+            assert a[k] == b[k], k
+        assert ptree.contents.root_path == root
+    finally:
+        lib.tree_free_host(ptree)
+        oracle.lib().m2ko_tree_free(otree)
+
+
+def test_packer_errors(tmp_path):
+    with pytest.raises(lib.M2KError) as ei:
+        lib.pack_tree_host(os.fsencode(str(tmp_path / "nope")))
+    assert ei.value.code == _abi.ERR_IO
+    d = tmp_path / "nl"
+    d.mkdir()
+    (d / "a\nb.go").write_text("x")
+    with pytest.raises(lib.M2KError) as ei:
+        lib.pack_tree_host(os.fsencode(str(d)))
+    assert ei.value.code == _abi.ERR_UNSUPPORTED
+
+
+def small_synth(seed=7, n_files=400, n_dirs=50, total=3 << 20, **kw):
+    return _abi.SynthParams(seed=seed, n_files=n_files, n_dirs=n_dirs, max_depth=5, n_ignore_files=4,
+                            total_bytes=total, n_huge=kw.get("n_huge", 0), huge_bytes=kw.get("huge_bytes", 0),
+                            tiny_min=kw.get("tiny_min", 0), tiny_max=kw.get("tiny_max", 0))
+
+
+def test_synthetic_tree_is_well_formed_and_deterministic(oracle):
+    t1 = lib.synth_tree_host(small_synth())
+    t2 = lib.synth_tree_host(small_synth())
+    try:
+        a, b = _tree_arrays(t1), _tree_arrays(t2)
+        assert a == b
+        t = t1.contents
+        nd, ne, nf = t.n_dirs, t.n_entries, t.n_files
+        assert nd == 50 and nf == 400 and ne == nd - 1 + nf
+        view = gc.TreeView(t1)
+        # pre-order ids with children in byte order; entries sorted by (dir, name)
+        for d in range(1, nd):
+            p = t.dir_parent[d]
+            assert p < d and t.dir_depth[d] == t.dir_depth[p] + 1 and p <= d < t.dir_end[p]
+        for e in range(1, ne):
+            assert (t.entry_dir[e - 1], view.entry_name[e - 1]) < (t.entry_dir[e], view.entry_name[e])
+        for f in range(nf):
+            assert t.file_off[f] % 16 == 0
+            if f:
+                assert t.file_off[f] == t.file_off[f - 1] + (t.file_len[f - 1] + 15) // 16 * 16
+        assert abs(t.content_bytes - (3 << 20)) < (3 << 20) * 0.05
+        assert sum(1 for n in view.entry_name if n == b".m2kignore") >= 1
+    finally:
+        lib.tree_free_host(t1)
+        lib.tree_free_host(t2)
+
+
+def test_synthetic_tree_exercises_every_signature(oracle):
+    """The oracle accepts the layout and the tree contains every case the kernels must tell apart."""
+    tp = lib.synth_tree_host(small_synth(seed=7, n_files=4000, n_dirs=200, total=16 << 20))
+    try:
+        nf, nd = tp.contents.n_files, tp.contents.n_dirs
+        res = oracle.detect(tp, n_threads=4)
+        r = res.contents
+        flags = r.file_flags[0:nf]
+        states = set(r.dir_state[0:nd])
+        assert r.n_services > 3
+        assert {_abi.DIR_NOT_VISITED, _abi.DIR_IGNORED_DESCEND, _abi.DIR_NOMATCH_DESCEND, _abi.DIR_SERVICE} <= states
+        assert any(x & _abi.FILE_DOCKERFILE for x in flags)
+        assert any(x & _abi.FILE_HAS_MAIN for x in flags)
+        assert any((x & _abi.FILE_FROM_FIRST) and not (x & _abi.FILE_DOCKERFILE) for x in flags)
+        assert any(m != _abi.NONE for m in r.dir_main_file[0:nd])
+        oracle.lib().m2ko_result_free(res)
+    finally:
+        lib.tree_free_host(tp)
+
+
+def test_synth_fill_host_is_random_access():
+    tp = lib.synth_tree_host(small_synth())
+    try:
+        t = tp.contents
+        whole = bytes(bytearray(t.bytes[0:t.n_bytes]))
+        f0, f1 = 100, 180
+        lo = t.file_off[f0]
+        hi = t.file_off[f1 - 1] + (t.file_len[f1 - 1] + 15) // 16 * 16
+        buf = (C.c_uint8 * (hi - lo))()
+        rc = lib.load().m2k_synth_fill_host(tp, 7, f0, f1, buf, 3)
+        assert rc == 0
+        assert bytes(buf) == whole[lo:hi]
+        assert lib.load().m2k_synth_fill_host(tp, 8, f0, f1, buf, 3) == _abi.ERR_ARG
+    finally:
+        lib.tree_free_host(tp)
+
+
+def test_path_helpers_follow_go(oracle):
+    import gopath
+    for p in [b"", b"/", b"a//b/../c/", b"../x/..", b"/a/../../b", b"./", b"a/b/../../.."]:
+        assert lib.path_clean(p) == gopath.clean(p) == oracle.clean(p)
+    for a, b in [(b"/R/K", "/r/K".encode()), (b"ss", "ß".encode()), (b"a\xffb", b"A\xfeB"), (b"I", "ı".encode()),
+                 ("ſ".encode(), b"S"), (b"abc", b"ab")]:
+        assert lib.equal_fold(a, b) == gopath.equal_fold(a, b) == oracle.equal_fold(a, b)
