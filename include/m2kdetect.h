@@ -192,6 +192,9 @@ typedef struct m2k_synth_params {
   uint32_t _pad;
   uint64_t huge_bytes;    /* size of each */
   uint32_t tiny_min, tiny_max; /* config D: tiny file size range (0,0 = log-normal sizes) */
+  uint32_t n_large;       /* config D: a second group of big files */
+  uint32_t _pad2;
+  uint64_t large_bytes;
 } m2k_synth_params;
 int m2k_synth_tree(m2k_ctx* ctx, const m2k_synth_params* p, int host_bytes, m2k_tree** out);
 /* bytes of file ids [file_begin, file_end) generated on the host into dst (file_off relative to
@@ -208,9 +211,9 @@ int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t
 int m2k_synth_fill_device(m2k_ctx* ctx, m2k_devtree* dt, uint64_t seed);
 /* phase A: name features + byte scan + Dockerfile check over the resident shard */
 int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
-/* per-directory partial arrays a multi-GPU run gathers (device pointers, n_dirs uint32 each):
- * content mask (OR-reducible) and lowest main-file id (MIN-reducible) */
-int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t** d_dir_content, uint32_t** d_dir_main, uint32_t* n_dirs);
+/* per-directory partial arrays a multi-GPU run gathers, copied device-to-device into the caller's
+ * buffers (n_dirs uint32 each): content mask (OR-reducible) and lowest main-file id (MIN-reducible) */
+int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_dst_content, uint32_t* d_dst_main);
 /* OR / MIN `n_ranks` gathered partial arrays (device memory, rank-major) into this shard's own */
 int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks);
 /* phase C: subtree OR, predicate combine, ignore join, prune; copies results to the host */

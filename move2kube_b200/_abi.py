@@ -72,4 +72,6 @@ class SynthParams(C.Structure):
         ("n_huge", C.c_uint32), ("_pad", C.c_uint32),
         ("huge_bytes", C.c_uint64),
         ("tiny_min", C.c_uint32), ("tiny_max", C.c_uint32),
+        ("n_large", C.c_uint32), ("_pad2", C.c_uint32),
+        ("large_bytes", C.c_uint64),
     ]

@@ -334,11 +334,13 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   return M2K_OK;
 }
 
-extern "C" int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t** d_dir_content, uint32_t** d_dir_main, uint32_t* n_dirs) {
-  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
-  if (d_dir_content) *d_dir_content = dt->t.dir_content;
-  if (d_dir_main) *d_dir_main = dt->t.dir_main;
-  if (n_dirs) *n_dirs = dt->t.n_dirs;
+extern "C" int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_dst_content, uint32_t* d_dst_main) {
+  if (!ctx || !dt || !d_dst_content || !d_dst_main) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaMemcpyAsync(d_dst_content, dt->t.dir_content, 4ull * dt->t.n_dirs, cudaMemcpyDeviceToDevice, C->stream));
+  CU(cudaMemcpyAsync(d_dst_main, dt->t.dir_main, 4ull * dt->t.n_dirs, cudaMemcpyDeviceToDevice, C->stream));
+  CU(cudaStreamSynchronize(C->stream));
   return M2K_OK;
 }
 
@@ -378,10 +380,11 @@ bool walk_before(const m2k_tree* t, uint32_t a, uint32_t b) {
 
 const uint8_t* host_file_bytes(const m2k_tree* t, uint32_t f, uint64_t* len) {
   *len = t->file_len[f];
-  if (t->bytes) return t->bytes + t->file_off[f];
+  // synthetic trees keep their rule files as literals (their bytes may live on another rank's shard)
   const TreeOwner* o = static_cast<const TreeOwner*>(t->owner);
   if (o) for (size_t k = 0; k < o->literal_file.size(); k++)
     if (o->literal_file[k] == f) return reinterpret_cast<const uint8_t*>(o->literal_data[k].data());
+  if (t->bytes) return t->bytes + t->file_off[f];
   return nullptr;
 }
 

@@ -170,10 +170,11 @@ int synth_tree_impl(bool pinned, const m2k_synth_params* p, int host_bytes, m2k_
   {
     std::vector<double> raw(nf, 0.0);
     double sum = 0;
-    uint32_t huge_left = p->n_huge;
+    uint32_t huge_left = p->n_huge, large_left = p->n_large;
     for (uint32_t f = 0; f < nf; f++) {
       if (files[f].literal >= 0) continue;
       if (huge_left && f >= n_marker) { files[f].len = p->huge_bytes; huge_left--; continue; }
+      if (large_left && f >= n_marker) { files[f].len = p->large_bytes; large_left--; continue; }
       if (p->tiny_max) { files[f].len = p->tiny_min + rng.below(p->tiny_max - p->tiny_min + 1); continue; }
       double v = exp(log(40000.0) + 1.5 * rng.normal());
       if (v > 8.0 * 1024 * 1024) v = 8.0 * 1024 * 1024;

@@ -60,7 +60,7 @@ def load():
     L.m2k_upload.argtypes = [vp, TP, C.c_uint32, C.c_uint32, C.POINTER(vp)]
     L.m2k_synth_fill_device.argtypes = [vp, vp, C.c_uint64]
     L.m2k_scan.argtypes = [vp, vp, PP]
-    L.m2k_partials.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(C.c_uint32)]
+    L.m2k_partials.argtypes = [vp, vp, vp, vp]
     L.m2k_merge_partials.argtypes = [vp, vp, vp, vp, C.c_uint32]
     L.m2k_finalize.argtypes = [vp, vp, PP, C.POINTER(RP)]
     L.m2k_devtree_free.argtypes = [vp, vp]
@@ -160,10 +160,9 @@ class Context:
         p, keep = make_params(flavor, (), skip_content)
         _check(self.L.m2k_scan(self.h, dt, C.byref(p)), self.h)
 
-    def partials(self, dt):
-        a, b, n = C.c_void_p(), C.c_void_p(), C.c_uint32()
-        _check(self.L.m2k_partials(self.h, dt, C.byref(a), C.byref(b), C.byref(n)), self.h)
-        return a.value, b.value, n.value
+    def partials(self, dt, dst_content_ptr, dst_main_ptr):
+        """Copies this shard's per-directory partials into caller-owned device buffers."""
+        _check(self.L.m2k_partials(self.h, dt, dst_content_ptr, dst_main_ptr), self.h)
 
     def merge_partials(self, dt, all_content_ptr, all_main_ptr, n_ranks):
         _check(self.L.m2k_merge_partials(self.h, dt, all_content_ptr, all_main_ptr, n_ranks), self.h)

@@ -801,7 +801,8 @@ uint32_t m2ko_dockerfile_flags(const uint8_t* data, uint64_t len) {
     }
   }
   free(line.p); free(cont.p);
-  if (decided && first_kind == 1 && first_from_match) flags |= M2K_FILE_FROM_FIRST;
+  /* FROM_FIRST is reported only for files without an over-long line (Parse fails on those anyway) */
+  if (decided && first_kind == 1 && first_from_match && !(flags & M2K_FILE_LONG_LINE)) flags |= M2K_FILE_FROM_FIRST;
   if (!parse_error && !(flags & M2K_FILE_LONG_LINE) && n_nodes > 0 && (flags & M2K_FILE_FROM_FIRST)) flags |= M2K_FILE_DOCKERFILE;
   return flags;
 }

@@ -52,7 +52,7 @@ def test_golden_fixture(ctx, oracle, tmp_path, spec, flavor):
     try:
         res = ctx.detect(tree, fl, pre)
         try:
-            assert res.contents.n_kernel_launches >= 5
+            assert res.contents.n_kernel_launches >= 3
             if not gc.has_user_scripts(spec):
                 gc.check(spec, flavor, gc.TreeView(tree), res, root)
             ores = oracle.detect(tree, fl, pre)
@@ -206,14 +206,9 @@ def test_sharded_scan_merges_to_the_whole(ctx, oracle):
             parts.append(dt)
         allc = torch.empty((2, nd), dtype=torch.int32, device="cuda")
         allm = torch.empty((2, nd), dtype=torch.int32, device="cuda")
-        cudart = torch.cuda.cudart()
         for i, dt in enumerate(parts):
-            pc, pm, n = ctx.partials(dt)
-            assert n == nd
-            assert int(cudart.cudaMemcpy(allc[i].data_ptr(), pc, 4 * nd, 3)) == 0
-            assert int(cudart.cudaMemcpy(allm[i].data_ptr(), pm, 4 * nd, 3)) == 0
+            ctx.partials(dt, allc[i].data_ptr(), allm[i].data_ptr())
         torch.cuda.synchronize()
-        flags = [0] * nf
         results = []
         for i, dt in enumerate(parts):
             ctx.merge_partials(dt, allc.data_ptr(), allm.data_ptr(), 2)
