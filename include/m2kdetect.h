@@ -221,6 +221,9 @@ int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params,
 void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt);
 /* device time of the byte-scan kernel alone in the last m2k_scan, and launches issued so far */
 int m2k_scan_kernel_ms(m2k_ctx* ctx, float* ms);
+/* milliseconds of the last m2k_scan + m2k_finalize by phase: name features, byte scan, per-file
+ * combine, isDockerFile, finalize kernels (device); ignore parsing, hit verification (host); D2H */
+int m2k_phase_ms(m2k_ctx* ctx, float* out, int cap);
 uint64_t m2k_launch_count(const m2k_ctx* ctx);
 void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
 

@@ -145,6 +145,11 @@ extern "C" int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes,
 
 extern "C" void* m2k_stream(m2k_ctx* ctx) { return ctx ? (void*)ctx->c.stream : nullptr; }
 extern "C" uint64_t m2k_launch_count(const m2k_ctx* ctx) { return ctx ? ctx->c.launches : 0; }
+extern "C" int m2k_phase_ms(m2k_ctx* ctx, float* out, int cap) {
+  if (!ctx || !out) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  for (int i = 0; i < cap && i < 8; i++) out[i] = ctx->c.phase_ms[i];
+  return M2K_OK;
+}
 extern "C" int m2k_scan_kernel_ms(m2k_ctx* ctx, float* ms) {
   if (!ctx || !ms) return fail(nullptr, M2K_ERR_ARG, "bad argument");
   *ms = ctx->c.last_scan_ms;
@@ -319,17 +324,27 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_main, 0xFF, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->file_flags, 0, t->n_files, s));
+  CU(cudaEventRecord(C->ev[8], s));
   launch_name_features(C, t);
+  CU(cudaEventRecord(C->ev[2], s));
   if (content) {
-    CU(cudaEventRecord(C->ev[2], s));
     launch_scan_bytes(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[3], s));
     launch_file_combine(C, t, t->chunk_rec);
+    CU(cudaEventRecord(C->ev[9], s));
     launch_dockerfile(C, t);
+    CU(cudaEventRecord(C->ev[10], s));
   }
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(s));
-  if (content) CU(cudaEventElapsedTime(&C->last_scan_ms, C->ev[2], C->ev[3]));
+  memset(C->phase_ms, 0, sizeof C->phase_ms);
+  CU(cudaEventElapsedTime(&C->phase_ms[0], C->ev[8], C->ev[2]));
+  if (content) {
+    CU(cudaEventElapsedTime(&C->last_scan_ms, C->ev[2], C->ev[3]));
+    C->phase_ms[1] = C->last_scan_ms;
+    CU(cudaEventElapsedTime(&C->phase_ms[2], C->ev[3], C->ev[9]));
+    CU(cudaEventElapsedTime(&C->phase_ms[3], C->ev[9], C->ev[10]));
+  }
   t->scanned = true;
   return M2K_OK;
 }
@@ -430,10 +445,13 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   launch_subtree(C, t);
   launch_combine_opts(C, t, sh);
   CU(cudaMemcpyAsync(r->entry_feat, t->entry_feat, 4ull * ne, cudaMemcpyDeviceToHost, s));
+  CU(cudaEventRecord(C->ev[7], s));
   CU(cudaStreamSynchronize(s));
 
   // getIgnorePaths (any2kube.go:151-181): the .m2kignore files come from the name-feature bit
   double h0 = now_ms();
+  const std::string root = tree->root_path ? tree->root_path : "";
+  const std::string clean_root = path_clean(root);
   std::vector<uint32_t> ign_entries;
   for (uint32_t e = 0; e < ne; e++) if (r->entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
   std::sort(ign_entries.begin(), ign_entries.end(), [&](uint32_t a, uint32_t b) { return walk_before(tree, a, b); });
@@ -447,49 +465,74 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
       if (len == 0) continue;
       return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
     }
-    std::string fpath = path_join(tree_dir_path(tree, tree->entry_dir[e]), ".m2kignore");
+    uint32_t d = tree->entry_dir[e];
+    std::string fpath = path_join(d == 0 ? root : fast_dir_path(tree, d, clean_root), ".m2kignore");
     parse_ignore_file(fpath, data, len, &ign_dirs, &ign_contents);
   }
-  // hash table over the case-folded entries; flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
-  const std::string root = tree->root_path ? tree->root_path : "";
+  // exact hash table over the case-folded entries, keyed by the folded rune sequence;
+  // flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
   uint8_t root_ignore = 0;
-  std::unordered_map<uint64_t, uint32_t> by_hash;
-  std::unordered_map<uint64_t, std::vector<std::pair<const std::string*, uint32_t>>> verify;
   std::vector<std::string> pre;
   for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
   const uint64_t seed0 = 0xcbf29ce484222325ull;
+  struct Ent { uint64_t key; uint32_t flags, off, len; };
+  std::vector<Ent> ents;
+  std::vector<uint32_t> runes, tmp, root_runes;
+  std::unordered_map<uint64_t, std::vector<uint32_t>> by_key;  // key -> indices into ents (collisions share a key)
+  fold_runes(root, &root_runes);
   auto add = [&](const std::string& sp, uint32_t flag) {
-    if (equal_fold(sp, root)) root_ignore |= (uint8_t)flag;
-    uint64_t key = hash_finish(hash_fold(seed0, sp));
-    by_hash[key] |= flag;
-    verify[key].push_back({&sp, flag});
+    fold_runes(sp, &tmp);
+    if (tmp == root_runes) root_ignore |= (uint8_t)flag;
+    uint64_t h = seed0;
+    for (uint32_t rr : tmp) h = hash_step(h, rr);
+    uint64_t key = hash_finish(h);
+    auto& lst = by_key[key];
+    for (uint32_t idx : lst) {
+      const Ent& en = ents[idx];
+      if (en.len == tmp.size() && std::equal(tmp.begin(), tmp.end(), runes.begin() + en.off)) { ents[idx].flags |= flag; return; }
+    }
+    lst.push_back((uint32_t)ents.size());
+    ents.push_back({key, flag, (uint32_t)runes.size(), (uint32_t)tmp.size()});
+    runes.insert(runes.end(), tmp.begin(), tmp.end());
   };
   for (const auto& x : ign_dirs) add(x, 1);
   for (const auto& x : ign_contents) add(x, 2);
   for (const auto& x : pre) add(x, 4);
+  // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
+  std::string prefix1 = clean_root;
+  if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
+  std::vector<uint32_t> prefix_runes;
+  fold_runes(prefix1, &prefix_runes);
+  uint64_t depth1_state = seed0;
+  for (uint32_t rr : prefix_runes) depth1_state = hash_step(depth1_state, rr);
   std::vector<IgnoreSlot> table;
   uint32_t table_mask = M2K_NONE;
-  IgnoreSlot* d_table = nullptr;
-  if (!by_hash.empty()) {
+  void* d_blob = nullptr;  // [table | entry runes | prefix runes] in one allocation
+  const IgnoreSlot* d_table = nullptr;
+  const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
+  if (!ents.empty()) {
     uint32_t cap = 16;
-    while (cap < by_hash.size() * 2) cap <<= 1;
-    table.assign(cap, IgnoreSlot{0, 0, 0});
+    while (cap < ents.size() * 2) cap <<= 1;
+    table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
     table_mask = cap - 1;
-    for (const auto& kv : by_hash) {
-      uint32_t sidx = (uint32_t)kv.first & table_mask;
+    for (const Ent& en : ents) {
+      uint32_t sidx = (uint32_t)en.key & table_mask;
       while (table[sidx].hash) sidx = (sidx + 1) & table_mask;
-      table[sidx].hash = kv.first; table[sidx].flags = kv.second;
+      table[sidx] = IgnoreSlot{en.key, en.flags, en.off, en.len, 0};
     }
-    CU(cudaMalloc(&d_table, sizeof(IgnoreSlot) * cap));
-    CU(cudaMemcpyAsync(d_table, table.data(), sizeof(IgnoreSlot) * cap, cudaMemcpyHostToDevice, s));
+    size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
+    CU(cudaMalloc(&d_blob, tb + rb + pb + 16));
+    CU(cudaMemcpyAsync(d_blob, table.data(), tb, cudaMemcpyHostToDevice, s));
+    if (rb) CU(cudaMemcpyAsync((char*)d_blob + tb, runes.data(), rb, cudaMemcpyHostToDevice, s));
+    if (pb) CU(cudaMemcpyAsync((char*)d_blob + tb + rb, prefix_runes.data(), pb, cudaMemcpyHostToDevice, s));
+    d_table = (const IgnoreSlot*)d_blob;
+    d_runes = (const uint32_t*)((char*)d_blob + tb);
+    d_prefix = (const uint32_t*)((char*)d_blob + tb + rb);
   }
-  // hash state shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
-  std::string prefix1 = path_clean(root);
-  if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
-  uint64_t depth1_state = hash_fold(seed0, prefix1);
   r->ms_host_ignore = (float)(now_ms() - h0);
 
-  launch_walk(C, t, d_table, table_mask, depth1_state, root_ignore);
+  CU(cudaEventRecord(C->ev[11], s));
+  launch_walk(C, t, d_table, table_mask, d_runes, d_prefix, (uint32_t)prefix_runes.size(), depth1_state, root_ignore);
   CU(cudaEventRecord(C->ev[5], s));
   CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, s));
@@ -500,28 +543,18 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);
-  if (d_table) cudaFree(d_table);
+  if (d_blob) cudaFree(d_blob);
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "walk kernels failed: %s", cudaGetErrorString(werr));
-  float ms_k = 0, ms_d = 0;
-  CU(cudaEventElapsedTime(&ms_k, C->ev[4], C->ev[5]));
+  float ms_k1 = 0, ms_k2 = 0, ms_d = 0;
+  CU(cudaEventElapsedTime(&ms_k1, C->ev[4], C->ev[7]));
+  CU(cudaEventElapsedTime(&ms_k2, C->ev[11], C->ev[5]));
   CU(cudaEventElapsedTime(&ms_d, C->ev[5], C->ev[6]));
-  r->ms_kernels = ms_k; r->ms_d2h = ms_d;
-
-  // the hash join is exact only up to 64-bit collisions: confirm every hit with a real EqualFold
-  for (uint32_t d = 1; d < nd; d++) {
-    if (!r->dir_ignore[d]) continue;
-    std::string p = tree_dir_path(tree, d);
-    uint64_t key = hash_finish(hash_fold(seed0, p));
-    uint32_t exact = 0;
-    auto it = verify.find(key);
-    if (it != verify.end()) for (const auto& pr : it->second) if (equal_fold(*pr.first, p)) exact |= pr.second;
-    if (exact != r->dir_ignore[d])
-      return fail(C, M2K_ERR_UNSUPPORTED, "64-bit path-hash collision on directory %s: refusing to return inexact ignore decisions", p.c_str());
-  }
-  for (uint32_t d = 0; d < nd; d++) {
-    r->dir_direct[d] |= 0;  // direct name features; content bits are part of dir_subtree
+  r->ms_kernels = ms_k1 + ms_k2; r->ms_d2h = ms_d;
+  C->phase_ms[4] = ms_k1 + ms_k2; C->phase_ms[5] = r->ms_host_ignore; C->phase_ms[7] = ms_d;
+  double v0 = now_ms();
+  for (uint32_t d = 0; d < nd; d++)
     if (r->dir_state[d] == M2K_DIR_SERVICE) r->service_dirs[r->n_services++] = d;
-  }
+  C->phase_ms[6] = (float)(now_ms() - v0);
   r->n_ignore_dirs = (uint32_t)ign_dirs.size(); r->ignore_dirs = dup_list(ign_dirs);
   r->n_ignore_contents = (uint32_t)ign_contents.size(); r->ignore_contents = dup_list(ign_contents);
   r->ms_h2d = dt->ms_h2d;

@@ -381,6 +381,7 @@ __device__ inline uint32_t classify(const uint8_t* p, uint64_t n, bool long_line
         while (t < n && alive) {
           uint32_t c0 = p[t];
           if (c0 == '\n' || ascii_ws(c0)) break;
+          if (c0 == f.esc) { alive = 0x1F; break; }  // may be a line continuation inside the word: exact path
           uint32_t w, r = decode_rune(p + t, n - t, &w);
           if (is_space_rune(r)) break;  // unicode space: leave it to the exact path
           alive = kw_step(alive, idx, r);

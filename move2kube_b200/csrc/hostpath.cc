@@ -16,28 +16,35 @@ namespace m2k {
 std::string path_clean(const std::string& p) {
   if (p.empty()) return ".";
   const bool rooted = p[0] == '/';
-  std::vector<std::string> parts;
-  size_t i = 0, n = p.size();
+  const size_t n = p.size();
+  std::string out;
+  out.reserve(n + 1);
+  if (rooted) out += '/';
+  const size_t floor0 = rooted ? 1 : 0;
+  size_t dotdot = floor0;  // output below this index is a run of leading ".." components: never popped
+  size_t i = floor0;
   while (i < n) {
-    while (i < n && p[i] == '/') i++;
+    if (p[i] == '/') { i++; continue; }
     size_t j = i;
     while (j < n && p[j] != '/') j++;
-    if (j > i) {
-      std::string comp = p.substr(i, j - i);
-      if (comp == ".") {
-      } else if (comp == "..") {
-        if (!parts.empty() && parts.back() != "..") parts.pop_back();
-        else if (!rooted) parts.push_back(comp);
-      } else {
-        parts.push_back(comp);
+    const size_t len = j - i;
+    if (len == 1 && p[i] == '.') {
+      // skip
+    } else if (len == 2 && p[i] == '.' && p[i + 1] == '.') {
+      if (out.size() > dotdot) {  // drop the last component
+        size_t k = out.size() - 1;
+        while (k > dotdot && out[k] != '/') k--;
+        out.resize(k);
+      } else if (!rooted) {
+        if (!out.empty()) out += '/';
+        out += "..";
+        dotdot = out.size();
       }
+    } else {
+      if (out.size() > floor0) out += '/';
+      out.append(p, i, len);
     }
     i = j;
-  }
-  std::string out = rooted ? "/" : "";
-  for (size_t k = 0; k < parts.size(); k++) {
-    if (k) out += '/';
-    out += parts[k];
   }
   return out.empty() ? "." : out;
 }
@@ -73,6 +80,16 @@ bool equal_fold(const std::string& a, const std::string& b) {
 
 uint64_t hash_fold(uint64_t h, const std::string& s) {
   return hash_fold_bytes(h, reinterpret_cast<const uint8_t*>(s.data()), s.size(), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
+}
+
+void fold_runes(const std::string& s, std::vector<uint32_t>* out) {
+  out->clear();
+  const uint8_t* p = reinterpret_cast<const uint8_t*>(s.data());
+  for (size_t i = 0; i < s.size();) {
+    uint32_t w;
+    out->push_back(fold_rune(decode_rune(p + i, s.size() - i, &w), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N));
+    i += w;
+  }
 }
 
 // strings.TrimSpace on [b, e)
@@ -137,6 +154,30 @@ std::string tree_dir_path(const m2k_tree* t, uint32_t d) {
   for (uint32_t x = d; x != 0; x = t->dir_parent[x]) chain.push_back(x);
   std::string p = t->root_path ? t->root_path : "";
   for (size_t k = chain.size(); k-- > 0;) p = path_join(p, entry_name(t, t->dir_entry[chain[k]]));
+  return p;
+}
+
+// Same string as tree_dir_path for d != 0, without cleaning at every level: entry names contain no
+// '/' and are never "." or "..", so appending "/name" to the cleaned root is already clean.
+std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clean_root) {
+  uint32_t chain[4096];
+  uint32_t n = 0;
+  size_t len = clean_root.size() + 1;
+  std::vector<uint32_t> big;
+  for (uint32_t x = d; x != 0; x = t->dir_parent[x]) {
+    uint32_t e = t->dir_entry[x];
+    len += t->entry_name_off[e + 1] - t->entry_name_off[e] + 1;
+    if (n < 4096) chain[n++] = e; else big.push_back(e);
+  }
+  std::string p;
+  p.reserve(len);
+  if (clean_root != ".") p = clean_root;
+  auto app = [&](uint32_t e) {
+    if (!p.empty() && p.back() != '/') p += '/';
+    p.append(reinterpret_cast<const char*>(t->names + t->entry_name_off[e]), t->entry_name_off[e + 1] - t->entry_name_off[e]);
+  };
+  for (size_t k = big.size(); k-- > 0;) app(big[k]);
+  for (uint32_t k = n; k-- > 0;) app(chain[k]);
   return p;
 }
 

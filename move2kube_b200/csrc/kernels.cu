@@ -422,63 +422,99 @@ void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor) {
 
 // ---------------------------------------------------------------------------------------------
 // Kernel 7: the walk (any2kube.go:58-98), top-down one level per launch.  Per directory: extend the
-// parent's case-folded path hash by "/name", probe the ignore table (hash join in place of
+// parent's case-folded path hash by "/name", probe the ignore table (an exact hash join in place of
 // O(#dirs x #entries) EqualFold scans, utils.go:308-315), then apply the walk's rules given whether
-// the parent was visited and descended into.
+// the parent was visited and descended into.  A hash hit is confirmed rune by rune against the
+// folded entry (walking up the parent chain), so 64-bit collisions cannot change a decision.
 // ---------------------------------------------------------------------------------------------
-__global__ void k_walk_level(const uint32_t* __restrict__ level_dirs, uint32_t n, uint32_t level,
-                             const uint32_t* __restrict__ dir_parent, const uint32_t* __restrict__ dir_entry,
-                             const uint8_t* __restrict__ dir_flags, const uint32_t* __restrict__ entry_name_off,
-                             const uint8_t* __restrict__ names, const uint32_t* __restrict__ fold_from,
-                             const uint32_t* __restrict__ fold_to, const IgnoreSlot* __restrict__ table, uint32_t table_mask,
-                             uint64_t depth1_state, uint8_t root_ignore, const uint32_t* __restrict__ dir_opts,
-                             uint64_t* __restrict__ dir_hash, uint8_t* __restrict__ dir_ignore, uint8_t* __restrict__ dir_state,
-                             uint8_t* __restrict__ dir_descend) {
+struct WalkArgs {
+  const uint32_t* dir_parent; const uint32_t* dir_entry; const uint8_t* dir_flags;
+  const uint32_t* entry_name_off; const uint8_t* names;
+  const uint32_t* fold_from; const uint32_t* fold_to;
+  const IgnoreSlot* table; uint32_t table_mask;
+  const uint32_t* runes;          // folded runes of all table entries
+  const uint32_t* prefix_runes;   // folded runes of the path prefix shared by depth-1 directories
+  uint32_t prefix_len;
+  uint64_t depth1_state; uint32_t root_ignore;
+  const uint32_t* dir_opts;
+  uint64_t* dir_hash; uint8_t* dir_ignore; uint8_t* dir_state; uint8_t* dir_descend;
+};
+
+// does the folded path of directory d equal entry runes E[0..L)?
+__device__ bool path_equals_entry(const WalkArgs& a, uint32_t d, const uint32_t* E, uint32_t L) {
+  uint32_t pos = L;
+  for (uint32_t cur = d;;) {
+    uint32_t e = a.dir_entry[cur];
+    const uint8_t* nm = a.names + a.entry_name_off[e];
+    uint32_t len = a.entry_name_off[e + 1] - a.entry_name_off[e];
+    uint32_t nr = 0;
+    for (uint32_t i = 0; i < len;) { uint32_t w; decode_rune(nm + i, len - i, &w); i += w; nr++; }
+    if (pos < nr) return false;
+    uint32_t k = pos - nr;
+    for (uint32_t i = 0; i < len;) {
+      uint32_t w, r = decode_rune(nm + i, len - i, &w);
+      if (E[k++] != fold_rune(r, a.fold_from, a.fold_to, M2K_CASEFOLD_N)) return false;
+      i += w;
+    }
+    pos -= nr;
+    uint32_t par = a.dir_parent[cur];
+    if (par == 0) break;
+    if (pos == 0 || E[pos - 1] != '/') return false;
+    pos--;
+    cur = par;
+  }
+  if (pos != a.prefix_len) return false;
+  for (uint32_t i = 0; i < pos; i++) if (E[i] != a.prefix_runes[i]) return false;
+  return true;
+}
+
+__global__ void k_walk_level(const uint32_t* __restrict__ level_dirs, uint32_t n, uint32_t level, WalkArgs a) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t d = level_dirs[i];
   uint32_t ign = 0;
   bool visited;
   if (level == 0) {
-    ign = root_ignore;  // the root path is compared on the host exactly as given
+    ign = a.root_ignore;  // the root path is compared on the host exactly as given
     visited = true;
   } else {
-    uint32_t p = dir_parent[d];
-    uint64_t h = (level == 1) ? depth1_state : hash_step(dir_hash[p], '/');
-    uint32_t e = dir_entry[d];
-    uint32_t off = entry_name_off[e], len = entry_name_off[e + 1] - off;
-    h = hash_fold_bytes(h, names + off, len, fold_from, fold_to, M2K_CASEFOLD_N);
-    dir_hash[d] = h;
-    if (table_mask != M2K_NONE) {
+    uint32_t p = a.dir_parent[d];
+    uint64_t h = (level == 1) ? a.depth1_state : hash_step(a.dir_hash[p], '/');
+    uint32_t e = a.dir_entry[d];
+    uint32_t off = a.entry_name_off[e], len = a.entry_name_off[e + 1] - off;
+    h = hash_fold_bytes(h, a.names + off, len, a.fold_from, a.fold_to, M2K_CASEFOLD_N);
+    a.dir_hash[d] = h;
+    if (a.table_mask != M2K_NONE) {
       uint64_t key = hash_finish(h);
-      for (uint32_t s = (uint32_t)key & table_mask;; s = (s + 1) & table_mask) {
-        uint64_t k = table[s].hash;
-        if (k == 0) break;
-        if (k == key) { ign = table[s].flags; break; }
+      for (uint32_t s = (uint32_t)key & a.table_mask;; s = (s + 1) & a.table_mask) {
+        IgnoreSlot sl = a.table[s];
+        if (sl.hash == 0) break;
+        if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, sl.len)) { ign = sl.flags; break; }
       }
     }
-    visited = dir_state[p] != M2K_DIR_NOT_VISITED && dir_descend[p];
+    visited = a.dir_state[p] != M2K_DIR_NOT_VISITED && a.dir_descend[p];
   }
-  dir_ignore[d] = (uint8_t)ign;
+  a.dir_ignore[d] = (uint8_t)ign;
   uint32_t state, descend = 0;
   if (!visited) state = M2K_DIR_NOT_VISITED;
-  else if (dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
+  else if (a.dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
   else if (ign & 4) state = M2K_DIR_PRECONTAINERIZED;
   else if (ign & 1) { if (ign & 2) state = M2K_DIR_IGNORED_PRUNE; else { state = M2K_DIR_IGNORED_DESCEND; descend = 1; } }
-  else if (dir_opts[d] == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
+  else if (a.dir_opts[d] == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
   else state = M2K_DIR_SERVICE;
-  dir_state[d] = (uint8_t)state;
-  dir_descend[d] = (uint8_t)descend;
+  a.dir_state[d] = (uint8_t)state;
+  a.dir_descend[d] = (uint8_t)descend;
 }
 
-void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, uint64_t depth1_state, uint8_t root_ignore) {
+void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
+                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore) {
+  WalkArgs a{t->dir_parent, t->dir_entry, t->dir_flags, t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to,
+             table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore, t->dir_opts,
+             t->dir_hash, t->dir_ignore, t->dir_state, t->dir_descend};
   for (uint32_t L = 0; L <= t->max_depth && t->n_dirs; L++) {
-    uint32_t a = t->level_off[L], b = t->level_off[L + 1];
-    if (b <= a) continue;
-    k_walk_level<<<(b - a + 127) / 128, 128, 0, c->stream>>>(t->level_dirs + a, b - a, L, t->dir_parent, t->dir_entry, t->dir_flags,
-                                                            t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to, table,
-                                                            table_mask, depth1_state, root_ignore, t->dir_opts, t->dir_hash,
-                                                            t->dir_ignore, t->dir_state, t->dir_descend);
+    uint32_t lo = t->level_off[L], hi = t->level_off[L + 1];
+    if (hi <= lo) continue;
+    k_walk_level<<<(hi - lo + 127) / 128, 128, 0, c->stream>>>(t->level_dirs + lo, hi - lo, L, a);
     c->launches++;
   }
 }

@@ -34,7 +34,7 @@ struct NameSig {
 };
 constexpr int kMaxNameSigs = 32;
 
-struct IgnoreSlot { uint64_t hash; uint32_t flags; uint32_t _pad; };
+struct IgnoreSlot { uint64_t hash; uint32_t flags; uint32_t off; uint32_t len; uint32_t _pad; };  // off/len: folded runes of the entry
 
 // a tree (metadata replicated) plus the bytes of file ids [file_begin, file_end) resident in HBM
 struct DevTree {
@@ -79,7 +79,8 @@ struct DevTree {
 struct Ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev[8] = {};
+  cudaEvent_t ev[12] = {};
+  float phase_ms[8] = {};  // names, scan, combine, dockerfile, finalize kernels, host ignore, host verify, d2h
   int sm_count = 0;
   uint64_t launches = 0;
   float last_scan_ms = 0.f;
@@ -96,8 +97,10 @@ void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec);
 void launch_dockerfile(Ctx* c, DevTree* t);
 void launch_subtree(Ctx* c, DevTree* t);
 void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor);
-void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, uint64_t depth1_state,
-                 uint8_t root_ignore);
+void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
+                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore);
+void fold_runes(const std::string& s, std::vector<uint32_t>* out);
+std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clean_root);
 void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, const uint32_t* all_main, uint32_t n_ranks);
 void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed);
 void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);

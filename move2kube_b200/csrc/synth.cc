@@ -197,6 +197,12 @@ int synth_tree_impl(bool pinned, const m2k_synth_params* p, int host_bytes, m2k_
     else if (c < 18) g.cls = SC_NONL;
     else if (c < 23) g.cls = (uint8_t)(SC_NEAR_ARGS + (c - 18) % 4);
     else g.cls = SC_TEXT;
+    if (g.len > (8ull << 20)) g.cls = SC_TEXT;  // config D's multi-GiB files are plain text
+    else if (g.cls == SC_DOCKERFILE || g.cls >= SC_NEAR_ARGS) {
+      // Dockerfiles are small in real trees: log-normal around 1.5 KB, at most 64 KiB
+      double v = exp(log(1500.0) + 1.0 * rng.normal());
+      g.len = (uint64_t)(v < 64 ? 64 : v > 65536 ? 65536 : v);
+    }
     uint32_t m = (uint32_t)((h >> 20) % 1000);
     bool inject = is_py ? (g.name == "main.py" ? m < 500 : m < 20) : m < 5;
     if (inject && g.len >= 72 && g.cls != SC_BINARY) {

@@ -26,7 +26,7 @@ EXPORTS = [
     "m2k_abi_version", "m2k_global_error", "m2k_ctx_create", "m2k_ctx_destroy", "m2k_last_error", "m2k_device_info",
     "m2k_pack_tree", "m2k_tree_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
     "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_finalize",
-    "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
+    "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries",
 ]
 
@@ -66,6 +66,7 @@ def load():
     L.m2k_devtree_free.argtypes = [vp, vp]
     L.m2k_devtree_free.restype = None
     L.m2k_scan_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.m2k_phase_ms.argtypes = [vp, C.POINTER(C.c_float), C.c_int]
     L.m2k_launch_count.argtypes = [vp]
     L.m2k_launch_count.restype = C.c_uint64
     L.m2k_stream.argtypes = [vp]
@@ -180,6 +181,13 @@ class Context:
         ms = C.c_float()
         _check(self.L.m2k_scan_kernel_ms(self.h, C.byref(ms)), self.h)
         return ms.value
+
+    PHASES = ["names", "scan", "combine", "dockerfile", "finalize_kernels", "host_ignore", "host_verify", "d2h"]
+
+    def phase_ms(self):
+        out = (C.c_float * 8)()
+        _check(self.L.m2k_phase_ms(self.h, out, 8), self.h)
+        return dict(zip(self.PHASES, [float(x) for x in out]))
 
     def launch_count(self):
         return int(self.L.m2k_launch_count(self.h))

@@ -1,0 +1,141 @@
+"""GPU tests of the host-side mirror of the reference's interfaces (pytest -m gpu): they read like
+internal/source/any2kube_test.go and internal/common/utils_test.go, with the golden fixtures as
+expected values."""
+import os
+
+import pytest
+
+import golden_check as gc
+import treespec
+from move2kube_b200 import common, containerizer, detection, plan as plantypes, source
+
+pytestmark = pytest.mark.gpu
+
+GOLDENS = {g["name"]: g for g in gc.load_goldens()}
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture()
+def assets(tmp_path, monkeypatch):
+    """An assets directory with the 18 built-in option directories (the mirror only looks at where
+    the detect scripts are, it never runs the built-in ones)."""
+    root = tmp_path / "m2kassets"
+    for n in ["django", "golang", "java-war-jboss", "java-war-liberty", "java-war-tomcat", "javaant", "javagradle",
+              "javamaven", "nodejs", "php", "python", "ruby"]:
+        (root / "dockerfiles" / n).mkdir(parents=True)
+        (root / "dockerfiles" / n / "m2kdfdetect.sh").write_text("#!/bin/sh\nexit 1\n")
+    for n in ["golang", "java", "nodejs", "php", "python", "ruby"]:
+        (root / "s2i" / n).mkdir(parents=True)
+        (root / "s2i" / n / "m2ks2idetect.sh").write_text("#!/bin/sh\nexit 1\n")
+    monkeypatch.setattr(containerizer, "AssetsPath", str(root))
+    yield str(root)
+    detection.reset()
+
+
+def golden_services(spec, root, assets, flavor="bash"):
+    out = []
+    for rel, name, bt, topts in spec["expect"][flavor]["services"]:
+        path = root if rel == "." else os.path.join(root, rel)
+        opts = []
+        for o in topts:
+            if o.startswith("m2kassets/"):
+                opts.append(os.path.join(assets, o[len("m2kassets/"):]))
+            else:
+                opts.append(os.path.join(root, o[len("tree:"):]))
+        out.append((name, bt, path, opts))
+    return out
+
+
+@pytest.mark.parametrize("name", ["samples", "samples_nodejs", "ignorecase1", "ignorecase2", "ignorecontents", "multiignores",
+                                  "emptydir", "nasty", "userscript", "random007", "random031"])
+def test_get_service_options(tmp_path, assets, name):
+    spec = GOLDENS[name]
+    root = treespec.materialize(spec, str(tmp_path / name))
+    translator = source.Any2KubeTranslator()
+    plan = plantypes.NewPlan()
+    plan.SetRootDir(root)
+    services, err = translator.GetServiceOptions(root, plan)
+    assert err is None
+    got = [(s.ServiceName, s.ContainerBuildType, s.SourceArtifacts["SourceCode"][0], s.ContainerizationTargetOptions)
+           for s in services]
+    assert got == golden_services(spec, root, assets)
+    for s in services:
+        assert s.Image == s.ServiceName + ":latest" and s.ServiceRelPath == "/" + s.ServiceName
+        assert s.TranslationType == "Any2Kube" and s.SourceTypes == ["Directory"]
+        assert s.BuildArtifacts["SourceCode"] == s.SourceArtifacts["SourceCode"]
+        assert s.UpdateContainerBuildPipeline and s.UpdateDeployPipeline
+
+
+def test_nonexistent_directory_gives_no_services_and_no_error(tmp_path, assets):
+    """any2kube_test.go:38-53"""
+    services, err = source.Any2KubeTranslator().GetServiceOptions(str(tmp_path / "nope"), plantypes.NewPlan())
+    assert services == [] and err is None
+
+
+def test_source_directory_already_in_the_plan(tmp_path, assets):
+    """any2kube_test.go:179-212: a directory some other translator already containerized is skipped."""
+    spec = GOLDENS["samples_nodejs_pre"]
+    root = treespec.materialize(spec, str(tmp_path / "nodejs"))
+    plan = plantypes.NewPlan()
+    svc = plantypes.NewService("nodejs", "Dockerfile2Kube")
+    svc.SourceArtifacts["SourceCode"] = [root]
+    plan.AddServicesToPlan([svc])
+    services, err = source.Any2KubeTranslator().GetServiceOptions(root, plan)
+    assert services == [] and err is None
+
+
+def test_without_assets_only_host_options_remain(tmp_path, monkeypatch):
+    """The reference's own unit tests run with a non-existent AssetsPath: no
+    Dockerfile / S2I options exist then, and without a container runtime no CNB ones either."""
+    monkeypatch.setattr(containerizer, "AssetsPath", str(tmp_path / "no-assets"))
+    spec = GOLDENS["samples_nodejs"]
+    root = treespec.materialize(spec, str(tmp_path / "nodejs"))
+    services, err = source.Any2KubeTranslator().GetServiceOptions(root, plantypes.NewPlan())
+    assert services == [] and err is None
+    # with a CNB provider hooked in, the golden of any2kube_test.go:97-131 comes back
+    monkeypatch.setattr(containerizer.CNBContainerizer, "provider", staticmethod(lambda path, builder: True))
+    containerizer.CNBContainerizer._cache.clear()
+    services, err = source.Any2KubeTranslator().GetServiceOptions(root, plantypes.NewPlan())
+    assert [(s.ServiceName, s.ContainerBuildType, s.ContainerizationTargetOptions) for s in services] == \
+        [("nodejs", "CNB", ["cloudfoundry/cnb:cflinuxfs3", "gcr.io/buildpacks/builder"])]
+    containerizer.CNBContainerizer._cache.clear()
+    detection.reset()
+
+
+def test_get_files_by_name_and_ext(tmp_path, assets):
+    """utils_test.go:32-140: Walk order, error on a missing root."""
+    spec = GOLDENS["multiignores"]
+    root = treespec.materialize(spec, str(tmp_path / "mi"))
+    files, err = common.GetFilesByName(root, [".m2kignore"])
+    assert err is None
+    assert files == [os.path.join(root, p) for p in [".m2kignore", "a/a/.m2kignore", "b/.m2kignore"]]
+    _, err = common.GetFilesByName(str(tmp_path / "nope"), [".m2kignore"])
+    assert err is not None
+    spec = GOLDENS["samples"]
+    root = treespec.materialize(spec, str(tmp_path / "samples"))
+    files, err = common.GetFilesByExt(root, [".yml", ".yaml"])
+    want = []
+    for dirpath, dirnames, filenames in os.walk(root):
+        for fn in filenames:
+            if os.path.splitext(fn)[1] in (".yml", ".yaml"):
+                want.append(os.path.join(dirpath, fn))
+    assert err is None and sorted(files) == sorted(want) and files == sorted(files, key=lambda p: p.split(os.sep))
+    files, err = common.GetFilesByName(root, ["package.json", "pom.xml"])
+    want = []
+    for dirpath, dirnames, filenames in os.walk(root):
+        want += [os.path.join(dirpath, fn) for fn in filenames if fn in ("package.json", "pom.xml")]
+    want.sort(key=lambda p: p.split(os.sep))
+    assert err is None and files == want and len(files) >= 3
+    assert common.IsStringPresent(["/A/b", "/c"], "/a/B") and not common.IsStringPresent(["/a"], "/ab")
+
+
+def test_dockerfile_translator_finds_dockerfiles(tmp_path, assets):
+    d = tmp_path / "df"
+    (d / "svc").mkdir(parents=True)
+    (d / "svc" / "Dockerfile").write_text("FROM alpine\nRUN true\n")
+    (d / "svc" / "notes.txt").write_text("FROM is just the first word here, twice\n")
+    (d / "build.Dockerfile").write_text("ARG V=1\nFROM alpine:$V AS b\n")
+    (d / "broken").write_text("FROM alpine\nENV X\n")
+    files, err = source.DockerfileTranslator().GetDockerfiles(str(d))
+    assert err is None
+    assert [os.path.relpath(f, str(d)) for f in files] == ["build.Dockerfile", "svc/Dockerfile"]
