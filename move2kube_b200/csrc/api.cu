@@ -15,7 +15,7 @@
 using namespace m2k;
 
 struct m2k_ctx { Ctx c; };
-struct m2k_devtree { DevTree t; float ms_h2d = 0.f; };
+struct m2k_devtree { DevTree t; float ms_h2d = 0.f; uint32_t* h_entry_feat = nullptr; bool content = true; };
 
 static thread_local std::string g_err;
 
@@ -152,7 +152,11 @@ extern "C" int m2k_phase_ms(m2k_ctx* ctx, float* out, int cap) {
 }
 extern "C" int m2k_scan_kernel_ms(m2k_ctx* ctx, float* ms) {
   if (!ctx || !ms) return fail(nullptr, M2K_ERR_ARG, "bad argument");
-  *ms = ctx->c.last_scan_ms;
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaStreamSynchronize(C->stream));
+  if (cudaEventElapsedTime(&C->last_scan_ms, C->ev[2], C->ev[3]) != cudaSuccess) cudaGetLastError();
+  *ms = C->last_scan_ms;
   return M2K_OK;
 }
 
@@ -196,7 +200,8 @@ static void devtree_release(DevTree* t) {
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
                   t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
-                  t->dir_descend, t->file_flags};
+                  t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
+                  t->cand_esc, t->stripe_state};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -204,6 +209,7 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (!dt) return;
   if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); }
   devtree_release(&dt->t);
+  if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
   delete dt;
 }
 
@@ -218,7 +224,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
   DevTree* t = &dt->t;
-  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); delete d; } } } guard{dt};
+  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); delete d; } } } guard{dt};
   t->host = tree;
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
   t->file_begin = file_begin; t->file_end = file_end;
@@ -257,11 +263,20 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(dev_alloc(&t->chunk_first, (size_t)ns + 1));
   CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne));
+  {
+    uint64_t cap = (t->shard_bytes + 4095) / 4096 + ns + 1;  // stripes of 4 KiB over every file body, rounded up per file
+    if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile stripe table");
+    t->stripe_cap = (uint32_t)cap;
+    CU(dev_alloc(&t->df_counters, 2)); CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_first, (size_t)ns + 1));
+    CU(dev_alloc(&t->cand_err, ns)); CU(dev_alloc(&t->cand_body, ns)); CU(dev_alloc(&t->cand_esc, ns));
+    CU(dev_alloc(&t->stripe_state, cap));
+  }
   CU(dev_alloc(&t->dir_direct, nd)); CU(dev_alloc(&t->dir_first_war, nd)); CU(dev_alloc(&t->dir_content, nd));
   CU(dev_alloc(&t->dir_main, nd)); CU(dev_alloc(&t->dir_subtree, nd)); CU(dev_alloc(&t->dir_main_sub, nd));
   CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_hash, nd)); CU(dev_alloc(&t->dir_ignore, nd));
   CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd)); CU(dev_alloc(&t->file_flags, nf));
 
+  CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
   cudaStream_t s = C->stream;
   CU(cudaEventRecord(C->ev[0], s));
   auto H2D = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess; };
@@ -326,7 +341,10 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaMemsetAsync(t->file_flags, 0, t->n_files, s));
   CU(cudaEventRecord(C->ev[8], s));
   launch_name_features(C, t);
+  // the host needs the name features (which entries are .m2kignore files) while the byte scan runs
+  CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[2], s));
+  dt->content = content;
   if (content) {
     launch_scan_bytes(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[3], s));
@@ -336,16 +354,20 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
     CU(cudaEventRecord(C->ev[10], s));
   }
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(s));
+  // no synchronisation here: m2k_finalize overlaps its host work with these kernels
+  t->scanned = true;
+  return M2K_OK;
+}
+
+static int collect_scan_timings(Ctx* C, m2k_devtree* dt) {
   memset(C->phase_ms, 0, sizeof C->phase_ms);
   CU(cudaEventElapsedTime(&C->phase_ms[0], C->ev[8], C->ev[2]));
-  if (content) {
+  if (dt->content) {
     CU(cudaEventElapsedTime(&C->last_scan_ms, C->ev[2], C->ev[3]));
     C->phase_ms[1] = C->last_scan_ms;
     CU(cudaEventElapsedTime(&C->phase_ms[2], C->ev[3], C->ev[9]));
     CU(cudaEventElapsedTime(&C->phase_ms[3], C->ev[9], C->ev[10]));
   }
-  t->scanned = true;
   return M2K_OK;
 }
 
@@ -444,9 +466,9 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaEventRecord(C->ev[4], s));
   launch_subtree(C, t);
   launch_combine_opts(C, t, sh);
-  CU(cudaMemcpyAsync(r->entry_feat, t->entry_feat, 4ull * ne, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[7], s));
-  CU(cudaStreamSynchronize(s));
+  CU(cudaEventSynchronize(C->ev[2]));  // name features are on the host; the byte scan may still be running
+  memcpy(r->entry_feat, dt->h_entry_feat, 4ull * ne);
 
   // getIgnorePaths (any2kube.go:151-181): the .m2kignore files come from the name-feature bit
   double h0 = now_ms();
@@ -545,6 +567,7 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   cudaError_t werr = cudaStreamSynchronize(s);
   if (d_blob) cudaFree(d_blob);
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "walk kernels failed: %s", cudaGetErrorString(werr));
+  if (int rc = collect_scan_timings(C, dt)) return rc;
   float ms_k1 = 0, ms_k2 = 0, ms_d = 0;
   CU(cudaEventElapsedTime(&ms_k1, C->ev[4], C->ev[7]));
   CU(cudaEventElapsedTime(&ms_k2, C->ev[11], C->ev[5]));

@@ -358,20 +358,23 @@ __device__ inline bool directive_ok(File& f, uint64_t lb, uint64_t le, bool* pro
   return true;
 }
 
-// Returns M2K_FILE_FROM_FIRST / M2K_FILE_DOCKERFILE bits (4 / 8).  `long_line`: the byte scan found
-// a line of >= 65536 bytes (Parse fails; also keeps this thread from walking such a line).
-__device__ inline uint32_t classify(const uint8_t* p, uint64_t n, bool long_line) {
-  if (long_line || n == 0) return 0;
+// Head of the file: parser directives, comments, ARG lines, up to the first other instruction.
+// Returns true when that instruction is FROM and matches the reference's regexp; then *body is the
+// offset of the first physical line after it and *esc the escape token in force.  Everything after
+// `body` can no longer change the answer except by a parse error, which the striped validation
+// below looks for in parallel.  `long_line`: the byte scan found a line of >= 65536 bytes (Parse
+// fails; it also keeps this thread from walking such a line).
+__device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64_t* body, uint32_t* esc) {
+  if (long_line || n == 0) return false;
   File f{p, n, '\\'};
   bool processing_complete = false, escape_seen = false;
-  bool decided = false, from_first = false;
   uint64_t pos = 0;
   bool first_line = true;
   while (pos < n) {
     uint64_t lb = pos, le;
-    // quick reject before looking for the end of the line: a first token that ends at a blank
-    // inside this physical line and is no keyword settles "first instruction is not FROM"
-    if (!decided) {
+    // quick reject before looking for the end of the line: once the first word can no longer become a
+    // keyword, "first instruction is not FROM" is settled
+    {
       uint64_t q = lb;
       if (first_line && n - q >= 3 && p[q] == 0xEF && p[q + 1] == 0xBB && p[q + 2] == 0xBF) q += 3;
       while (q < n && p[q] != '\n') { uint32_t w, r = decode_rune(p + q, n - q, &w); if (!is_space_rune(r)) break; q += w; }
@@ -387,29 +390,99 @@ __device__ inline uint32_t classify(const uint8_t* p, uint64_t n, bool long_line
           alive = kw_step(alive, idx, r);
           idx++; t += w;
         }
-        if (alive == 0) return 0;  // the command word cannot become from/arg/env/label/onbuild any more
+        if (alive == 0) return false;  // the command word cannot become from/arg/env/label/onbuild any more
       }
     }
     pos = phys_line(f, lb, &le);
     if (first_line) { if (le - lb >= 3 && p[lb] == 0xEF && p[lb + 1] == 0xBB && p[lb + 2] == 0xBF) lb += 3; first_line = false; }
     while (lb < le) { uint32_t w, r = decode_rune(p + lb, le - lb, &w); if (!is_space_rune(r)) break; lb += w; }  // trimWhitespace
-    if (!directive_ok(f, lb, le, &processing_complete, &escape_seen)) return 0;
+    if (!directive_ok(f, lb, le, &processing_complete, &escape_seen)) return false;
     if (lb < le && p[lb] == '#') le = lb;  // trimComments
     bool more = trim_continuation(f, lb, &le);
     if (!more && le == lb) continue;
     LCur start{lb, le, pos, more};
     int kind;
-    if (!node_from_line(f, start, &kind)) return from_first ? 4u : 0u;
-    if (!decided && kind != 2) {
-      decided = true;
-      if (kind != 1 || !from_regex(f, start)) return 0;
-      from_first = true;
-    }
+    if (!node_from_line(f, start, &kind)) return false;
     LCur endc = start;
     while (lc_get(f, endc) >= 0) {}
     pos = endc.next_line;
+    if (kind == 2) continue;  // ARG: keep looking
+    if (kind != 1 || !from_regex(f, start)) return false;
+    *body = pos < n ? pos : n;
+    *esc = f.esc;
+    return true;
   }
-  return from_first ? (4u | 8u) : 0u;
+  return false;  // file with no instructions (or only ARG)
+}
+
+// ---- striped validation of the body ---------------------------------------------------------------
+// Whether a physical line starts a logical line depends on one bit of state carried from the line
+// before it: OUT (0) or inside a continuation (1).  Each line maps that state to the next, so the
+// state at any offset is a prefix composition of 2-bit maps: bit0 = next state from OUT, bit1 = next
+// state from IN.  Stripes of the body compute their composed map (k_df_maps), a per-file scan turns
+// the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
+// lines that start inside it (k_df_validate).
+constexpr uint32_t kStripe = 4096;
+
+__device__ inline uint32_t line_map(const File& f, uint64_t lb, uint64_t le) {
+  // from IN: comment and blank lines are dropped and the continuation goes on
+  bool cont = false;
+  { uint64_t e = le; cont = trim_continuation(f, lb, &e); }
+  bool raw_comment = lb < le && f.p[lb] == '#';
+  bool blank_line = all_space(f, lb, le);
+  uint32_t from_in = (raw_comment || blank_line) ? 1u : (cont ? 1u : 0u);
+  // from OUT: the line is left-trimmed first; comments and empty lines are skipped
+  uint64_t t = lb;
+  while (t < le) { uint32_t w, r = decode_rune(f.p + t, le - t, &w); if (!is_space_rune(r)) break; t += w; }
+  uint32_t from_out = (t == le || f.p[t] == '#') ? 0u : (cont ? 1u : 0u);
+  return from_out | (from_in << 1);
+}
+__device__ __forceinline__ uint32_t map_apply(uint32_t m, uint32_t state) { return (m >> state) & 1u; }
+__device__ __forceinline__ uint32_t map_compose(uint32_t first, uint32_t then) {  // then(first(x))
+  return map_apply(then, map_apply(first, 0)) | (map_apply(then, map_apply(first, 1)) << 1);
+}
+
+// first physical-line start at or after `a` (a line starts at `body` or right after a '\n')
+__device__ inline uint64_t first_line_start(const File& f, uint64_t body, uint64_t a) {
+  if (a <= body) return body;
+  uint64_t q = a;
+  if (f.p[q - 1] == '\n') return q;
+  while (q < f.n && f.p[q] != '\n') q++;
+  return q + 1;
+}
+
+// composed map of the lines that START in [a, b)
+__device__ inline uint32_t stripe_map(const File& f, uint64_t body, uint64_t a, uint64_t b) {
+  uint32_t m = 0x2;  // identity: OUT->OUT, IN->IN
+  uint64_t q = first_line_start(f, body, a);
+  while (q < b && q < f.n) {
+    uint64_t le, next = phys_line(f, q, &le);
+    m = map_compose(m, line_map(f, q, le));
+    q = next;
+  }
+  return m;
+}
+
+// checks every logical line that starts in [a, b), given the state at the first line start; false = parse error
+__device__ inline bool stripe_validate(const File& f, uint64_t body, uint64_t a, uint64_t b, uint32_t state) {
+  uint64_t q = first_line_start(f, body, a);
+  while (q < b && q < f.n) {
+    uint64_t le, next = phys_line(f, q, &le);
+    if (state == 0) {
+      uint64_t lb = q;
+      while (lb < le) { uint32_t w, r = decode_rune(f.p + lb, le - lb, &w); if (!is_space_rune(r)) break; lb += w; }
+      if (lb < le && f.p[lb] != '#') {
+        uint64_t e2 = le;
+        bool more = trim_continuation(f, lb, &e2);
+        LCur start{lb, e2, next, more};
+        int kind;
+        if (!node_from_line(f, start, &kind)) return false;
+      }
+    }
+    state = map_apply(line_map(f, q, le), state);
+    q = next;
+  }
+  return true;
 }
 
 }  // namespace df

@@ -316,30 +316,152 @@ void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 4: isDockerFile, one thread per file (dockerfile_dev.cuh).  Nearly every file leaves after
-// a few bytes ("first instruction is not FROM"); real Dockerfiles are parsed to the end.
+// Kernel 4: isDockerFile (dockerfile_dev.cuh), in five small launches so that no single thread ever
+// walks a whole file:
+//   k_df_head     one thread per file: directives, comments, ARGs, first instruction.  Nearly every
+//                 file leaves after a few bytes; FROM-first files become candidates (scratch list).
+//   k_df_prefix   one block: exclusive prefix of the candidates' stripe counts.
+//   k_df_maps     one thread per 4 KiB stripe of candidate bodies: composed line-state map.
+//   k_df_scan     one thread per candidate: state at every stripe start.
+//   k_df_validate one thread per stripe: parse errors of the logical lines starting in it;
+//   k_df_finish   one thread per candidate: DOCKERFILE bit + per-directory content bit.
+// Grids are fixed multiples of the SM count and read the candidate counts from device memory, so the
+// host never waits for them.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_dockerfile(
-    uint32_t n_shard_files, uint32_t file_begin, const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len,
-    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, const uint32_t* __restrict__ file_entry,
-    const uint32_t* __restrict__ entry_dir, uint8_t* __restrict__ file_flags, uint32_t* __restrict__ dir_content) {
+struct DfArgs {
+  uint32_t n_shard_files, file_begin;
+  const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
+  const uint32_t* file_entry; const uint32_t* entry_dir;
+  uint8_t* file_flags; uint32_t* dir_content;
+  uint32_t* counters;     // [0] candidates, [1] total stripes
+  uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_first; uint32_t* cand_err;
+  uint8_t* stripe_state;  // per stripe: bits 0-1 composed map, bit 2 state at the stripe start
+  uint32_t stripe_cap;
+};
+
+__device__ __forceinline__ df::File df_file(const DfArgs& a, uint32_t f, uint32_t esc) {
+  return df::File{a.bytes + (a.file_off[f] - a.shard_byte0), a.file_len[f], esc};
+}
+
+__global__ void __launch_bounds__(128) k_df_head(DfArgs a) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_shard_files) return;
-  uint32_t f = file_begin + i;
-  uint32_t flags = file_flags[f];
-  uint32_t bits = df::classify(bytes + (file_off[f] - shard_byte0), file_len[f], (flags & M2K_FILE_LONG_LINE) != 0);
-  if (bits) {
-    file_flags[f] = (uint8_t)(flags | bits);
-    if (bits & M2K_FILE_DOCKERFILE) atomicOr(&dir_content[entry_dir[file_entry[f]]], 1u << M2K_C_DOCKERFILE);
+  if (i >= a.n_shard_files) return;
+  uint32_t f = a.file_begin + i;
+  uint32_t flags = a.file_flags[f];
+  uint64_t body = 0, n = a.file_len[f];
+  uint32_t esc = '\\';
+  if (!df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n, (flags & M2K_FILE_LONG_LINE) != 0, &body, &esc)) return;
+  a.file_flags[f] = (uint8_t)(flags | M2K_FILE_FROM_FIRST);
+  uint32_t c = atomicAdd(&a.counters[0], 1u);
+  a.cand_file[c] = f;
+  a.cand_body[c] = body;
+  a.cand_esc[c] = (uint8_t)esc;
+  a.cand_err[c] = 0;
+  a.cand_first[c] = (uint32_t)((n - body + df::kStripe - 1) / df::kStripe);  // stripe count, prefix-summed next
+}
+
+__global__ void __launch_bounds__(1024) k_df_prefix(DfArgs a) {
+  __shared__ uint32_t s_part[1024];
+  __shared__ uint32_t s_carry;
+  const uint32_t n = a.counters[0];
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < n; base += 1024) {
+    uint32_t i = base + threadIdx.x;
+    uint32_t v = i < n ? a.cand_first[i] : 0;
+    s_part[threadIdx.x] = v;
+    __syncthreads();
+    for (uint32_t off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
+      uint32_t t = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0;
+      __syncthreads();
+      s_part[threadIdx.x] += t;
+      __syncthreads();
+    }
+    uint32_t incl = s_part[threadIdx.x], carry = s_carry;
+    if (i < n) a.cand_first[i] = carry + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = carry + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    uint32_t total = s_carry;
+    a.cand_first[n] = total;
+    a.counters[1] = total <= a.stripe_cap ? total : 0xFFFFFFFFu;  // cannot happen: the cap is the worst case
+  }
+}
+
+__device__ __forceinline__ bool df_stripe(const DfArgs& a, uint32_t s, uint32_t* c, uint64_t* lo, uint64_t* hi) {
+  uint32_t nc = a.counters[0];
+  uint32_t l = 0, h = nc;  // last candidate with cand_first <= s
+  while (h - l > 1) { uint32_t m = (l + h) >> 1; if (a.cand_first[m] <= s) l = m; else h = m; }
+  *c = l;
+  uint64_t body = a.cand_body[l];
+  *lo = body + (uint64_t)(s - a.cand_first[l]) * df::kStripe;
+  uint64_t n = a.file_len[a.cand_file[l]];
+  *hi = *lo + df::kStripe < n ? *lo + df::kStripe : n;
+  return true;
+}
+
+__global__ void __launch_bounds__(128) k_df_maps(DfArgs a) {
+  const uint32_t total = a.counters[1];
+  if (total == 0xFFFFFFFFu) return;
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < total; s += gridDim.x * blockDim.x) {
+    uint32_t c; uint64_t lo, hi;
+    df_stripe(a, s, &c, &lo, &hi);
+    df::File f = df_file(a, a.cand_file[c], a.cand_esc[c]);
+    a.stripe_state[s] = (uint8_t)df::stripe_map(f, a.cand_body[c], lo, hi);
+  }
+}
+
+__global__ void __launch_bounds__(128) k_df_scan(DfArgs a) {
+  const uint32_t nc = a.counters[0];
+  if (a.counters[1] == 0xFFFFFFFFu) return;
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
+    uint32_t state = 0;
+    for (uint32_t s = a.cand_first[c]; s < a.cand_first[c + 1]; s++) {
+      uint32_t m = a.stripe_state[s] & 3u;
+      a.stripe_state[s] = (uint8_t)(m | (state << 2));
+      state = df::map_apply(m, state);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) k_df_validate(DfArgs a) {
+  const uint32_t total = a.counters[1];
+  if (total == 0xFFFFFFFFu) return;
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < total; s += gridDim.x * blockDim.x) {
+    uint32_t c; uint64_t lo, hi;
+    df_stripe(a, s, &c, &lo, &hi);
+    df::File f = df_file(a, a.cand_file[c], a.cand_esc[c]);
+    if (!df::stripe_validate(f, a.cand_body[c], lo, hi, (a.stripe_state[s] >> 2) & 1u)) a.cand_err[c] = 1;
+  }
+}
+
+__global__ void __launch_bounds__(128) k_df_finish(DfArgs a) {
+  const uint32_t nc = a.counters[0];
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
+    if (a.cand_err[c] || a.counters[1] == 0xFFFFFFFFu) continue;
+    uint32_t f = a.cand_file[c];
+    a.file_flags[f] |= M2K_FILE_DOCKERFILE;
+    atomicOr(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
   }
 }
 
 void launch_dockerfile(Ctx* c, DevTree* t) {
   uint32_t nf = t->file_end - t->file_begin;
   if (!nf) return;
-  k_dockerfile<<<(nf + 127) / 128, 128, 0, c->stream>>>(nf, t->file_begin, t->file_off, t->file_len, t->bytes, t->shard_byte0,
-                                                        t->file_entry, t->entry_dir, t->file_flags, t->dir_content);
-  c->launches++;
+  DfArgs a{nf, t->file_begin, t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir,
+           t->file_flags, t->dir_content, t->df_counters, t->cand_file, t->cand_body, t->cand_esc, t->cand_first, t->cand_err,
+           t->stripe_state, t->stripe_cap};
+  cudaMemsetAsync(t->df_counters, 0, 8, c->stream);
+  k_df_head<<<(nf + 127) / 128, 128, 0, c->stream>>>(a);
+  k_df_prefix<<<1, 1024, 0, c->stream>>>(a);
+  const int grid = c->sm_count * 8;
+  k_df_maps<<<grid, 128, 0, c->stream>>>(a);
+  k_df_scan<<<grid, 128, 0, c->stream>>>(a);
+  k_df_validate<<<grid, 128, 0, c->stream>>>(a);
+  k_df_finish<<<grid, 128, 0, c->stream>>>(a);
+  c->launches += 6;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -60,6 +60,12 @@ struct DevTree {
   uint64_t* synth_inject = nullptr;
   // work buffers
   uint32_t* chunk_rec = nullptr;          // [n_chunks] scratch
+  // isDockerFile scratch: candidate list and per-stripe line states (worst case: every file a candidate)
+  uint32_t* df_counters = nullptr;        // [2]
+  uint32_t *cand_file = nullptr, *cand_first = nullptr, *cand_err = nullptr;
+  uint64_t* cand_body = nullptr;
+  uint8_t *cand_esc = nullptr, *stripe_state = nullptr;
+  uint32_t stripe_cap = 0;
   uint32_t* entry_feat = nullptr;         // [n_entries]
   uint32_t* dir_direct = nullptr;         // [n_dirs]
   uint32_t* dir_first_war = nullptr;      // [n_dirs]
