@@ -264,7 +264,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne));
   {
-    uint64_t cap = (t->shard_bytes + 4095) / 4096 + ns + 1;  // stripes of 4 KiB over every file body, rounded up per file
+    uint64_t cap = (t->shard_bytes + kDfStripe - 1) / kDfStripe + ns + 1;  // stripes over every file body, rounded up per file
     if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile stripe table");
     t->stripe_cap = (uint32_t)cap;
     CU(dev_alloc(&t->df_counters, 2)); CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_first, (size_t)ns + 1));

@@ -28,10 +28,23 @@ __device__ __forceinline__ bool blank(uint32_t c) { return c == ' ' || c == '\t'
 __device__ __forceinline__ bool ascii_ws(uint32_t c) { return c == '\t' || c == '\v' || c == '\f' || c == '\r' || c == ' '; }  // tokenWhitespace
 __device__ __forceinline__ bool re_s(uint32_t c) { return c == '\t' || c == '\n' || c == '\f' || c == '\r' || c == ' '; }        // RE2 \s
 
-// physical line starting at pos: [lb, le) without '\n' and one trailing '\r'; returns start of next line
+// physical line starting at pos: [lb, le) without '\n' and one trailing '\r'; returns start of next line.
+// File bases are 16-byte aligned and zero padded to 16 bytes (include/m2kdetect.h), so the search for
+// the newline reads aligned 8-byte words (SWAR) once pos is aligned.
 __device__ inline uint64_t phys_line(const File& f, uint64_t pos, uint64_t* le) {
   uint64_t e = pos;
-  while (e < f.n && f.p[e] != '\n') e++;
+  while (e < f.n && (e & 7) && f.p[e] != '\n') e++;
+  if (e < f.n && !(e & 7) && f.p[e] != '\n') {
+    const uint64_t ones = 0x0101010101010101ull, nl = 0x0A0A0A0A0A0A0A0Aull;
+    for (;;) {
+      uint64_t w = *reinterpret_cast<const uint64_t*>(f.p + e) ^ nl;
+      uint64_t z = (w - ones) & ~w & 0x8080808080808080ull;
+      if (z) { e += (uint64_t)(__ffsll((long long)z) - 1) >> 3; break; }
+      e += 8;
+      if (e >= f.n) break;
+    }
+    if (e > f.n) e = f.n;
+  }
   uint64_t next = e + 1;
   if (e > pos && f.p[e - 1] == '\r') e--;
   *le = e;
@@ -422,7 +435,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 // state from IN.  Stripes of the body compute their composed map (k_df_maps), a per-file scan turns
 // the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
 // lines that start inside it (k_df_validate).
-constexpr uint32_t kStripe = 4096;
+constexpr uint32_t kStripe = 1024;  // == kDfStripe (m2k_internal.h)
 
 __device__ inline uint32_t line_map(const File& f, uint64_t lb, uint64_t le) {
   // from IN: comment and blank lines are dropped and the continuation goes on
@@ -471,7 +484,21 @@ __device__ inline bool stripe_validate(const File& f, uint64_t body, uint64_t a,
     if (state == 0) {
       uint64_t lb = q;
       while (lb < le) { uint32_t w, r = decode_rune(f.p + lb, le - lb, &w); if (!is_space_rune(r)) break; lb += w; }
-      if (lb < le && f.p[lb] != '#') {
+      bool check = lb < le && f.p[lb] != '#';
+      if (check) {
+        // only ENV, LABEL and ONBUILD can fail: skip the line when its first word, ended by a blank
+        // inside this physical line, cannot be one of them
+        uint32_t alive = 4 | 8 | 16, idx = 0;
+        for (uint64_t t = lb; t < le && alive; idx++) {
+          uint32_t c0 = f.p[t];
+          if (ascii_ws(c0)) break;
+          if (c0 == f.esc || c0 >= 0x80) { alive = 0x1F; break; }  // continuation or non-ASCII: exact path
+          alive = kw_step(alive, idx, c0);
+          t++;
+        }
+        check = alive != 0;
+      }
+      if (check) {
         uint64_t e2 = le;
         bool more = trim_continuation(f, lb, &e2);
         LCur start{lb, e2, next, more};

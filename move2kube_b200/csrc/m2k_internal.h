@@ -11,6 +11,7 @@ namespace m2k {
 
 constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
+constexpr uint32_t kDfStripe = 1024;     // bytes of one stripe of the parallel Dockerfile validation
 constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
 constexpr uint32_t kLongUnits = (kLongLine - 30 + 15) / 16;  // newline-free 16-byte units a long line must contain (4095)
 
