@@ -159,7 +159,10 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
     const uint64_t range = flen - start < kChunkBytes ? flen - start : kChunkBytes;
     const uint32_t n_units = (uint32_t)((range + 15) >> 4);
     const uint4* src = reinterpret_cast<const uint4*>(fbase + start);
-    uint32_t q = 0, lead = M2K_NONE, found = 0;
+    // Inside one 64 KiB chunk a newline-free run that is closed on both sides is shorter than 64 KiB,
+    // so only the first and the last newline of the chunk matter: newlines are looked for until the
+    // first one is found, and again in the last batch of rows.
+    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0;
     for (uint32_t u0 = 0; u0 < n_units; u0 += 32 * kScanRows) {
       uint4 v[kScanRows];
 #pragma unroll
@@ -167,34 +170,54 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
         uint32_t u = u0 + r * 32 + lane;
         v[r] = u < n_units ? ldg_stream(src + u) : make_uint4(0, 0, 0, 0);
       }
+      const bool want_nl = lead == M2K_NONE || u0 + 32 * kScanRows >= n_units;  // warp-uniform
+      bool hit_any = false;
 #pragma unroll
-      for (int r = 0; r < kScanRows; r++) {
-        uint32_t ubase = u0 + r * 32;
-        if (ubase >= n_units) break;  // warp-uniform
-        uint32_t valid = n_units - ubase < 32 ? n_units - ubase : 32;
-        bool hit = main_word(v[r].x) || main_word(v[r].y) || main_word(v[r].z) || main_word(v[r].w);
-        uint32_t nlm = has_newline(v[r]);
-        uint32_t B = __ballot_sync(FULL, nlm != 0);
-        if (__any_sync(FULL, hit)) {
-          bool ok = false;
-          if (hit) {
-            uint64_t pos = start + (uint64_t)(ubase + lane) * 16;
-            if (main_word(v[r].x)) ok = ok || confirm_main(fbase, flen, pos);
-            if (main_word(v[r].y)) ok = ok || confirm_main(fbase, flen, pos + 4);
-            if (main_word(v[r].z)) ok = ok || confirm_main(fbase, flen, pos + 8);
-            if (main_word(v[r].w)) ok = ok || confirm_main(fbase, flen, pos + 12);
-          }
-          if (__any_sync(FULL, ok)) found = 1;
+      for (int r = 0; r < kScanRows; r++)
+        hit_any = hit_any || main_word(v[r].x) || main_word(v[r].y) || main_word(v[r].z) || main_word(v[r].w);
+      if (__any_sync(FULL, hit_any)) {  // rare: confirm bytewise, file bounds respected
+        bool ok = false;
+#pragma unroll
+        for (int r = 0; r < kScanRows; r++) {
+          uint64_t pos = start + (uint64_t)(u0 + r * 32 + lane) * 16;
+          if (main_word(v[r].x)) ok = ok || confirm_main(fbase, flen, pos);
+          if (main_word(v[r].y)) ok = ok || confirm_main(fbase, flen, pos + 4);
+          if (main_word(v[r].z)) ok = ok || confirm_main(fbase, flen, pos + 8);
+          if (main_word(v[r].w)) ok = ok || confirm_main(fbase, flen, pos + 12);
         }
-        if (B == 0) q += valid;
-        else {
-          uint32_t firstl = __ffs(B) - 1, lastl = 31 - __clz(B);
-          if (lead == M2K_NONE) lead = q + firstl;
-          q = valid - 1 - lastl;
+        if (__any_sync(FULL, ok)) found = 1;
+      }
+      if (want_nl) {
+#pragma unroll
+        for (int r = 0; r < kScanRows; r++) {
+          uint32_t ubase = u0 + r * 32;
+          uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);  // rows past the end are zero: no newline
+          if (B) {
+            if (lead == M2K_NONE) lead = ubase + (uint32_t)__ffs(B) - 1;
+            last_nl = ubase + 31 - (uint32_t)__clz(B);
+          }
         }
       }
     }
-    if (lead == M2K_NONE) lead = q;
+    uint32_t trail;
+    if (lead == M2K_NONE) {
+      lead = trail = n_units;  // no newline in the whole chunk
+    } else {
+      const uint32_t last_batch0 = ((n_units - 1) / (32 * kScanRows)) * (32 * kScanRows);
+      if (last_nl == M2K_NONE || last_nl < last_batch0) {
+        // the last batch has no newline (rare): walk back row by row; the unit `lead` stops the search
+        uint32_t ubase = last_batch0;
+        last_nl = M2K_NONE;
+        while (last_nl == M2K_NONE) {
+          ubase -= 32;
+          uint4 w = ldg_stream(src + ubase + lane);
+          uint32_t B = __ballot_sync(FULL, has_newline(w) != 0);
+          if (B) last_nl = ubase + 31 - (uint32_t)__clz(B);
+        }
+      }
+      trail = n_units - 1 - last_nl;
+    }
+    const uint32_t q = trail;
     if (lane == 0) chunk_rec[item] = rec_pack(lead, q, found);
   }
 }
