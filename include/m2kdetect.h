@@ -227,6 +227,27 @@ int m2k_phase_ms(m2k_ctx* ctx, float* out, int cap);
 uint64_t m2k_launch_count(const m2k_ctx* ctx);
 void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
 
+/* -- the byte scan without any GPU allocation (no counterpart in the reference) --
+ * For hosts that cannot call cudaMalloc where they call this library: inside work they are
+ * capturing or replaying, under a device-memory arena that is handed out once and then locked, or
+ * under a fixed memory quota.  The caller owns every buffer; the scan's only scratch, the per-chunk
+ * record table, is a fixed 1 MiB array in the library image (held by every GPU that loads the
+ * library until exit), which limits one call to 262144 chunks of 64 KiB (16 GiB of content): more
+ * is refused with M2K_ERR_LIMIT.  All pointers are DEVICE pointers on `device`:
+ *   d_bytes        file contents; each file starts at a multiple of 16, is zero padded to 16 bytes,
+ *                  and at least 16 zero bytes follow the last file
+ *   d_file_off/len [n_files] offset into d_bytes / length in bytes
+ *   d_chunk_first  [n_files+1] exclusive prefix sum of ceil(len / 65536); n_chunks = d_chunk_first[n_files]
+ *   d_file_flags   [n_files] out: M2K_FILE_HAS_MAIN | M2K_FILE_LONG_LINE
+ * Work is queued on `stream` (a cudaStream_t, NULL = default stream) and not waited for.  The first
+ * call on a device looks up the table's device address: make it before any stream capture.  Calls
+ * share the table; run them one after the other (overlapping calls race on it).  Nothing in the
+ * table needs clearing between calls: each call writes every record it later reads.
+ * Error text: m2k_global_error(). */
+int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d_bytes, const uint64_t* d_file_off,
+                           const uint64_t* d_file_len, const uint32_t* d_chunk_first, uint32_t n_files,
+                           uint32_t n_chunks, uint8_t* d_file_flags);
+
 /* -- host-side path helpers the mirror needs (Go stdlib semantics) -- */
 int m2k_path_clean(const char* path, char* out, size_t cap);              /* filepath.Clean */
 int m2k_equal_fold(const char* a, size_t na, const char* b, size_t nb);   /* strings.EqualFold */

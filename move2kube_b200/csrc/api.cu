@@ -30,6 +30,10 @@ static int fail(Ctx* c, int code, const char* fmt, ...) {
   return code;
 }
 
+namespace m2k {
+void set_global_error(const char* msg) { g_err = msg ? msg : ""; }
+}  // namespace m2k
+
 #define CU(call)                                                                                              \
   do {                                                                                                        \
     cudaError_t e_ = (call);                                                                                  \

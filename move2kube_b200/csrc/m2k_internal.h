@@ -112,6 +112,8 @@ void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, cons
 void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed);
 void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
 
+void set_global_error(const char* msg);  // api.cu: what m2k_global_error() returns on this thread
+
 // ---- host helpers (hostpath.cc) ----
 std::string path_clean(const std::string& p);
 std::string path_join(const std::string& a, const std::string& b);

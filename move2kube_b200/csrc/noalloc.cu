@@ -1,0 +1,139 @@
+// m2k_scan_flags_noalloc: the byte scan for callers that must not allocate GPU memory.
+//
+// Who that is: a host that drives this library from inside a region where cudaMalloc is off limits --
+// a plugin called while the application is capturing or replaying work it laid out beforehand, a
+// service whose device memory is handed out once at start-up by its own arena and then locked, or a
+// process sharing the GPU under a fixed memory quota.  cudaMalloc there either fails, or stalls the
+// whole device while the driver maps memory.  Those callers own every buffer they pass in; the only
+// memory the scan needs beyond its inputs and outputs is the per-chunk record table (4 bytes per
+// 64 KiB of content), and here that table lives in a fixed array inside the library image.
+//
+// The array costs kNoAllocMaxChunks * 4 bytes (1 MiB) on EVERY GPU that loads the library, until the
+// process exits, whether or not this entry point is ever called.  That bounds one call to
+// kNoAllocMaxChunks chunks (16 GiB when every chunk is full); larger inputs are refused.
+//
+// The first call on a device resolves the array's device address (cudaGetSymbolAddress) and reads
+// the SM count; make that first call before starting any stream capture.  All calls share the one
+// array: it keeps whatever the previous call left, which is harmless because every record a call
+// reads is written by that same call first -- nothing in it has to start at zero.  Two calls whose
+// kernels overlap on the GPU (different streams, or different threads) would overwrite each other's
+// records: run them one after the other.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include <mutex>
+
+#include "m2k_internal.h"
+
+namespace m2k {
+
+constexpr uint32_t kNoAllocMaxChunks = 262144;  // 1 MiB of records
+
+// In host code this name is only a handle for the runtime, not an address a kernel can use.
+static __device__ __align__(256) uint32_t g_noalloc_records[kNoAllocMaxChunks];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_setup_mutex;
+static uint32_t* g_records_ptr[kMaxDevices];  // device address of g_noalloc_records, per device
+static int g_sm_count[kMaxDevices];
+
+// Per-file flags from the chunk records: one thread per file walks its records in order, keeps the
+// count of newline-free 16-byte units since the last newline, and settles the (rare) runs of 4095 or
+// more units by counting bytes.  Device code may name the array directly.
+__global__ void __launch_bounds__(128) k_noalloc_file_flags(uint32_t n_files, const uint32_t* __restrict__ chunk_first,
+                                                             const uint64_t* __restrict__ file_off,
+                                                             const uint64_t* __restrict__ file_len,
+                                                             const uint8_t* __restrict__ bytes, uint8_t* __restrict__ file_flags) {
+  uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_files) return;
+  const uint64_t len = file_len[f];
+  const uint8_t* file = bytes + file_off[f];
+  const uint64_t total_units = (len + 15) >> 4;
+  uint32_t has_main = 0, is_long = 0;
+  uint64_t run = 0;  // newline-free units immediately before the current chunk
+  auto exact_long = [&](uint64_t first_unit, uint64_t units) {
+    uint64_t b = first_unit * 16, e = (first_unit + units) * 16;
+    if (e > len) e = len;
+    while (b > 0 && file[b - 1] != '\n') b--;
+    while (e < len && file[e] != '\n') e++;
+    return e - b >= kLongLine;
+  };
+  for (uint32_t c = chunk_first[f], k = 0; c < chunk_first[f + 1]; c++, k++) {
+    const uint32_t rec = g_noalloc_records[c];
+    const uint64_t u0 = (uint64_t)k * kUnitsPerChunk;
+    const uint64_t nu = total_units - u0 < kUnitsPerChunk ? total_units - u0 : kUnitsPerChunk;
+    has_main |= rec_main(rec);
+    if (rec_lead(rec) == nu) { run += nu; continue; }  // no newline in this chunk
+    const uint64_t closed = run + rec_lead(rec);
+    if (closed >= kLongUnits && exact_long(u0 - run, closed)) is_long = 1;
+    run = rec_trail(rec);
+  }
+  if (run >= kLongUnits && exact_long(total_units - run, run)) is_long = 1;
+  file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0) | (is_long ? M2K_FILE_LONG_LINE : 0));
+}
+
+}  // namespace m2k
+
+using namespace m2k;
+
+// messages go where every other entry point's go: m2k_global_error()
+static int noalloc_fail(int code, const char* fmt, ...) {
+  char buf[320];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  set_global_error(buf);
+  return code;
+}
+
+extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d_bytes, const uint64_t* d_file_off,
+                                      const uint64_t* d_file_len, const uint32_t* d_chunk_first, uint32_t n_files,
+                                      uint32_t n_chunks, uint8_t* d_file_flags) {
+  if (device < 0 || device >= kMaxDevices || !d_bytes || !d_file_off || !d_file_len || !d_chunk_first || !d_file_flags)
+    return noalloc_fail(M2K_ERR_ARG, "m2k_scan_flags_noalloc: bad argument");
+  if (n_chunks > kNoAllocMaxChunks)
+    return noalloc_fail(M2K_ERR_LIMIT,
+                        "m2k_scan_flags_noalloc: %u chunks of 64 KiB exceed the built-in record table (%u chunks, 16 GiB of "
+                        "content): split the input or use m2k_scan", n_chunks, kNoAllocMaxChunks);
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  {
+    // set-up, once per device, with that device current
+    std::lock_guard<std::mutex> lock(g_setup_mutex);
+    if (!g_records_ptr[device]) {
+      uint32_t* ptr = nullptr;
+      e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_records);
+      if (e != cudaSuccess || !ptr)
+        return noalloc_fail(M2K_ERR_CUDA, "cudaGetSymbolAddress(record table) on device %d: %s", device, cudaGetErrorString(e));
+      int sms = 0;
+      e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+      if (e != cudaSuccess || sms <= 0)
+        return noalloc_fail(M2K_ERR_CUDA, "cudaDeviceGetAttribute(SM count) on device %d: %s", device, cudaGetErrorString(e));
+      g_sm_count[device] = sms;
+      g_records_ptr[device] = ptr;
+    }
+  }
+  if (n_files == 0) return M2K_OK;
+  // the existing scan kernel, pointed at the caller's buffers and at the built-in record table
+  Ctx c;
+  c.device = device;
+  c.stream = (cudaStream_t)stream;
+  c.sm_count = g_sm_count[device];
+  DevTree t;
+  t.n_files = n_files;
+  t.file_begin = 0;
+  t.file_end = n_files;
+  t.n_chunks = n_chunks;
+  t.chunk_first = const_cast<uint32_t*>(d_chunk_first);
+  t.file_off = const_cast<uint64_t*>(d_file_off);
+  t.file_len = const_cast<uint64_t*>(d_file_len);
+  t.bytes = const_cast<uint8_t*>(d_bytes);
+  t.shard_byte0 = 0;
+  launch_scan_bytes(&c, &t, g_records_ptr[device]);
+  k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, d_chunk_first, d_file_off, d_file_len, d_bytes, d_file_flags);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: kernel launch: %s", cudaGetErrorString(e));
+  return M2K_OK;
+}
