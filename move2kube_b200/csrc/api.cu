@@ -429,9 +429,19 @@ const uint8_t* host_file_bytes(const m2k_tree* t, uint32_t f, uint64_t* len) {
   return nullptr;
 }
 
+// one allocation: the pointer array followed by the characters (freed with a single free())
 char** dup_list(const std::vector<std::string>& v) {
-  char** out = static_cast<char**>(calloc(v.size() ? v.size() : 1, sizeof(char*)));
-  for (size_t i = 0; i < v.size(); i++) out[i] = strdup(v[i].c_str());
+  size_t chars = 0;
+  for (const auto& x : v) chars += x.size() + 1;
+  size_t head = (v.size() ? v.size() : 1) * sizeof(char*);
+  char** out = static_cast<char**>(malloc(head + chars + 1));
+  char* w = reinterpret_cast<char*>(out) + head;
+  out[0] = nullptr;
+  for (size_t i = 0; i < v.size(); i++) {
+    out[i] = w;
+    memcpy(w, v[i].c_str(), v[i].size() + 1);
+    w += v[i].size() + 1;
+  }
   return out;
 }
 
@@ -441,9 +451,7 @@ extern "C" void m2k_result_free(m2k_result* r) {
   if (!r) return;
   free(r->dir_opts); free(r->dir_direct); free(r->dir_subtree); free(r->dir_state); free(r->dir_ignore); free(r->dir_main_file);
   free(r->file_flags); free(r->service_dirs); free(r->entry_feat);
-  for (uint32_t i = 0; i < r->n_ignore_dirs; i++) free(r->ignore_dirs[i]);
-  for (uint32_t i = 0; i < r->n_ignore_contents; i++) free(r->ignore_contents[i]);
-  free(r->ignore_dirs); free(r->ignore_contents);
+  free(r->ignore_dirs); free(r->ignore_contents);  // each list is one block (dup_list)
   free(r);
 }
 

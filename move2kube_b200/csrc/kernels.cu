@@ -141,6 +141,36 @@ __device__ __noinline__ bool confirm_main(const uint8_t* file, uint64_t len, uin
   return false;
 }
 
+// First 16 bytes of a file (lane 0 of chunk 0): can the first instruction still be FROM?  Returns
+// true when it cannot -- the first word, read past blank lines, is neither a keyword of the
+// Dockerfile head (from / arg / env / label / onbuild) nor possibly continued -- so isDockerFile is
+// false without ever touching the file again.  Anything unusual (comment or directive, non-ASCII
+// byte, escape character, NUL, no verdict within 16 bytes) is left to k_df_head.
+__device__ __noinline__ bool first_word_rules_out_dockerfile(uint4 v) {
+  uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  int start = ((v.x & 0xFFFFFFu) == 0xBFBBEFu) ? 3 : 0;  // UTF-8 byte order mark
+  uint32_t alive = 0x1F, idx = 0;
+  bool in_word = false;
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    if (i < start) continue;
+    uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xFF;
+    bool ws = c == ' ' || (c >= 0x09 && c <= 0x0D);
+    if (!in_word) {
+      if (ws) continue;
+      if (c == 0 || c == '#' || c == '\\' || c >= 0x80) return false;
+      in_word = true;
+    } else {
+      if (ws) return df::kw_final(alive, idx) == 0;
+      if (c == 0 || c == '\\' || c >= 0x80) return false;
+    }
+    alive = df::kw_step(alive, idx, c);
+    idx++;
+    if (alive == 0) return true;
+  }
+  return false;
+}
+
 __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
     uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first,
     const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, uint32_t file_begin,
@@ -162,7 +192,7 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
     // Inside one 64 KiB chunk a newline-free run that is closed on both sides is shorter than 64 KiB,
     // so only the first and the last newline of the chunk matter: newlines are looked for until the
     // first one is found, and again in the last batch of rows.
-    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0;
+    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0, not_df = 0;
     for (uint32_t u0 = 0; u0 < n_units; u0 += 32 * kScanRows) {
       uint4 v[kScanRows];
 #pragma unroll
@@ -170,6 +200,7 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
         uint32_t u = u0 + r * 32 + lane;
         v[r] = u < n_units ? ldg_stream(src + u) : make_uint4(0, 0, 0, 0);
       }
+      if (start == 0 && u0 == 0 && lane == 0) not_df = first_word_rules_out_dockerfile(v[0]) ? 1u : 0u;
       const bool want_nl = lead == M2K_NONE || u0 + 32 * kScanRows >= n_units;  // warp-uniform
       bool hit_any = false;
 #pragma unroll
@@ -218,7 +249,7 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
       trail = n_units - 1 - last_nl;
     }
     const uint32_t q = trail;
-    if (lane == 0) chunk_rec[item] = rec_pack(lead, q, found);
+    if (lane == 0) chunk_rec[item] = rec_pack(lead, q, found) | (not_df << 27);
   }
 }
 
@@ -234,7 +265,8 @@ void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 3: per-file combine of the chunk records (one warp per file).  Produces HAS_MAIN and
+// Kernel 3: per-file combine of the chunk records (one thread per file; the whole warp for files of
+// more than 128 chunks).  Produces HAS_MAIN and
 // LONG_LINE, and the per-directory content partials for "__main__" in a file named *py.
 // ---------------------------------------------------------------------------------------------
 struct RunAcc {            // monoid over a span of 16-byte units
@@ -269,74 +301,109 @@ __device__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b, const uint8_t* fil
   return r;
 }
 
-__global__ void __launch_bounds__(256) k_file_combine(
-    uint32_t n_shard_files, uint32_t file_begin, const uint32_t* __restrict__ chunk_first, const uint32_t* __restrict__ chunk_rec,
-    const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, const uint8_t* __restrict__ bytes,
-    uint64_t shard_byte0, const uint32_t* __restrict__ file_entry, const uint32_t* __restrict__ entry_dir,
-    const uint32_t* __restrict__ entry_name_off, const uint8_t* __restrict__ names, uint8_t* __restrict__ file_flags,
-    uint32_t* __restrict__ dir_content, uint32_t* __restrict__ dir_main) {
-  uint32_t lane = threadIdx.x & 31;
-  uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (w >= n_shard_files) return;
-  uint32_t f = file_begin + w;
-  uint64_t len = file_len[f];
-  const uint8_t* file = bytes + (file_off[f] - shard_byte0);
-  uint32_t c0 = chunk_first[w], c1 = chunk_first[w + 1], nc = c1 - c0;
-  // each lane folds a contiguous slice of the records, then lane 0 folds the 32 partials
-  uint32_t per = (nc + 31) / 32;
-  uint32_t k0 = lane * per < nc ? lane * per : nc, k1 = (lane + 1) * per < nc ? (lane + 1) * per : nc;
+constexpr uint32_t kCombineWarpChunks = 128;  // files with more chunks are folded by the whole warp
+
+struct CombineArgs {
+  uint32_t n_shard_files, file_begin;
+  const uint32_t* chunk_first; const uint32_t* chunk_rec;
+  const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
+  const uint32_t* file_entry; const uint32_t* entry_dir; const uint32_t* entry_name_off; const uint8_t* names;
+  uint8_t* file_flags; uint32_t* dir_content; uint32_t* dir_main;
+};
+
+// fold records [k0, k1) of one file; *has_main / *not_df accumulate the flag bits
+__device__ __forceinline__ RunAcc fold_records(const CombineArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t total_units,
+                                               const uint8_t* file, uint64_t len, uint32_t* has_main, uint32_t* not_df) {
   RunAcc acc{0, 0, 0, 0};
-  uint32_t has_main = 0;
-  uint64_t total_units = (len + 15) >> 4;
-  uint64_t slice_start = (uint64_t)k0 * kUnitsPerChunk;
+  const uint64_t slice_start = (uint64_t)k0 * kUnitsPerChunk;
   for (uint32_t k = k0; k < k1; k++) {
-    uint32_t rec = chunk_rec[c0 + k];
+    uint32_t rec = a.chunk_rec[c0 + k];
     uint64_t ustart = (uint64_t)k * kUnitsPerChunk;
     uint64_t nu = total_units - ustart < kUnitsPerChunk ? total_units - ustart : kUnitsPerChunk;
     RunAcc b{nu, rec_lead(rec), rec_trail(rec), 0};
-    has_main |= rec_main(rec);
+    *has_main |= rec_main(rec);
+    *not_df |= (rec >> 27) & 1u;
     acc = acc_merge(acc, b, file, len, slice_start);
   }
-  has_main = __any_sync(FULL, has_main);
-  RunAcc tot{0, 0, 0, 0};
-  uint64_t tot_start = 0;
-  for (int l = 0; l < 32; l++) {
-    RunAcc b;
-    b.units = __shfl_sync(FULL, acc.units, l);
-    b.lead = __shfl_sync(FULL, acc.lead, l);
-    b.trail = __shfl_sync(FULL, acc.trail, l);
-    b.longf = __shfl_sync(FULL, acc.longf, l);
-    if (lane == 0) tot = acc_merge(tot, b, file, len, tot_start);
+  return acc;
+}
+
+__device__ __forceinline__ void finish_file(const CombineArgs& a, uint32_t f, const RunAcc& tot, const uint8_t* file, uint64_t len,
+                                            uint32_t has_main, uint32_t not_df) {
+  uint32_t longf = tot.longf;
+  if (!longf && tot.units) {
+    bool all_free = tot.lead == tot.units;
+    // runs open toward the file start / end
+    if (tot.lead >= kLongUnits && run_is_long(file, len, 0, tot.lead)) longf = 1;
+    if (!all_free && tot.trail >= kLongUnits && run_is_long(file, len, tot.units - tot.trail, tot.trail)) longf = 1;
   }
-  if (lane == 0) {
-    uint32_t longf = tot.longf;
-    if (!longf && tot.units) {
-      bool all_free = tot.lead == tot.units;
-      // runs open toward the file start / end
-      if (tot.lead >= kLongUnits && run_is_long(file, len, 0, tot.lead)) longf = 1;
-      if (!all_free && tot.trail >= kLongUnits && run_is_long(file, len, tot.units - tot.trail, tot.trail)) longf = 1;
+  // bit 7 is internal: "the first word already rules out a Dockerfile" (cleared again by k_df_head)
+  a.file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0) | (longf ? M2K_FILE_LONG_LINE : 0) | (not_df ? 0x80 : 0));
+  if (has_main) {
+    uint32_t e = a.file_entry[f];
+    uint32_t off = a.entry_name_off[e], nl = a.entry_name_off[e + 1] - off;
+    if (nl >= 2 && a.names[off + nl - 2] == 'p' && a.names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
+      uint32_t d = a.entry_dir[e];
+      atomicOr(&a.dir_content[d], 1u << M2K_C_MAIN_PY);
+      atomicMin(&a.dir_main[d], f);
     }
-    uint32_t flags = (has_main ? M2K_FILE_HAS_MAIN : 0) | (longf ? M2K_FILE_LONG_LINE : 0);
-    file_flags[f] = (uint8_t)flags;
-    if (has_main) {
-      uint32_t e = file_entry[f];
-      uint32_t off = entry_name_off[e], nl = entry_name_off[e + 1] - off;
-      if (nl >= 2 && names[off + nl - 2] == 'p' && names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
-        uint32_t d = entry_dir[e];
-        atomicOr(&dir_content[d], 1u << M2K_C_MAIN_PY);
-        atomicMin(&dir_main[d], f);
-      }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_file_combine(CombineArgs a) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = i < a.n_shard_files;
+  uint32_t f = 0, c0 = 0, nc = 0;
+  uint64_t len = 0;
+  const uint8_t* file = nullptr;
+  if (valid) {
+    f = a.file_begin + i;
+    len = a.file_len[f];
+    file = a.bytes + (a.file_off[f] - a.shard_byte0);
+    c0 = a.chunk_first[i];
+    nc = a.chunk_first[i + 1] - c0;
+  }
+  const uint64_t total_units = (len + 15) >> 4;
+  if (valid && nc <= kCombineWarpChunks) {  // the common case: one thread, a handful of records
+    uint32_t has_main = 0, not_df = 0;
+    RunAcc tot = fold_records(a, c0, 0, nc, total_units, file, len, &has_main, &not_df);
+    finish_file(a, f, tot, file, len, has_main, not_df);
+  }
+  // files with many chunks (config D's multi-GiB files): the warp folds them together, one at a time
+  uint32_t big = __ballot_sync(FULL, valid && nc > kCombineWarpChunks);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const uint32_t bf = __shfl_sync(FULL, f, src), bc0 = __shfl_sync(FULL, c0, src), bnc = __shfl_sync(FULL, nc, src);
+    const uint64_t blen = __shfl_sync(FULL, len, src);
+    const uint8_t* bfile = reinterpret_cast<const uint8_t*>(__shfl_sync(FULL, reinterpret_cast<unsigned long long>(file), src));
+    const uint64_t bunits = (blen + 15) >> 4;
+    const uint32_t per = (bnc + 31) / 32;
+    const uint32_t k0 = lane * per < bnc ? lane * per : bnc, k1 = (lane + 1) * per < bnc ? (lane + 1) * per : bnc;
+    uint32_t has_main = 0, not_df = 0;
+    RunAcc acc = fold_records(a, bc0, k0, k1, bunits, bfile, blen, &has_main, &not_df);
+    has_main = __any_sync(FULL, has_main);
+    not_df = __any_sync(FULL, not_df);
+    RunAcc tot{0, 0, 0, 0};
+    for (int l = 0; l < 32; l++) {
+      RunAcc b;
+      b.units = __shfl_sync(FULL, acc.units, l);
+      b.lead = __shfl_sync(FULL, acc.lead, l);
+      b.trail = __shfl_sync(FULL, acc.trail, l);
+      b.longf = __shfl_sync(FULL, acc.longf, l);
+      if (lane == 0) tot = acc_merge(tot, b, bfile, blen, 0);
     }
+    if (lane == 0) finish_file(a, bf, tot, bfile, blen, has_main, not_df);
   }
 }
 
 void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec) {
   uint32_t nf = t->file_end - t->file_begin;
   if (!nf) return;
-  uint32_t blocks = (nf + 7) / 8;
-  k_file_combine<<<blocks, 256, 0, c->stream>>>(nf, t->file_begin, t->chunk_first, chunk_rec, t->file_off, t->file_len, t->bytes,
-                                                t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
-                                                t->file_flags, t->dir_content, t->dir_main);
+  CombineArgs a{nf, t->file_begin, t->chunk_first, chunk_rec, t->file_off, t->file_len, t->bytes, t->shard_byte0,
+                t->file_entry, t->entry_dir, t->entry_name_off, t->names, t->file_flags, t->dir_content, t->dir_main};
+  k_file_combine<<<(nf + 255) / 256, 256, 0, c->stream>>>(a);
   c->launches++;
 }
 
@@ -373,6 +440,7 @@ __global__ void __launch_bounds__(128) k_df_head(DfArgs a) {
   if (i >= a.n_shard_files) return;
   uint32_t f = a.file_begin + i;
   uint32_t flags = a.file_flags[f];
+  if (flags & 0x80) { a.file_flags[f] = (uint8_t)(flags & 0x7F); return; }  // ruled out by the scan kernel (first word)
   uint64_t body = 0, n = a.file_len[f];
   uint32_t esc = '\\';
   if (!df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n, (flags & M2K_FILE_LONG_LINE) != 0, &body, &esc)) return;
@@ -568,11 +636,11 @@ void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 7: the walk (any2kube.go:58-98), top-down one level per launch.  Per directory: extend the
-// parent's case-folded path hash by "/name", probe the ignore table (an exact hash join in place of
-// O(#dirs x #entries) EqualFold scans, utils.go:308-315), then apply the walk's rules given whether
-// the parent was visited and descended into.  A hash hit is confirmed rune by rune against the
-// folded entry (walking up the parent chain), so 64-bit collisions cannot change a decision.
+// Kernel 7: the walk (any2kube.go:58-98) in two launches.  k_walk_local: per directory, the
+// case-folded hash of its path, a probe of the ignore table (an exact hash join in place of
+// O(#dirs x #entries) EqualFold scans, utils.go:308-315; a hash hit is confirmed rune by rune against
+// the folded entry, so 64-bit collisions cannot change a decision) and the walk's local rule.
+// k_walk_reach: a directory is visited iff the walk descends below all of its ancestors.
 // ---------------------------------------------------------------------------------------------
 struct WalkArgs {
   const uint32_t* dir_parent; const uint32_t* dir_entry; const uint8_t* dir_flags;
@@ -615,36 +683,52 @@ __device__ bool path_equals_entry(const WalkArgs& a, uint32_t d, const uint32_t*
   return true;
 }
 
-__global__ void k_walk_level(const uint32_t* __restrict__ level_dirs, uint32_t n, uint32_t level, WalkArgs a) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint32_t d = level_dirs[i];
+constexpr uint32_t kChainMax = 64;
+
+// folded hash of "/name" appended to h (or of "name" right after the shared prefix)
+__device__ __forceinline__ uint64_t hash_dir_name(const WalkArgs& a, uint64_t h, uint32_t d, bool first) {
+  if (!first) h = hash_step(h, '/');
+  uint32_t e = a.dir_entry[d];
+  uint32_t off = a.entry_name_off[e];
+  return hash_fold_bytes(h, a.names + off, a.entry_name_off[e + 1] - off, a.fold_from, a.fold_to, M2K_CASEFOLD_N);
+}
+
+// Step 1, one thread per directory, no dependency between directories: the case-folded hash of the
+// directory's own path (hashing down its ancestor chain), the ignore-table probe with exact
+// confirmation, and the walk's LOCAL rule -- what any2kube.go:58-98 does with this directory if it
+// is reached, and whether the walk would descend below it.
+__global__ void __launch_bounds__(128) k_walk_local(uint32_t n_dirs, const uint32_t* __restrict__ dir_depth, WalkArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs) return;
   uint32_t ign = 0;
-  bool visited;
-  if (level == 0) {
+  if (d == 0) {
     ign = a.root_ignore;  // the root path is compared on the host exactly as given
-    visited = true;
-  } else {
-    uint32_t p = a.dir_parent[d];
-    uint64_t h = (level == 1) ? a.depth1_state : hash_step(a.dir_hash[p], '/');
-    uint32_t e = a.dir_entry[d];
-    uint32_t off = a.entry_name_off[e], len = a.entry_name_off[e + 1] - off;
-    h = hash_fold_bytes(h, a.names + off, len, a.fold_from, a.fold_to, M2K_CASEFOLD_N);
-    a.dir_hash[d] = h;
-    if (a.table_mask != M2K_NONE) {
-      uint64_t key = hash_finish(h);
-      for (uint32_t s = (uint32_t)key & a.table_mask;; s = (s + 1) & a.table_mask) {
-        IgnoreSlot sl = a.table[s];
-        if (sl.hash == 0) break;
-        if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, sl.len)) { ign = sl.flags; break; }
+  } else if (a.table_mask != M2K_NONE) {
+    const uint32_t depth = dir_depth[d];
+    uint64_t h = a.depth1_state;
+    if (depth <= kChainMax) {
+      uint32_t chain[kChainMax];
+      uint32_t x = d;
+      for (uint32_t i = depth; i-- > 0;) { chain[i] = x; x = a.dir_parent[x]; }
+      for (uint32_t i = 0; i < depth; i++) h = hash_dir_name(a, h, chain[i], i == 0);
+    } else {
+      // very deep paths: find the ancestor of each level by walking up again (quadratic, but only here)
+      for (uint32_t lvl = 1; lvl <= depth; lvl++) {
+        uint32_t x = d;
+        for (uint32_t up = depth - lvl; up > 0; up--) x = a.dir_parent[x];
+        h = hash_dir_name(a, h, x, lvl == 1);
       }
     }
-    visited = a.dir_state[p] != M2K_DIR_NOT_VISITED && a.dir_descend[p];
+    uint64_t key = hash_finish(h);
+    for (uint32_t s = (uint32_t)key & a.table_mask;; s = (s + 1) & a.table_mask) {
+      IgnoreSlot sl = a.table[s];
+      if (sl.hash == 0) break;
+      if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, sl.len)) { ign = sl.flags; break; }
+    }
   }
   a.dir_ignore[d] = (uint8_t)ign;
   uint32_t state, descend = 0;
-  if (!visited) state = M2K_DIR_NOT_VISITED;
-  else if (a.dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
+  if (a.dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
   else if (ign & 4) state = M2K_DIR_PRECONTAINERIZED;
   else if (ign & 1) { if (ign & 2) state = M2K_DIR_IGNORED_PRUNE; else { state = M2K_DIR_IGNORED_DESCEND; descend = 1; } }
   else if (a.dir_opts[d] == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
@@ -653,17 +737,26 @@ __global__ void k_walk_level(const uint32_t* __restrict__ level_dirs, uint32_t n
   a.dir_descend[d] = (uint8_t)descend;
 }
 
+// Step 2: a directory is reached iff the walk descends below every one of its ancestors.
+__global__ void __launch_bounds__(128) k_walk_reach(uint32_t n_dirs, WalkArgs a) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs || d == 0) return;
+  for (uint32_t x = a.dir_parent[d];; x = a.dir_parent[x]) {
+    if (!a.dir_descend[x]) { a.dir_state[d] = M2K_DIR_NOT_VISITED; return; }
+    if (x == 0) return;
+  }
+}
+
 void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
                  const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore) {
+  if (!t->n_dirs) return;
   WalkArgs a{t->dir_parent, t->dir_entry, t->dir_flags, t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to,
              table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore, t->dir_opts,
              t->dir_hash, t->dir_ignore, t->dir_state, t->dir_descend};
-  for (uint32_t L = 0; L <= t->max_depth && t->n_dirs; L++) {
-    uint32_t lo = t->level_off[L], hi = t->level_off[L + 1];
-    if (hi <= lo) continue;
-    k_walk_level<<<(hi - lo + 127) / 128, 128, 0, c->stream>>>(t->level_dirs + lo, hi - lo, L, a);
-    c->launches++;
-  }
+  uint32_t blocks = (t->n_dirs + 127) / 128;
+  k_walk_local<<<blocks, 128, 0, c->stream>>>(t->n_dirs, t->dir_depth, a);
+  k_walk_reach<<<blocks, 128, 0, c->stream>>>(t->n_dirs, a);
+  c->launches += 2;
 }
 
 // ---------------------------------------------------------------------------------------------

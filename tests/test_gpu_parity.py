@@ -240,3 +240,30 @@ def test_names_only_mode(ctx, oracle, tmp_path):
     assert not any(res.contents.file_flags[0:res.contents.n_files])
     ctx.result_free(res)
     ctx.tree_free(tree)
+
+
+def test_very_deep_tree(ctx, oracle, tmp_path):
+    """Paths deeper than the walk kernel's in-register ancestor chain (64) take its slow branch."""
+    root = tmp_path / "deep"
+    p = root
+    rel = []
+    for i in range(90):
+        name = "d%d" % (i % 7)
+        p = p / name
+        rel.append(name)
+    p.mkdir(parents=True)
+    (p / "package.json").write_text("{}")
+    (root / ".m2kignore").write_text(".\n" + "/".join(rel[:70]) + "/\n" + "/".join(rel[:75]).upper() + "/\n"
+                                     + "/".join(rel[:80]) + "/*\n")
+    (root.joinpath(*rel[:72]) / "main.go").write_text("package main\n")
+    broot = os.fsencode(str(root))
+    tree = ctx.pack_tree(broot)
+    res = ctx.detect(tree)
+    ores = oracle.detect(tree)
+    compare_with_oracle(oracle, tree, res, ores)
+    r = res.contents
+    states = r.dir_state[0:r.n_dirs]
+    assert states.count(_abi.DIR_IGNORED_DESCEND) == 3 and r.n_services == 1 and _abi.DIR_NOT_VISITED in states
+    oracle.lib().m2ko_result_free(ores)
+    ctx.result_free(res)
+    ctx.tree_free(tree)
