@@ -205,7 +205,7 @@ static void devtree_release(DevTree* t) {
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
                   t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
                   t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
-                  t->cand_esc, t->stripe_state};
+                  t->cand_esc, t->stripe_state, t->ign_blob};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -555,7 +555,14 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
       table[sidx] = IgnoreSlot{en.key, en.flags, en.off, en.len, 0};
     }
     size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
-    CU(cudaMalloc(&d_blob, tb + rb + pb + 16));
+    if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
+      if (t->ign_blob) CU(cudaFree(t->ign_blob));
+      t->ign_blob = nullptr; t->ign_blob_cap = 0;
+      size_t want = (tb + rb + pb + 16) * 2;
+      CU(cudaMalloc(&t->ign_blob, want));
+      t->ign_blob_cap = want;
+    }
+    d_blob = t->ign_blob;
     CU(cudaMemcpyAsync(d_blob, table.data(), tb, cudaMemcpyHostToDevice, s));
     if (rb) CU(cudaMemcpyAsync((char*)d_blob + tb, runes.data(), rb, cudaMemcpyHostToDevice, s));
     if (pb) CU(cudaMemcpyAsync((char*)d_blob + tb + rb, prefix_runes.data(), pb, cudaMemcpyHostToDevice, s));
@@ -577,7 +584,6 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);
-  if (d_blob) cudaFree(d_blob);
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "walk kernels failed: %s", cudaGetErrorString(werr));
   if (int rc = collect_scan_timings(C, dt)) return rc;
   float ms_k1 = 0, ms_k2 = 0, ms_d = 0;

@@ -252,10 +252,9 @@ def test_very_deep_tree(ctx, oracle, tmp_path):
         p = p / name
         rel.append(name)
     p.mkdir(parents=True)
-    (p / "package.json").write_text("{}")
+    (root.joinpath(*rel[:83]) / "package.json").write_text("{}")
     (root / ".m2kignore").write_text(".\n" + "/".join(rel[:70]) + "/\n" + "/".join(rel[:75]).upper() + "/\n"
-                                     + "/".join(rel[:80]) + "/*\n")
-    (root.joinpath(*rel[:72]) / "main.go").write_text("package main\n")
+                                     + "/".join(rel[:86]) + "/*\n")
     broot = os.fsencode(str(root))
     tree = ctx.pack_tree(broot)
     res = ctx.detect(tree)
