@@ -216,6 +216,10 @@ int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
 int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_dst_content, uint32_t* d_dst_main);
 /* OR / MIN `n_ranks` gathered partial arrays (device memory, rank-major) into this shard's own */
 int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks);
+/* optional, between m2k_scan and m2k_finalize: the host half of getIgnorePaths (any2kube.go:151-181) --
+ * parse the .m2kignore files the name kernel found and upload the lookup table -- while the byte scan
+ * is still running on the GPU.  m2k_finalize does it itself when this was not called. */
+int m2k_prepare(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
 /* phase C: subtree OR, predicate combine, ignore join, prune; copies results to the host */
 int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params, m2k_result** out);
 void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt);

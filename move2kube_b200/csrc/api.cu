@@ -5,7 +5,9 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <thread>
 #include <unordered_map>
 
 #include "casefold_table.h"
@@ -15,7 +17,30 @@
 using namespace m2k;
 
 struct m2k_ctx { Ctx c; };
-struct m2k_devtree { DevTree t; float ms_h2d = 0.f; uint32_t* h_entry_feat = nullptr; bool content = true; };
+constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2kignore, user detect scripts) listed by the device
+
+// what m2k_prepare / m2k_finalize derive from the .m2kignore files (host side of a2 / a4)
+struct IgnorePrep {
+  bool ready = false;
+  std::vector<std::string> ign_dirs, ign_contents;
+  std::vector<IgnoreSlot> table;
+  std::vector<uint32_t> runes, prefix_runes;
+  uint32_t table_mask = M2K_NONE, prefix_len = 0;
+  uint64_t depth1_state = 0;
+  uint8_t root_ignore = 0;
+  const IgnoreSlot* d_table = nullptr;
+  const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
+  float ms_host = 0.f;
+};
+
+struct m2k_devtree {
+  DevTree t;
+  float ms_h2d = 0.f;
+  uint32_t* h_entry_feat = nullptr;  // pinned
+  uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
+  bool content = true;
+  IgnorePrep prep;
+};
 
 static thread_local std::string g_err;
 
@@ -205,7 +230,7 @@ static void devtree_release(DevTree* t) {
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
                   t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
                   t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
-                  t->cand_esc, t->stripe_state, t->ign_blob};
+                  t->cand_esc, t->stripe_state, t->ign_blob, t->special};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -214,6 +239,7 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); }
   devtree_release(&dt->t);
   if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
+  if (dt->h_special) cudaFreeHost(dt->h_special);
   delete dt;
 }
 
@@ -228,7 +254,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
   DevTree* t = &dt->t;
-  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); delete d; } } } guard{dt};
+  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); if (d->h_special) cudaFreeHost(d->h_special); delete d; } } } guard{dt};
   t->host = tree;
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
   t->file_begin = file_begin; t->file_end = file_end;
@@ -281,6 +307,9 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd)); CU(dev_alloc(&t->file_flags, nf));
 
   CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
+  CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
+  CU(dev_alloc(&t->special, (size_t)kSpecialCap + 1));
+  t->special_cap = kSpecialCap;
   cudaStream_t s = C->stream;
   CU(cudaEventRecord(C->ev[0], s));
   auto H2D = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess; };
@@ -343,9 +372,12 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_main, 0xFF, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->file_flags, 0, t->n_files, s));
+  CU(cudaMemsetAsync(t->special, 0, 4, s));
+  dt->prep.ready = false;
   CU(cudaEventRecord(C->ev[8], s));
   launch_name_features(C, t);
   // the host needs the name features (which entries are .m2kignore files) while the byte scan runs
+  CU(cudaMemcpyAsync(dt->h_special, t->special, 4ull * (kSpecialCap + 1), cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[2], s));
   dt->content = content;
@@ -455,6 +487,156 @@ extern "C" void m2k_result_free(m2k_result* r) {
   free(r);
 }
 
+// getIgnorePaths (any2kube.go:151-181) + the lookup structure of IsStringPresent (utils.go:308-315):
+// host work that needs only the name features, so it runs while the byte scan is still on the GPU.
+static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* params) {
+  DevTree* t = &dt->t;
+  IgnorePrep& P = dt->prep;
+  const m2k_tree* tree = t->host;
+  cudaStream_t s = C->stream;
+  CU(cudaEventSynchronize(C->ev[2]));  // name features and the special-entry list are on the host now
+  double h0 = now_ms();
+  P = IgnorePrep();
+  const std::string root = tree->root_path ? tree->root_path : "";
+  const std::string clean_root = path_clean(root);
+  // the .m2kignore files: from the compacted list of special entries, or a scan of all features if it overflowed
+  std::vector<uint32_t> ign_entries;
+  const uint32_t n_special = dt->h_special[0];
+  if (n_special <= kSpecialCap) {
+    for (uint32_t i = 0; i < n_special; i++) {
+      uint32_t e = dt->h_special[1 + i];
+      if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
+    }
+  } else {
+    for (uint32_t e = 0; e < t->n_entries; e++) if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
+  }
+  // filepath.Walk order: compare the chains of entry indices from the root down
+  const size_t nfiles = ign_entries.size();
+  std::vector<std::vector<uint32_t>> chains(nfiles);
+  for (size_t i = 0; i < nfiles; i++) {
+    for (uint32_t e = ign_entries[i];;) {
+      chains[i].push_back(e);
+      uint32_t d = tree->entry_dir[e];
+      if (d == 0) break;
+      e = tree->dir_entry[d];
+    }
+    std::reverse(chains[i].begin(), chains[i].end());
+  }
+  std::vector<uint32_t> order(nfiles);
+  for (size_t i = 0; i < nfiles; i++) order[i] = (uint32_t)i;
+  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return chains[x] < chains[y]; });
+  // parse the files in parallel (each is independent), keep Walk order when concatenating
+  struct Parsed { std::vector<std::string> dirs, contents; bool missing = false; };
+  std::vector<Parsed> parsed(nfiles);
+  {
+    unsigned nt = std::thread::hardware_concurrency();
+    if (nt == 0) nt = 4;
+    if (nt > 16) nt = 16;
+    if (nt > nfiles / 64 + 1) nt = (unsigned)(nfiles / 64 + 1);
+    std::atomic<size_t> next{0};
+    auto worker = [&]() {
+      for (;;) {
+        size_t k = next.fetch_add(1);
+        if (k >= nfiles) break;
+        uint32_t e = ign_entries[order[k]];
+        uint32_t f = tree->entry_child[e];
+        if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
+        uint64_t len;
+        const uint8_t* data = host_file_bytes(tree, f, &len);
+        if (!data) { parsed[k].missing = len != 0; continue; }
+        uint32_t d = tree->entry_dir[e];
+        std::string fpath = path_join(d == 0 ? root : fast_dir_path(tree, d, clean_root), ".m2kignore");
+        parse_ignore_file(fpath, data, len, &parsed[k].dirs, &parsed[k].contents);
+      }
+    };
+    std::vector<std::thread> th;
+    for (unsigned i = 1; i < nt; i++) th.emplace_back(worker);
+    worker();
+    for (auto& x : th) x.join();
+  }
+  for (size_t k = 0; k < nfiles; k++) {
+    if (parsed[k].missing) return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
+    for (auto& x : parsed[k].dirs) P.ign_dirs.push_back(std::move(x));
+    for (auto& x : parsed[k].contents) P.ign_contents.push_back(std::move(x));
+  }
+  // exact hash table over the case-folded entries, keyed by the folded rune sequence;
+  // flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
+  std::vector<std::string> pre;
+  for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
+  const uint64_t seed0 = 0xcbf29ce484222325ull;
+  struct Ent { uint64_t key; uint32_t flags, off, len; };
+  std::vector<Ent> ents;
+  std::vector<uint32_t> runes, tmp, root_runes;
+  std::unordered_map<uint64_t, std::vector<uint32_t>> by_key;  // key -> indices into ents (collisions share a key)
+  by_key.reserve(P.ign_dirs.size() + P.ign_contents.size() + pre.size());
+  fold_runes(root, &root_runes);
+  auto add = [&](const std::string& sp, uint32_t flag) {
+    fold_runes(sp, &tmp);
+    if (tmp == root_runes) P.root_ignore |= (uint8_t)flag;
+    uint64_t h = seed0;
+    for (uint32_t rr : tmp) h = hash_step(h, rr);
+    uint64_t key = hash_finish(h);
+    auto& lst = by_key[key];
+    for (uint32_t idx : lst) {
+      const Ent& en = ents[idx];
+      if (en.len == tmp.size() && std::equal(tmp.begin(), tmp.end(), runes.begin() + en.off)) { ents[idx].flags |= flag; return; }
+    }
+    lst.push_back((uint32_t)ents.size());
+    ents.push_back({key, flag, (uint32_t)runes.size(), (uint32_t)tmp.size()});
+    runes.insert(runes.end(), tmp.begin(), tmp.end());
+  };
+  for (const auto& x : P.ign_dirs) add(x, 1);
+  for (const auto& x : P.ign_contents) add(x, 2);
+  for (const auto& x : pre) add(x, 4);
+  // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
+  std::string prefix1 = clean_root;
+  if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
+  std::vector<uint32_t> prefix_runes;
+  fold_runes(prefix1, &prefix_runes);
+  P.depth1_state = seed0;
+  for (uint32_t rr : prefix_runes) P.depth1_state = hash_step(P.depth1_state, rr);
+  P.prefix_len = (uint32_t)prefix_runes.size();
+  if (!ents.empty()) {
+    uint32_t cap = 16;
+    while (cap < ents.size() * 2) cap <<= 1;
+    P.table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
+    P.table_mask = cap - 1;
+    for (const Ent& en : ents) {
+      uint32_t sidx = (uint32_t)en.key & P.table_mask;
+      while (P.table[sidx].hash) sidx = (sidx + 1) & P.table_mask;
+      P.table[sidx] = IgnoreSlot{en.key, en.flags, en.off, en.len, 0};
+    }
+    size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
+    if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
+      if (t->ign_blob) CU(cudaFree(t->ign_blob));
+      t->ign_blob = nullptr; t->ign_blob_cap = 0;
+      size_t want = (tb + rb + pb + 16) * 2;
+      CU(cudaMalloc(&t->ign_blob, want));
+      t->ign_blob_cap = want;
+    }
+    // staged through vectors that live in the prep until finalize has synchronised
+    P.runes.swap(runes);
+    P.prefix_runes.swap(prefix_runes);
+    CU(cudaMemcpyAsync(t->ign_blob, P.table.data(), tb, cudaMemcpyHostToDevice, s));
+    if (rb) CU(cudaMemcpyAsync((char*)t->ign_blob + tb, P.runes.data(), rb, cudaMemcpyHostToDevice, s));
+    if (pb) CU(cudaMemcpyAsync((char*)t->ign_blob + tb + rb, P.prefix_runes.data(), pb, cudaMemcpyHostToDevice, s));
+    P.d_table = (const IgnoreSlot*)t->ign_blob;
+    P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
+    P.d_prefix = (const uint32_t*)((char*)t->ign_blob + tb + rb);
+  }
+  P.ms_host = (float)(now_ms() - h0);
+  P.ready = true;
+  return M2K_OK;
+}
+
+extern "C" int m2k_prepare(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  if (!dt->t.scanned) return fail(C, M2K_ERR_ARG, "m2k_prepare before m2k_scan");
+  CU(cudaSetDevice(C->device));
+  return prepare_ignore(C, dt, params);
+}
+
 extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params, m2k_result** out) {
   if (!ctx || !dt || !out) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
   Ctx* C = &ctx->c;
@@ -463,7 +645,6 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   if (!t->scanned) return fail(C, M2K_ERR_ARG, "m2k_finalize before m2k_scan");
   CU(cudaSetDevice(C->device));
   cudaStream_t s = C->stream;
-  const m2k_tree* tree = t->host;
   const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
   const uint32_t sh = params ? params->sh_flavor : M2K_SH_BASH;
   m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
@@ -479,101 +660,13 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   launch_subtree(C, t);
   launch_combine_opts(C, t, sh);
   CU(cudaEventRecord(C->ev[7], s));
-  CU(cudaEventSynchronize(C->ev[2]));  // name features are on the host; the byte scan may still be running
+  if (!dt->prep.ready) { if (int rc = prepare_ignore(C, dt, params)) return rc; }
+  IgnorePrep& P = dt->prep;
   memcpy(r->entry_feat, dt->h_entry_feat, 4ull * ne);
-
-  // getIgnorePaths (any2kube.go:151-181): the .m2kignore files come from the name-feature bit
-  double h0 = now_ms();
-  const std::string root = tree->root_path ? tree->root_path : "";
-  const std::string clean_root = path_clean(root);
-  std::vector<uint32_t> ign_entries;
-  for (uint32_t e = 0; e < ne; e++) if (r->entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
-  std::sort(ign_entries.begin(), ign_entries.end(), [&](uint32_t a, uint32_t b) { return walk_before(tree, a, b); });
-  std::vector<std::string> ign_dirs, ign_contents;
-  for (uint32_t e : ign_entries) {
-    uint32_t f = tree->entry_child[e];
-    if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
-    uint64_t len;
-    const uint8_t* data = host_file_bytes(tree, f, &len);
-    if (!data) {
-      if (len == 0) continue;
-      return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
-    }
-    uint32_t d = tree->entry_dir[e];
-    std::string fpath = path_join(d == 0 ? root : fast_dir_path(tree, d, clean_root), ".m2kignore");
-    parse_ignore_file(fpath, data, len, &ign_dirs, &ign_contents);
-  }
-  // exact hash table over the case-folded entries, keyed by the folded rune sequence;
-  // flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
-  uint8_t root_ignore = 0;
-  std::vector<std::string> pre;
-  for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
-  const uint64_t seed0 = 0xcbf29ce484222325ull;
-  struct Ent { uint64_t key; uint32_t flags, off, len; };
-  std::vector<Ent> ents;
-  std::vector<uint32_t> runes, tmp, root_runes;
-  std::unordered_map<uint64_t, std::vector<uint32_t>> by_key;  // key -> indices into ents (collisions share a key)
-  fold_runes(root, &root_runes);
-  auto add = [&](const std::string& sp, uint32_t flag) {
-    fold_runes(sp, &tmp);
-    if (tmp == root_runes) root_ignore |= (uint8_t)flag;
-    uint64_t h = seed0;
-    for (uint32_t rr : tmp) h = hash_step(h, rr);
-    uint64_t key = hash_finish(h);
-    auto& lst = by_key[key];
-    for (uint32_t idx : lst) {
-      const Ent& en = ents[idx];
-      if (en.len == tmp.size() && std::equal(tmp.begin(), tmp.end(), runes.begin() + en.off)) { ents[idx].flags |= flag; return; }
-    }
-    lst.push_back((uint32_t)ents.size());
-    ents.push_back({key, flag, (uint32_t)runes.size(), (uint32_t)tmp.size()});
-    runes.insert(runes.end(), tmp.begin(), tmp.end());
-  };
-  for (const auto& x : ign_dirs) add(x, 1);
-  for (const auto& x : ign_contents) add(x, 2);
-  for (const auto& x : pre) add(x, 4);
-  // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
-  std::string prefix1 = clean_root;
-  if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
-  std::vector<uint32_t> prefix_runes;
-  fold_runes(prefix1, &prefix_runes);
-  uint64_t depth1_state = seed0;
-  for (uint32_t rr : prefix_runes) depth1_state = hash_step(depth1_state, rr);
-  std::vector<IgnoreSlot> table;
-  uint32_t table_mask = M2K_NONE;
-  void* d_blob = nullptr;  // [table | entry runes | prefix runes] in one allocation
-  const IgnoreSlot* d_table = nullptr;
-  const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
-  if (!ents.empty()) {
-    uint32_t cap = 16;
-    while (cap < ents.size() * 2) cap <<= 1;
-    table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
-    table_mask = cap - 1;
-    for (const Ent& en : ents) {
-      uint32_t sidx = (uint32_t)en.key & table_mask;
-      while (table[sidx].hash) sidx = (sidx + 1) & table_mask;
-      table[sidx] = IgnoreSlot{en.key, en.flags, en.off, en.len, 0};
-    }
-    size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
-    if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
-      if (t->ign_blob) CU(cudaFree(t->ign_blob));
-      t->ign_blob = nullptr; t->ign_blob_cap = 0;
-      size_t want = (tb + rb + pb + 16) * 2;
-      CU(cudaMalloc(&t->ign_blob, want));
-      t->ign_blob_cap = want;
-    }
-    d_blob = t->ign_blob;
-    CU(cudaMemcpyAsync(d_blob, table.data(), tb, cudaMemcpyHostToDevice, s));
-    if (rb) CU(cudaMemcpyAsync((char*)d_blob + tb, runes.data(), rb, cudaMemcpyHostToDevice, s));
-    if (pb) CU(cudaMemcpyAsync((char*)d_blob + tb + rb, prefix_runes.data(), pb, cudaMemcpyHostToDevice, s));
-    d_table = (const IgnoreSlot*)d_blob;
-    d_runes = (const uint32_t*)((char*)d_blob + tb);
-    d_prefix = (const uint32_t*)((char*)d_blob + tb + rb);
-  }
-  r->ms_host_ignore = (float)(now_ms() - h0);
+  r->ms_host_ignore = P.ms_host;
 
   CU(cudaEventRecord(C->ev[11], s));
-  launch_walk(C, t, d_table, table_mask, d_runes, d_prefix, (uint32_t)prefix_runes.size(), depth1_state, root_ignore);
+  launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore);
   CU(cudaEventRecord(C->ev[5], s));
   CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, s));
@@ -584,7 +677,7 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, s));
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);
-  if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "walk kernels failed: %s", cudaGetErrorString(werr));
+  if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "detection kernels failed: %s", cudaGetErrorString(werr));
   if (int rc = collect_scan_timings(C, dt)) return rc;
   float ms_k1 = 0, ms_k2 = 0, ms_d = 0;
   CU(cudaEventElapsedTime(&ms_k1, C->ev[4], C->ev[7]));
@@ -595,9 +688,10 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   double v0 = now_ms();
   for (uint32_t d = 0; d < nd; d++)
     if (r->dir_state[d] == M2K_DIR_SERVICE) r->service_dirs[r->n_services++] = d;
+  r->n_ignore_dirs = (uint32_t)P.ign_dirs.size(); r->ignore_dirs = dup_list(P.ign_dirs);
+  r->n_ignore_contents = (uint32_t)P.ign_contents.size(); r->ignore_contents = dup_list(P.ign_contents);
   C->phase_ms[6] = (float)(now_ms() - v0);
-  r->n_ignore_dirs = (uint32_t)ign_dirs.size(); r->ignore_dirs = dup_list(ign_dirs);
-  r->n_ignore_contents = (uint32_t)ign_contents.size(); r->ignore_contents = dup_list(ign_contents);
+  P.ready = false;
   r->ms_h2d = dt->ms_h2d;
   r->ms_scan_kernel = C->last_scan_ms;
   r->n_kernel_launches = (uint32_t)C->launches;

@@ -50,7 +50,8 @@ void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n) {
 __global__ void __launch_bounds__(256) k_name_features(
     uint32_t n_entries, const uint32_t* __restrict__ entry_dir, const uint32_t* __restrict__ entry_name_off,
     const uint8_t* __restrict__ entry_type, const uint8_t* __restrict__ names, const NameSig* __restrict__ sigs, int n_sigs,
-    uint32_t* __restrict__ entry_feat, uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_first_war) {
+    uint32_t* __restrict__ entry_feat, uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_first_war,
+    uint32_t* __restrict__ special, uint32_t special_cap) {
   __shared__ NameSig s_sigs[kMaxNameSigs];
   for (int i = threadIdx.x; i < n_sigs; i += blockDim.x) s_sigs[i] = sigs[i];
   __syncthreads();
@@ -83,6 +84,11 @@ __global__ void __launch_bounds__(256) k_name_features(
       }
     }
     entry_feat[e] = feat;
+    if (feat & ((1u << M2K_N_IGNOREFILE) | (1u << M2K_N_USER_DF) | (1u << M2K_N_USER_S2I))) {
+      // rare: list these entries so the host need not look through every feature word
+      uint32_t k = atomicAdd(&special[0], 1u);
+      if (k < special_cap) special[1 + k] = e;
+    }
     if (feat & (1u << M2K_N_WAR)) atomicMin(&dir_first_war[dir], e);  // entries are name-sorted inside a directory
   }
   // segmented OR over the lanes that share a directory
@@ -96,7 +102,8 @@ void launch_name_features(Ctx* c, DevTree* t) {
   if (!t->n_entries) return;
   uint32_t blocks = (t->n_entries + 255) / 256;
   k_name_features<<<blocks, 256, 0, c->stream>>>(t->n_entries, t->entry_dir, t->entry_name_off, t->entry_type, t->names,
-                                                 c->d_sigs, c->n_sigs, t->entry_feat, t->dir_direct, t->dir_first_war);
+                                                 c->d_sigs, c->n_sigs, t->entry_feat, t->dir_direct, t->dir_first_war,
+                                                 t->special, t->special_cap);
   c->launches++;
 }
 

@@ -67,6 +67,8 @@ struct DevTree {
   uint64_t* cand_body = nullptr;
   uint8_t *cand_esc = nullptr, *stripe_state = nullptr;
   uint32_t stripe_cap = 0;
+  uint32_t* special = nullptr;            // [0] count, then ids of entries with a special name (compacted by k_name_features)
+  uint32_t special_cap = 0;
   void* ign_blob = nullptr;               // ignore table + folded runes of the last finalize (grow-only)
   size_t ign_blob_cap = 0;
   uint32_t* entry_feat = nullptr;         // [n_entries]

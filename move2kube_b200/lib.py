@@ -25,7 +25,7 @@ class M2KError(RuntimeError):
 EXPORTS = [
     "m2k_abi_version", "m2k_global_error", "m2k_ctx_create", "m2k_ctx_destroy", "m2k_last_error", "m2k_device_info",
     "m2k_pack_tree", "m2k_tree_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
-    "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_finalize",
+    "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_prepare", "m2k_finalize",
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc",
 ]
@@ -62,6 +62,7 @@ def load():
     L.m2k_scan.argtypes = [vp, vp, PP]
     L.m2k_partials.argtypes = [vp, vp, vp, vp]
     L.m2k_merge_partials.argtypes = [vp, vp, vp, vp, C.c_uint32]
+    L.m2k_prepare.argtypes = [vp, vp, PP]
     L.m2k_finalize.argtypes = [vp, vp, PP, C.POINTER(RP)]
     L.m2k_devtree_free.argtypes = [vp, vp]
     L.m2k_devtree_free.restype = None
@@ -168,6 +169,10 @@ class Context:
 
     def merge_partials(self, dt, all_content_ptr, all_main_ptr, n_ranks):
         _check(self.L.m2k_merge_partials(self.h, dt, all_content_ptr, all_main_ptr, n_ranks), self.h)
+
+    def prepare(self, dt, flavor=_abi.SH_BASH, pre=()):
+        p, keep = make_params(flavor, pre, False)
+        _check(self.L.m2k_prepare(self.h, dt, C.byref(p)), self.h)
 
     def finalize(self, dt, flavor=_abi.SH_BASH, pre=()):
         p, keep = make_params(flavor, pre, False)
