@@ -182,6 +182,9 @@ int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes, char* name
  *    (utils.go:85-120 x3 per Any2Kube call, any2kube.go:58, dockerfile2kube.go:154) -- */
 int m2k_pack_tree(m2k_ctx* ctx, const char* root_path, int read_content, m2k_tree** out);
 void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree);
+/* pinned host memory for callers that stage file bytes themselves (NULL on failure, see m2k_last_error) */
+void* m2k_pinned_alloc(m2k_ctx* ctx, size_t bytes);
+void m2k_pinned_free(m2k_ctx* ctx, void* p);
 
 /* -- synthetic trees of BASELINE.md section 4 (configs B, C, D), deterministic in `seed` -- */
 typedef struct m2k_synth_params {

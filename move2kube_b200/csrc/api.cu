@@ -218,6 +218,21 @@ extern "C" int m2k_synth_fill_host(const m2k_tree* tree, uint64_t seed, uint32_t
   return M2K_OK;
 }
 
+// pinned host arena for callers that stage file bytes themselves (never hand
+// garbage-collected memory to asynchronous copies)
+extern "C" void* m2k_pinned_alloc(m2k_ctx* ctx, size_t bytes) {
+  if (!ctx || !bytes) { fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_pinned_alloc: bad argument"); return nullptr; }
+  cudaSetDevice(ctx->c.device);
+  void* p = nullptr;
+  cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocPortable);
+  if (e != cudaSuccess) { cudaGetLastError(); fail(&ctx->c, M2K_ERR_NOMEM, "cudaHostAlloc(%zu bytes): %s", bytes, cudaGetErrorString(e)); return nullptr; }
+  return p;
+}
+extern "C" void m2k_pinned_free(m2k_ctx* ctx, void* p) {
+  if (ctx) cudaSetDevice(ctx->c.device);
+  if (p) cudaFreeHost(p);
+}
+
 extern "C" void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree) {
   if (ctx) cudaSetDevice(ctx->c.device);
   tree_release(tree);

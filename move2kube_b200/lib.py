@@ -24,7 +24,7 @@ class M2KError(RuntimeError):
 # every symbol include/m2kdetect.h declares
 EXPORTS = [
     "m2k_abi_version", "m2k_global_error", "m2k_ctx_create", "m2k_ctx_destroy", "m2k_last_error", "m2k_device_info",
-    "m2k_pack_tree", "m2k_tree_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
+    "m2k_pack_tree", "m2k_tree_free", "m2k_pinned_alloc", "m2k_pinned_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
     "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_prepare", "m2k_finalize",
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc",
@@ -52,6 +52,10 @@ def load():
     L.m2k_pack_tree.argtypes = [vp, C.c_char_p, C.c_int, C.POINTER(TP)]
     L.m2k_tree_free.argtypes = [vp, TP]
     L.m2k_tree_free.restype = None
+    L.m2k_pinned_alloc.argtypes = [vp, C.c_size_t]
+    L.m2k_pinned_alloc.restype = vp
+    L.m2k_pinned_free.argtypes = [vp, vp]
+    L.m2k_pinned_free.restype = None
     L.m2k_synth_tree.argtypes = [vp, C.POINTER(_abi.SynthParams), C.c_int, C.POINTER(TP)]
     L.m2k_synth_fill_host.argtypes = [TP, C.c_uint64, C.c_uint32, C.c_uint32, vp, C.c_int]
     L.m2k_detect.argtypes = [vp, TP, PP, C.POINTER(RP)]
@@ -134,6 +138,15 @@ class Context:
         tp = C.POINTER(_abi.Tree)()
         _check(self.L.m2k_synth_tree(self.h, C.byref(params), 1 if host_bytes else 0, C.byref(tp)), self.h)
         return tp
+
+    def pinned_alloc(self, nbytes):
+        p = self.L.m2k_pinned_alloc(self.h, nbytes)
+        if not p:
+            _check(_abi.ERR_NOMEM, self.h)
+        return p
+
+    def pinned_free(self, p):
+        self.L.m2k_pinned_free(self.h, p)
 
     def tree_free(self, tree):
         self.L.m2k_tree_free(self.h, tree)
