@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -38,6 +39,8 @@ struct m2k_devtree {
   float ms_h2d = 0.f;
   uint32_t* h_entry_feat = nullptr;  // pinned
   uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
+  void* h_ign = nullptr;             // pinned staging of the ignore table (grow-only)
+  size_t h_ign_cap = 0;
   bool content = true;
   IgnorePrep prep;
 };
@@ -255,6 +258,7 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   devtree_release(&dt->t);
   if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
   if (dt->h_special) cudaFreeHost(dt->h_special);
+  if (dt->h_ign) cudaFreeHost(dt->h_ign);
   delete dt;
 }
 
@@ -269,7 +273,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
   DevTree* t = &dt->t;
-  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); if (d->h_special) cudaFreeHost(d->h_special); delete d; } } } guard{dt};
+  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); if (d->h_special) cudaFreeHost(d->h_special); if (d->h_ign) cudaFreeHost(d->h_ign); delete d; } } } guard{dt};
   t->host = tree;
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
   t->file_begin = file_begin; t->file_end = file_end;
@@ -525,6 +529,7 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   } else {
     for (uint32_t e = 0; e < t->n_entries; e++) if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
   }
+  double h1 = now_ms();
   // filepath.Walk order: compare the chains of entry indices from the root down
   const size_t nfiles = ign_entries.size();
   std::vector<std::vector<uint32_t>> chains(nfiles);
@@ -540,6 +545,7 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   std::vector<uint32_t> order(nfiles);
   for (size_t i = 0; i < nfiles; i++) order[i] = (uint32_t)i;
   std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return chains[x] < chains[y]; });
+  double h2 = now_ms();
   // parse the files in parallel (each is independent), keep Walk order when concatenating
   struct Parsed { std::vector<std::string> dirs, contents; bool missing = false; };
   std::vector<Parsed> parsed(nfiles);
@@ -574,35 +580,76 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     for (auto& x : parsed[k].dirs) P.ign_dirs.push_back(std::move(x));
     for (auto& x : parsed[k].contents) P.ign_contents.push_back(std::move(x));
   }
+  double h3 = now_ms();
   // exact hash table over the case-folded entries, keyed by the folded rune sequence;
   // flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
   std::vector<std::string> pre;
   for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
   const uint64_t seed0 = 0xcbf29ce484222325ull;
-  struct Ent { uint64_t key; uint32_t flags, off, len; };
-  std::vector<Ent> ents;
-  std::vector<uint32_t> runes, tmp, root_runes;
-  std::unordered_map<uint64_t, std::vector<uint32_t>> by_key;  // key -> indices into ents (collisions share a key)
-  by_key.reserve(P.ign_dirs.size() + P.ign_contents.size() + pre.size());
-  fold_runes(root, &root_runes);
-  auto add = [&](const std::string& sp, uint32_t flag) {
-    fold_runes(sp, &tmp);
-    if (tmp == root_runes) P.root_ignore |= (uint8_t)flag;
-    uint64_t h = seed0;
-    for (uint32_t rr : tmp) h = hash_step(h, rr);
-    uint64_t key = hash_finish(h);
-    auto& lst = by_key[key];
-    for (uint32_t idx : lst) {
-      const Ent& en = ents[idx];
-      if (en.len == tmp.size() && std::equal(tmp.begin(), tmp.end(), runes.begin() + en.off)) { ents[idx].flags |= flag; return; }
+  struct Src { const std::string* s; uint32_t flag; };
+  std::vector<Src> srcs;
+  srcs.reserve(P.ign_dirs.size() + P.ign_contents.size() + pre.size());
+  for (const auto& x : P.ign_dirs) srcs.push_back({&x, 1});
+  for (const auto& x : P.ign_contents) srcs.push_back({&x, 2});
+  for (const auto& x : pre) srcs.push_back({&x, 4});
+  // fold + hash every entry (independent: threads), then insert one after the other into the
+  // open-addressing table that is uploaded as is; equal folded sequences share a slot
+  struct Folded { uint64_t key; uint32_t off, len; };
+  const size_t ns_ = srcs.size();
+  std::vector<Folded> folded(ns_);
+  unsigned nt2 = std::thread::hardware_concurrency();
+  if (nt2 == 0) nt2 = 4;
+  if (nt2 > 16) nt2 = 16;
+  if (nt2 > ns_ / 512 + 1) nt2 = (unsigned)(ns_ / 512 + 1);
+  std::vector<std::vector<uint32_t>> rune_parts(nt2);
+  {
+    auto worker = [&](unsigned tid) {
+      size_t lo = ns_ * tid / nt2, hi = ns_ * (tid + 1) / nt2;
+      std::vector<uint32_t>& out = rune_parts[tid];
+      std::vector<uint32_t> tmp;
+      for (size_t i = lo; i < hi; i++) {
+        fold_runes(*srcs[i].s, &tmp);
+        uint64_t h = seed0;
+        for (uint32_t rr : tmp) h = hash_step(h, rr);
+        folded[i] = {hash_finish(h), (uint32_t)out.size(), (uint32_t)tmp.size()};
+        out.insert(out.end(), tmp.begin(), tmp.end());
+      }
+    };
+    std::vector<std::thread> th;
+    for (unsigned i = 1; i < nt2; i++) th.emplace_back(worker, i);
+    worker(0);
+    for (auto& x : th) x.join();
+  }
+  std::vector<uint32_t> runes, root_runes;
+  {
+    size_t total = 0;
+    std::vector<size_t> base(nt2);
+    for (unsigned k = 0; k < nt2; k++) { base[k] = total; total += rune_parts[k].size(); }
+    runes.resize(total);
+    for (unsigned k = 0; k < nt2; k++) {
+      if (!rune_parts[k].empty()) memcpy(runes.data() + base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
+      size_t lo = ns_ * k / nt2, hi = ns_ * (k + 1) / nt2;
+      for (size_t i = lo; i < hi; i++) folded[i].off += (uint32_t)base[k];
     }
-    lst.push_back((uint32_t)ents.size());
-    ents.push_back({key, flag, (uint32_t)runes.size(), (uint32_t)tmp.size()});
-    runes.insert(runes.end(), tmp.begin(), tmp.end());
-  };
-  for (const auto& x : P.ign_dirs) add(x, 1);
-  for (const auto& x : P.ign_contents) add(x, 2);
-  for (const auto& x : pre) add(x, 4);
+  }
+  fold_runes(root, &root_runes);
+  size_t n_slots_used = 0;
+  if (ns_) {
+    uint32_t cap = 16;
+    while (cap < ns_ * 2) cap <<= 1;
+    P.table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
+    P.table_mask = cap - 1;
+    for (size_t i = 0; i < ns_; i++) {
+      const Folded& fo = folded[i];
+      const uint32_t* rp = runes.data() + fo.off;
+      if (fo.len == root_runes.size() && std::equal(rp, rp + fo.len, root_runes.begin())) P.root_ignore |= (uint8_t)srcs[i].flag;
+      for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
+        IgnoreSlot& sl = P.table[sidx];
+        if (sl.hash == 0) { sl = IgnoreSlot{fo.key, srcs[i].flag, fo.off, fo.len, 0}; n_slots_used++; break; }
+        if (sl.hash == fo.key && sl.len == fo.len && std::equal(rp, rp + fo.len, runes.data() + sl.off)) { sl.flags |= srcs[i].flag; break; }
+      }
+    }
+  }
   // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
   std::string prefix1 = clean_root;
   if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
@@ -611,16 +658,8 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   P.depth1_state = seed0;
   for (uint32_t rr : prefix_runes) P.depth1_state = hash_step(P.depth1_state, rr);
   P.prefix_len = (uint32_t)prefix_runes.size();
-  if (!ents.empty()) {
-    uint32_t cap = 16;
-    while (cap < ents.size() * 2) cap <<= 1;
-    P.table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
-    P.table_mask = cap - 1;
-    for (const Ent& en : ents) {
-      uint32_t sidx = (uint32_t)en.key & P.table_mask;
-      while (P.table[sidx].hash) sidx = (sidx + 1) & P.table_mask;
-      P.table[sidx] = IgnoreSlot{en.key, en.flags, en.off, en.len, 0};
-    }
+  if (n_slots_used) {
+    const uint32_t cap = P.table_mask + 1;
     size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
     if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
       if (t->ign_blob) CU(cudaFree(t->ign_blob));
@@ -629,17 +668,26 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
       CU(cudaMalloc(&t->ign_blob, want));
       t->ign_blob_cap = want;
     }
-    // staged through vectors that live in the prep until finalize has synchronised
-    P.runes.swap(runes);
-    P.prefix_runes.swap(prefix_runes);
-    CU(cudaMemcpyAsync(t->ign_blob, P.table.data(), tb, cudaMemcpyHostToDevice, s));
-    if (rb) CU(cudaMemcpyAsync((char*)t->ign_blob + tb, P.runes.data(), rb, cudaMemcpyHostToDevice, s));
-    if (pb) CU(cudaMemcpyAsync((char*)t->ign_blob + tb + rb, P.prefix_runes.data(), pb, cudaMemcpyHostToDevice, s));
+    // staged through a pinned buffer kept with the device tree: a copy from pageable memory would
+    // make this call wait for the byte scan that is queued ahead of it on the stream
+    if (tb + rb + pb > dt->h_ign_cap) {
+      if (dt->h_ign) cudaFreeHost(dt->h_ign);
+      dt->h_ign = nullptr; dt->h_ign_cap = 0;
+      CU(cudaHostAlloc(&dt->h_ign, (tb + rb + pb) * 2, cudaHostAllocDefault));
+      dt->h_ign_cap = (tb + rb + pb) * 2;
+    }
+    memcpy(dt->h_ign, P.table.data(), tb);
+    if (rb) memcpy((char*)dt->h_ign + tb, runes.data(), rb);
+    if (pb) memcpy((char*)dt->h_ign + tb + rb, prefix_runes.data(), pb);
+    CU(cudaMemcpyAsync(t->ign_blob, dt->h_ign, tb + rb + pb, cudaMemcpyHostToDevice, s));
     P.d_table = (const IgnoreSlot*)t->ign_blob;
     P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
     P.d_prefix = (const uint32_t*)((char*)t->ign_blob + tb + rb);
   }
   P.ms_host = (float)(now_ms() - h0);
+  if (getenv("M2K_DEBUG_TIMING"))
+    fprintf(stderr, "[m2k] prepare: find %.2f ms, order %.2f ms, parse %.2f ms, table+upload %.2f ms (%zu files, %zu+%zu entries)\n",
+            h1 - h0, h2 - h1, h3 - h2, now_ms() - h3, nfiles, P.ign_dirs.size(), P.ign_contents.size());
   P.ready = true;
   return M2K_OK;
 }
