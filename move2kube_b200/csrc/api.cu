@@ -40,6 +40,7 @@ struct m2k_devtree {
   uint32_t* h_entry_feat = nullptr;  // pinned
   uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
   void* h_ign = nullptr;             // pinned staging of the ignore table (grow-only)
+  m2k_result* pending = nullptr;     // result arrays allocated by m2k_prepare
   size_t h_ign_cap = 0;
   bool content = true;
   IgnorePrep prep;
@@ -259,6 +260,7 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
   if (dt->h_special) cudaFreeHost(dt->h_special);
   if (dt->h_ign) cudaFreeHost(dt->h_ign);
+  if (dt->pending) m2k_result_free(dt->pending);
   delete dt;
 }
 
@@ -684,6 +686,20 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
     P.d_prefix = (const uint32_t*)((char*)t->ign_blob + tb + rb);
   }
+  // result arrays, and the host copy of the name features, while the GPU is still busy
+  {
+    if (dt->pending) { m2k_result_free(dt->pending); dt->pending = nullptr; }
+    const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
+    m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
+    r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
+    auto HA = [&](size_t bytes) { return calloc(bytes ? bytes : 1, 1); };
+    r->dir_opts = (uint32_t*)HA(4ull * nd); r->dir_direct = (uint32_t*)HA(4ull * nd); r->dir_subtree = (uint32_t*)HA(4ull * nd);
+    r->dir_state = (uint8_t*)HA(nd); r->dir_ignore = (uint8_t*)HA(nd); r->dir_main_file = (uint32_t*)HA(4ull * nd);
+    r->file_flags = (uint8_t*)HA(nf); r->service_dirs = (uint32_t*)HA(4ull * nd);
+    r->entry_feat = (uint32_t*)malloc(4ull * (ne ? ne : 1));
+    memcpy(r->entry_feat, dt->h_entry_feat, 4ull * ne);
+    dt->pending = r;
+  }
   P.ms_host = (float)(now_ms() - h0);
   if (getenv("M2K_DEBUG_TIMING"))
     fprintf(stderr, "[m2k] prepare: find %.2f ms, order %.2f ms, parse %.2f ms, table+upload %.2f ms (%zu files, %zu+%zu entries)\n",
@@ -710,14 +726,8 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   cudaStream_t s = C->stream;
   const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
   const uint32_t sh = params ? params->sh_flavor : M2K_SH_BASH;
-  m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
-  struct RG { m2k_result* r; bool keep = false; ~RG() { if (!keep) m2k_result_free(r); } } rg{r};
-  r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
-  auto HA = [&](size_t bytes) { return calloc(bytes ? bytes : 1, 1); };
-  r->dir_opts = (uint32_t*)HA(4ull * nd); r->dir_direct = (uint32_t*)HA(4ull * nd); r->dir_subtree = (uint32_t*)HA(4ull * nd);
-  r->dir_state = (uint8_t*)HA(nd); r->dir_ignore = (uint8_t*)HA(nd); r->dir_main_file = (uint32_t*)HA(4ull * nd);
-  r->file_flags = (uint8_t*)HA(nf); r->service_dirs = (uint32_t*)HA(4ull * nd); r->entry_feat = (uint32_t*)HA(4ull * ne);
-
+  // the result arrays (and the copy of the name features) were prepared under the byte scan when
+  // m2k_prepare ran; otherwise they are made now
   // bottom-up and the predicate table do not depend on the ignore rules: queue them first
   CU(cudaEventRecord(C->ev[4], s));
   launch_subtree(C, t);
@@ -725,7 +735,9 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaEventRecord(C->ev[7], s));
   if (!dt->prep.ready) { if (int rc = prepare_ignore(C, dt, params)) return rc; }
   IgnorePrep& P = dt->prep;
-  memcpy(r->entry_feat, dt->h_entry_feat, 4ull * ne);
+  m2k_result* r = dt->pending;
+  dt->pending = nullptr;
+  struct RG { m2k_result* r; bool keep = false; ~RG() { if (!keep) m2k_result_free(r); } } rg{r};
   r->ms_host_ignore = P.ms_host;
 
   CU(cudaEventRecord(C->ev[11], s));
