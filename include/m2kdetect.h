@@ -138,7 +138,11 @@ typedef struct m2k_tree {
   void* owner;               /* library bookkeeping */
 } m2k_tree;
 
-/* ---- results (host memory, owned by the library, freed with m2k_result_free) ---- */
+/* ---- results (host memory, owned by the library, released with m2k_result_free) ----
+ * The arrays are pinned buffers the device copies into directly.  A result of m2k_detect stays valid
+ * until m2k_result_free.  A result of m2k_finalize borrows the buffers of its device tree: it is valid
+ * until the next m2k_scan / m2k_prepare / m2k_finalize on that tree or its m2k_devtree_free, and must
+ * be released before or together with the tree. */
 typedef struct m2k_result {
   uint32_t n_dirs, n_files, n_services, n_entries;
   uint32_t* dir_opts;      /* [n_dirs] built-in option bits (M2K_DF_*, M2K_S2I_*) for EVERY directory */
@@ -157,6 +161,7 @@ typedef struct m2k_result {
   float ms_h2d, ms_kernels, ms_scan_kernel, ms_d2h, ms_host_ignore, ms_total;
   uint32_t n_kernel_launches;
   uint32_t _pad;
+  void* owner;             /* library bookkeeping */
 } m2k_result;
 
 typedef struct m2k_detect_params {
@@ -219,6 +224,10 @@ int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
 int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_dst_content, uint32_t* d_dst_main);
 /* OR / MIN `n_ranks` gathered partial arrays (device memory, rank-major) into this shard's own */
 int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks);
+/* per-file flags of a sharded run, copied device-to-device out of / into the device tree ([n_files] bytes):
+ * each rank writes only its own file range, so a byte-wise sum across ranks is the union */
+int m2k_file_flags_get(m2k_ctx* ctx, m2k_devtree* dt, uint8_t* d_dst);
+int m2k_file_flags_set(m2k_ctx* ctx, m2k_devtree* dt, const uint8_t* d_src);
 /* optional, between m2k_scan and m2k_finalize: the host half of getIgnorePaths (any2kube.go:151-181) --
  * parse the .m2kignore files the name kernel found and upload the lookup table -- while the byte scan
  * is still running on the GPU.  m2k_finalize does it itself when this was not called. */

@@ -53,6 +53,7 @@ class Result(C.Structure):
         ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_scan_kernel", C.c_float),
         ("ms_d2h", C.c_float), ("ms_host_ignore", C.c_float), ("ms_total", C.c_float),
         ("n_kernel_launches", C.c_uint32), ("_pad", C.c_uint32),
+        ("owner", C.c_void_p),
     ]
 
 

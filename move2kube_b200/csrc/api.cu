@@ -40,7 +40,8 @@ struct m2k_devtree {
   uint32_t* h_entry_feat = nullptr;  // pinned
   uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
   void* h_ign = nullptr;             // pinned staging of the ignore table (grow-only)
-  m2k_result* pending = nullptr;     // result arrays allocated by m2k_prepare
+  m2k_result* pending = nullptr;     // result shell made by m2k_prepare
+  uint8_t* h_results = nullptr;      // pinned: every per-directory / per-file result array (see result_layout)
   size_t h_ign_cap = 0;
   bool content = true;
   IgnorePrep prep;
@@ -253,15 +254,21 @@ static void devtree_release(DevTree* t) {
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
+// pinned host buffers and the object itself (device memory is released separately)
+static void free_devtree_shell(m2k_devtree* dt) {
+  if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
+  if (dt->h_special) cudaFreeHost(dt->h_special);
+  if (dt->h_ign) cudaFreeHost(dt->h_ign);
+  if (dt->h_results) cudaFreeHost(dt->h_results);
+  if (dt->pending) { m2k_result* p = dt->pending; dt->pending = nullptr; p->owner = nullptr; m2k_result_free(p); }
+  delete dt;
+}
+
 extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (!dt) return;
   if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); }
   devtree_release(&dt->t);
-  if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
-  if (dt->h_special) cudaFreeHost(dt->h_special);
-  if (dt->h_ign) cudaFreeHost(dt->h_ign);
-  if (dt->pending) m2k_result_free(dt->pending);
-  delete dt;
+  free_devtree_shell(dt);
 }
 
 template <typename T>
@@ -275,7 +282,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
   DevTree* t = &dt->t;
-  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); if (d->h_entry_feat) cudaFreeHost(d->h_entry_feat); if (d->h_special) cudaFreeHost(d->h_special); if (d->h_ign) cudaFreeHost(d->h_ign); delete d; } } } guard{dt};
+  struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); free_devtree_shell(d); } } } guard{dt};
   t->host = tree;
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
   t->file_begin = file_begin; t->file_end = file_end;
@@ -329,6 +336,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
 
   CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
   CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
+  CU(cudaHostAlloc((void**)&dt->h_results, 22ull * (nd ? nd : 1) + nf + 64, cudaHostAllocDefault));
   CU(dev_alloc(&t->special, (size_t)kSpecialCap + 1));
   t->special_cap = kSpecialCap;
   cudaStream_t s = C->stream;
@@ -438,6 +446,24 @@ extern "C" int m2k_partials(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_dst_conte
   return M2K_OK;
 }
 
+// per-file flags of a sharded run: every rank fills only its own file range (the rest stays zero), so
+// a byte-wise sum over ranks is the union
+extern "C" int m2k_file_flags_get(m2k_ctx* ctx, m2k_devtree* dt, uint8_t* d_dst) {
+  if (!ctx || !dt || !d_dst) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaMemcpyAsync(d_dst, dt->t.file_flags, dt->t.n_files, cudaMemcpyDeviceToDevice, C->stream));
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+extern "C" int m2k_file_flags_set(m2k_ctx* ctx, m2k_devtree* dt, const uint8_t* d_src) {
+  if (!ctx || !dt || !d_src) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaMemcpyAsync(dt->t.file_flags, d_src, dt->t.n_files, cudaMemcpyDeviceToDevice, C->stream));
+  return M2K_OK;
+}
+
 extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks) {
   if (!ctx || !dt || !d_all_content || !d_all_main || !n_ranks) return fail(nullptr, M2K_ERR_ARG, "bad argument");
   Ctx* C = &ctx->c;
@@ -502,9 +528,14 @@ char** dup_list(const std::vector<std::string>& v) {
 
 extern "C" void m2k_result_free(m2k_result* r) {
   if (!r) return;
-  free(r->dir_opts); free(r->dir_direct); free(r->dir_subtree); free(r->dir_state); free(r->dir_ignore); free(r->dir_main_file);
-  free(r->file_flags); free(r->service_dirs); free(r->entry_feat);
+  // the per-directory / per-file / per-entry arrays live in pinned buffers of the device tree (the
+  // D2H copies land there directly); a result of m2k_detect owns what is left of its device tree
   free(r->ignore_dirs); free(r->ignore_contents);  // each list is one block (dup_list)
+  if (r->owner) {
+    m2k_devtree* dt = static_cast<m2k_devtree*>(r->owner);
+    if (dt->pending == r) dt->pending = nullptr;
+    free_devtree_shell(dt);
+  }
   free(r);
 }
 
@@ -692,12 +723,17 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
     m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
     r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
-    auto HA = [&](size_t bytes) { return calloc(bytes ? bytes : 1, 1); };
-    r->dir_opts = (uint32_t*)HA(4ull * nd); r->dir_direct = (uint32_t*)HA(4ull * nd); r->dir_subtree = (uint32_t*)HA(4ull * nd);
-    r->dir_state = (uint8_t*)HA(nd); r->dir_ignore = (uint8_t*)HA(nd); r->dir_main_file = (uint32_t*)HA(4ull * nd);
-    r->file_flags = (uint8_t*)HA(nf); r->service_dirs = (uint32_t*)HA(4ull * nd);
-    r->entry_feat = (uint32_t*)malloc(4ull * (ne ? ne : 1));
-    memcpy(r->entry_feat, dt->h_entry_feat, 4ull * ne);
+    // layout of dt->h_results: five uint32 arrays of n_dirs, two byte arrays of n_dirs, one of n_files
+    uint8_t* b = dt->h_results;
+    r->dir_opts = (uint32_t*)b; b += 4ull * nd;
+    r->dir_direct = (uint32_t*)b; b += 4ull * nd;
+    r->dir_subtree = (uint32_t*)b; b += 4ull * nd;
+    r->dir_main_file = (uint32_t*)b; b += 4ull * nd;
+    r->service_dirs = (uint32_t*)b; b += 4ull * nd;
+    r->dir_state = b; b += nd;
+    r->dir_ignore = b; b += nd;
+    r->file_flags = b;
+    r->entry_feat = dt->h_entry_feat;
     dt->pending = r;
   }
   P.ms_host = (float)(now_ms() - h0);
@@ -739,6 +775,7 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   dt->pending = nullptr;
   struct RG { m2k_result* r; bool keep = false; ~RG() { if (!keep) m2k_result_free(r); } } rg{r};
   r->ms_host_ignore = P.ms_host;
+  r->n_services = 0;
 
   CU(cudaEventRecord(C->ev[11], s));
   launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore);
@@ -788,7 +825,13 @@ extern "C" int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_p
   if (rc != M2K_OK) return rc;
   rc = m2k_scan(ctx, dt, params);
   if (rc == M2K_OK) rc = m2k_finalize(ctx, dt, params, out);
-  m2k_devtree_free(ctx, dt);
+  if (rc != M2K_OK) { m2k_devtree_free(ctx, dt); return rc; }
+  // the result's arrays live in the device tree's pinned buffers: free the device memory now, hand the
+  // rest to the result
+  cudaStreamSynchronize(ctx->c.stream);
+  devtree_release(&dt->t);
+  dt->t = DevTree();
+  (*out)->owner = dt;
   if (rc == M2K_OK) {
     (*out)->ms_total = (float)(now_ms() - t0);
     (*out)->n_kernel_launches = (uint32_t)(ctx->c.launches - l0);

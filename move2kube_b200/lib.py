@@ -25,7 +25,7 @@ class M2KError(RuntimeError):
 EXPORTS = [
     "m2k_abi_version", "m2k_global_error", "m2k_ctx_create", "m2k_ctx_destroy", "m2k_last_error", "m2k_device_info",
     "m2k_pack_tree", "m2k_tree_free", "m2k_pinned_alloc", "m2k_pinned_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
-    "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_prepare", "m2k_finalize",
+    "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_file_flags_get", "m2k_file_flags_set", "m2k_prepare", "m2k_finalize",
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc",
 ]
@@ -66,6 +66,8 @@ def load():
     L.m2k_scan.argtypes = [vp, vp, PP]
     L.m2k_partials.argtypes = [vp, vp, vp, vp]
     L.m2k_merge_partials.argtypes = [vp, vp, vp, vp, C.c_uint32]
+    L.m2k_file_flags_get.argtypes = [vp, vp, vp]
+    L.m2k_file_flags_set.argtypes = [vp, vp, vp]
     L.m2k_prepare.argtypes = [vp, vp, PP]
     L.m2k_finalize.argtypes = [vp, vp, PP, C.POINTER(RP)]
     L.m2k_devtree_free.argtypes = [vp, vp]
@@ -182,6 +184,12 @@ class Context:
 
     def merge_partials(self, dt, all_content_ptr, all_main_ptr, n_ranks):
         _check(self.L.m2k_merge_partials(self.h, dt, all_content_ptr, all_main_ptr, n_ranks), self.h)
+
+    def file_flags_get(self, dt, dst_ptr):
+        _check(self.L.m2k_file_flags_get(self.h, dt, dst_ptr), self.h)
+
+    def file_flags_set(self, dt, src_ptr):
+        _check(self.L.m2k_file_flags_set(self.h, dt, src_ptr), self.h)
 
     def prepare(self, dt, flavor=_abi.SH_BASH, pre=()):
         p, keep = make_params(flavor, pre, False)
