@@ -23,15 +23,18 @@ constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2k
 // what m2k_prepare / m2k_finalize derive from the .m2kignore files (host side of a2 / a4)
 struct IgnorePrep {
   bool ready = false;
-  std::vector<std::string> ign_dirs, ign_contents;
+  std::vector<PathArena> arenas;  // cleaned entries in the reference's list order; the last arena = preContainerized
   std::vector<IgnoreSlot> table;
-  std::vector<uint32_t> runes, prefix_runes;
   uint32_t table_mask = M2K_NONE, prefix_len = 0;
   uint64_t depth1_state = 0;
   uint8_t root_ignore = 0;
   const IgnoreSlot* d_table = nullptr;
   const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
   float ms_host = 0.f;
+  void reset() {
+    ready = false; arenas.clear(); table.clear(); table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
+    d_table = nullptr; d_runes = d_prefix = nullptr; ms_host = 0.f;
+  }
 };
 
 struct m2k_devtree {
@@ -509,18 +512,26 @@ const uint8_t* host_file_bytes(const m2k_tree* t, uint32_t f, uint64_t* len) {
 }
 
 // one allocation: the pointer array followed by the characters (freed with a single free())
-char** dup_list(const std::vector<std::string>& v) {
-  size_t chars = 0;
-  for (const auto& x : v) chars += x.size() + 1;
-  size_t head = (v.size() ? v.size() : 1) * sizeof(char*);
+char** list_from_arenas(const std::vector<PathArena>& arenas, uint8_t flag, uint32_t* count) {
+  size_t n = 0, chars = 0;
+  for (const PathArena& A : arenas)
+    for (size_t i = 0; i < A.size(); i++)
+      if (A.flag[i] == flag) { n++; chars += A.off[i + 1] - A.off[i] + 1; }
+  size_t head = (n ? n : 1) * sizeof(char*);
   char** out = static_cast<char**>(malloc(head + chars + 1));
   char* w = reinterpret_cast<char*>(out) + head;
   out[0] = nullptr;
-  for (size_t i = 0; i < v.size(); i++) {
-    out[i] = w;
-    memcpy(w, v[i].c_str(), v[i].size() + 1);
-    w += v[i].size() + 1;
-  }
+  size_t k = 0;
+  for (const PathArena& A : arenas)
+    for (size_t i = 0; i < A.size(); i++)
+      if (A.flag[i] == flag) {
+        size_t len = A.off[i + 1] - A.off[i];
+        out[k++] = w;
+        memcpy(w, A.chars.data() + A.off[i], len);
+        w[len] = 0;
+        w += len + 1;
+      }
+  *count = (uint32_t)n;
   return out;
 }
 
@@ -541,6 +552,22 @@ extern "C" void m2k_result_free(m2k_result* r) {
 
 // getIgnorePaths (any2kube.go:151-181) + the lookup structure of IsStringPresent (utils.go:308-315):
 // host work that needs only the name features, so it runs while the byte scan is still on the GPU.
+static unsigned host_threads(size_t work_items, size_t per_thread) {
+  unsigned nt = std::thread::hardware_concurrency();
+  if (nt == 0) nt = 4;
+  if (nt > 32) nt = 32;
+  if (nt > work_items / per_thread + 1) nt = (unsigned)(work_items / per_thread + 1);
+  return nt;
+}
+
+template <typename F>
+static void run_threads(unsigned nt, F&& fn) {
+  std::vector<std::thread> th;
+  for (unsigned i = 1; i < nt; i++) th.emplace_back(fn, i);
+  fn(0u);
+  for (auto& x : th) x.join();
+}
+
 static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* params) {
   DevTree* t = &dt->t;
   IgnorePrep& P = dt->prep;
@@ -548,7 +575,7 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   cudaStream_t s = C->stream;
   CU(cudaEventSynchronize(C->ev[2]));  // name features and the special-entry list are on the host now
   double h0 = now_ms();
-  P = IgnorePrep();
+  P.reset();
   const std::string root = tree->root_path ? tree->root_path : "";
   const std::string clean_root = path_clean(root);
   // the .m2kignore files: from the compacted list of special entries, or a scan of all features if it overflowed
@@ -563,125 +590,117 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     for (uint32_t e = 0; e < t->n_entries; e++) if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
   }
   double h1 = now_ms();
-  // filepath.Walk order: compare the chains of entry indices from the root down
+  // filepath.Walk order: compare the chains of entry indices from the root down (one flat array)
   const size_t nfiles = ign_entries.size();
-  std::vector<std::vector<uint32_t>> chains(nfiles);
+  std::vector<uint32_t> chain_off(nfiles + 1, 0), chain;
+  chain.reserve(nfiles * 8);
   for (size_t i = 0; i < nfiles; i++) {
+    size_t at = chain.size();
     for (uint32_t e = ign_entries[i];;) {
-      chains[i].push_back(e);
+      chain.push_back(e);
       uint32_t d = tree->entry_dir[e];
       if (d == 0) break;
       e = tree->dir_entry[d];
     }
-    std::reverse(chains[i].begin(), chains[i].end());
+    std::reverse(chain.begin() + at, chain.end());
+    chain_off[i + 1] = (uint32_t)chain.size();
   }
   std::vector<uint32_t> order(nfiles);
   for (size_t i = 0; i < nfiles; i++) order[i] = (uint32_t)i;
-  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return chains[x] < chains[y]; });
+  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
+    return std::lexicographical_compare(chain.begin() + chain_off[x], chain.begin() + chain_off[x + 1],
+                                        chain.begin() + chain_off[y], chain.begin() + chain_off[y + 1]);
+  });
   double h2 = now_ms();
-  // parse the files in parallel (each is independent), keep Walk order when concatenating
-  struct Parsed { std::vector<std::string> dirs, contents; bool missing = false; };
-  std::vector<Parsed> parsed(nfiles);
+  // parse the files in parallel: thread k takes a contiguous run of files (in Walk order) into its own
+  // arena, so the arenas in thread order are the reference's two lists in order
+  const unsigned nt = host_threads(nfiles, 64);
+  P.arenas.assign(nt + 1, PathArena());  // the last arena holds the preContainerized paths
+  run_threads(nt, [&](unsigned tid) {
+    PathArena& A = P.arenas[tid];
+    A.off.push_back(0);
+    size_t lo = nfiles * tid / nt, hi = nfiles * (tid + 1) / nt;
+    for (size_t k = lo; k < hi; k++) {
+      uint32_t e = ign_entries[order[k]];
+      uint32_t f = tree->entry_child[e];
+      if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
+      uint64_t len;
+      const uint8_t* data = host_file_bytes(tree, f, &len);
+      if (!data) { if (len) A.missing = true; continue; }
+      uint32_t d = tree->entry_dir[e];
+      parse_ignore_file_arena(d == 0 ? clean_root : fast_dir_path(tree, d, clean_root), data, len, &A);
+    }
+  });
   {
-    unsigned nt = std::thread::hardware_concurrency();
-    if (nt == 0) nt = 4;
-    if (nt > 16) nt = 16;
-    if (nt > nfiles / 64 + 1) nt = (unsigned)(nfiles / 64 + 1);
-    std::atomic<size_t> next{0};
-    auto worker = [&]() {
-      for (;;) {
-        size_t k = next.fetch_add(1);
-        if (k >= nfiles) break;
-        uint32_t e = ign_entries[order[k]];
-        uint32_t f = tree->entry_child[e];
-        if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
-        uint64_t len;
-        const uint8_t* data = host_file_bytes(tree, f, &len);
-        if (!data) { parsed[k].missing = len != 0; continue; }
-        uint32_t d = tree->entry_dir[e];
-        std::string fpath = path_join(d == 0 ? root : fast_dir_path(tree, d, clean_root), ".m2kignore");
-        parse_ignore_file(fpath, data, len, &parsed[k].dirs, &parsed[k].contents);
-      }
-    };
-    std::vector<std::thread> th;
-    for (unsigned i = 1; i < nt; i++) th.emplace_back(worker);
-    worker();
-    for (auto& x : th) x.join();
+    PathArena& A = P.arenas[nt];
+    A.off.push_back(0);
+    for (uint32_t i = 0; params && i < params->n_pre; i++) {
+      const char* pp = params->pre_paths[i] ? params->pre_paths[i] : "";
+      A.chars.insert(A.chars.end(), pp, pp + strlen(pp));
+      A.off.push_back((uint32_t)A.chars.size());
+      A.flag.push_back(4);
+    }
   }
-  for (size_t k = 0; k < nfiles; k++) {
-    if (parsed[k].missing) return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
-    for (auto& x : parsed[k].dirs) P.ign_dirs.push_back(std::move(x));
-    for (auto& x : parsed[k].contents) P.ign_contents.push_back(std::move(x));
+  size_t total = 0;
+  std::vector<size_t> abase(P.arenas.size() + 1, 0);
+  for (size_t k = 0; k < P.arenas.size(); k++) {
+    if (P.arenas[k].missing) return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
+    total += P.arenas[k].size();
+    abase[k + 1] = total;
   }
   double h3 = now_ms();
-  // exact hash table over the case-folded entries, keyed by the folded rune sequence;
-  // flags: 1 ignoreDirectories, 2 ignoreContents, 4 preContainerized
-  std::vector<std::string> pre;
-  for (uint32_t i = 0; params && i < params->n_pre; i++) pre.push_back(params->pre_paths[i] ? params->pre_paths[i] : "");
+  // exact hash table over the case-folded entries; flags: 1 ignoreDirectories, 2 ignoreContents,
+  // 4 preContainerized.  Fold + hash in parallel, then insert in parallel into 16 regions selected by
+  // the top bits of the key (each region is its own linear-probing table, so threads never meet).
   const uint64_t seed0 = 0xcbf29ce484222325ull;
-  struct Src { const std::string* s; uint32_t flag; };
-  std::vector<Src> srcs;
-  srcs.reserve(P.ign_dirs.size() + P.ign_contents.size() + pre.size());
-  for (const auto& x : P.ign_dirs) srcs.push_back({&x, 1});
-  for (const auto& x : P.ign_contents) srcs.push_back({&x, 2});
-  for (const auto& x : pre) srcs.push_back({&x, 4});
-  // fold + hash every entry (independent: threads), then insert one after the other into the
-  // open-addressing table that is uploaded as is; equal folded sequences share a slot
-  struct Folded { uint64_t key; uint32_t off, len; };
-  const size_t ns_ = srcs.size();
-  std::vector<Folded> folded(ns_);
-  unsigned nt2 = std::thread::hardware_concurrency();
-  if (nt2 == 0) nt2 = 4;
-  if (nt2 > 16) nt2 = 16;
-  if (nt2 > ns_ / 512 + 1) nt2 = (unsigned)(ns_ / 512 + 1);
+  struct Folded { uint64_t key; uint32_t off, len; uint32_t flag; };
+  std::vector<Folded> folded(total);
+  const unsigned nt2 = host_threads(total, 1024);
   std::vector<std::vector<uint32_t>> rune_parts(nt2);
-  {
-    auto worker = [&](unsigned tid) {
-      size_t lo = ns_ * tid / nt2, hi = ns_ * (tid + 1) / nt2;
-      std::vector<uint32_t>& out = rune_parts[tid];
-      std::vector<uint32_t> tmp;
-      for (size_t i = lo; i < hi; i++) {
-        fold_runes(*srcs[i].s, &tmp);
-        uint64_t h = seed0;
-        for (uint32_t rr : tmp) h = hash_step(h, rr);
-        folded[i] = {hash_finish(h), (uint32_t)out.size(), (uint32_t)tmp.size()};
-        out.insert(out.end(), tmp.begin(), tmp.end());
-      }
-    };
-    std::vector<std::thread> th;
-    for (unsigned i = 1; i < nt2; i++) th.emplace_back(worker, i);
-    worker(0);
-    for (auto& x : th) x.join();
-  }
-  std::vector<uint32_t> runes, root_runes;
-  {
-    size_t total = 0;
-    std::vector<size_t> base(nt2);
-    for (unsigned k = 0; k < nt2; k++) { base[k] = total; total += rune_parts[k].size(); }
-    runes.resize(total);
-    for (unsigned k = 0; k < nt2; k++) {
-      if (!rune_parts[k].empty()) memcpy(runes.data() + base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
-      size_t lo = ns_ * k / nt2, hi = ns_ * (k + 1) / nt2;
-      for (size_t i = lo; i < hi; i++) folded[i].off += (uint32_t)base[k];
-    }
-  }
+  std::vector<uint32_t> root_runes;
   fold_runes(root, &root_runes);
-  size_t n_slots_used = 0;
-  if (ns_) {
-    uint32_t cap = 16;
-    while (cap < ns_ * 2) cap <<= 1;
-    P.table.assign(cap, IgnoreSlot{0, 0, 0, 0, 0});
-    P.table_mask = cap - 1;
-    for (size_t i = 0; i < ns_; i++) {
-      const Folded& fo = folded[i];
-      const uint32_t* rp = runes.data() + fo.off;
-      if (fo.len == root_runes.size() && std::equal(rp, rp + fo.len, root_runes.begin())) P.root_ignore |= (uint8_t)srcs[i].flag;
-      for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
-        IgnoreSlot& sl = P.table[sidx];
-        if (sl.hash == 0) { sl = IgnoreSlot{fo.key, srcs[i].flag, fo.off, fo.len, 0}; n_slots_used++; break; }
-        if (sl.hash == fo.key && sl.len == fo.len && std::equal(rp, rp + fo.len, runes.data() + sl.off)) { sl.flags |= srcs[i].flag; break; }
+  std::atomic<uint32_t> root_flags{0};
+  auto entry_at = [&](size_t g, const char** p, size_t* n, uint32_t* flag) {
+    size_t k = std::upper_bound(abase.begin(), abase.end(), g) - abase.begin() - 1;
+    const PathArena& A = P.arenas[k];
+    size_t i = g - abase[k];
+    *p = A.chars.data() + A.off[i];
+    *n = A.off[i + 1] - A.off[i];
+    *flag = A.flag[i];
+  };
+  run_threads(nt2, [&](unsigned tid) {
+    size_t lo = total * tid / nt2, hi = total * (tid + 1) / nt2;
+    std::vector<uint32_t>& out = rune_parts[tid];
+    out.reserve((hi - lo) * 48);
+    for (size_t g = lo; g < hi; g++) {
+      const char* p; size_t n; uint32_t flag;
+      entry_at(g, &p, &n, &flag);
+      const uint32_t off = (uint32_t)out.size();
+      uint64_t h = seed0;
+      for (size_t i = 0; i < n;) {
+        uint32_t w;
+        uint32_t r = fold_rune(decode_rune(reinterpret_cast<const uint8_t*>(p) + i, n - i, &w), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
+        out.push_back(r);
+        h = hash_step(h, r);
+        i += w;
       }
+      const uint32_t len = (uint32_t)out.size() - off;
+      folded[g] = {hash_finish(h), off, len, flag};
+      if (len == root_runes.size() && std::equal(root_runes.begin(), root_runes.end(), out.begin() + off)) root_flags |= flag;
     }
+  });
+  P.root_ignore = (uint8_t)root_flags.load();
+  std::vector<uint32_t> runes;
+  {
+    size_t tot = 0;
+    std::vector<size_t> base(nt2);
+    for (unsigned k = 0; k < nt2; k++) { base[k] = tot; tot += rune_parts[k].size(); }
+    runes.resize(tot);
+    run_threads(nt2, [&](unsigned k) {
+      if (!rune_parts[k].empty()) memcpy(runes.data() + base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
+      size_t lo = total * k / nt2, hi = total * (k + 1) / nt2;
+      for (size_t g = lo; g < hi; g++) folded[g].off += (uint32_t)base[k];
+    });
   }
   // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
   std::string prefix1 = clean_root;
@@ -691,8 +710,31 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   P.depth1_state = seed0;
   for (uint32_t rr : prefix_runes) P.depth1_state = hash_step(P.depth1_state, rr);
   P.prefix_len = (uint32_t)prefix_runes.size();
-  if (n_slots_used) {
-    const uint32_t cap = P.table_mask + 1;
+  if (total) {
+    uint32_t region_count[kIgnoreRegions] = {0};
+    for (size_t g = 0; g < total; g++) region_count[folded[g].key >> (64 - kIgnoreRegionBits)]++;
+    uint32_t maxc = 1;
+    for (uint32_t c : region_count) maxc = std::max(maxc, c);
+    uint32_t R = 2;
+    while (R < maxc * 2) R <<= 1;
+    P.table.assign((size_t)R * kIgnoreRegions, IgnoreSlot{0, 0, 0, 0, 0});
+    P.table_mask = R - 1;
+    const unsigned nt3 = std::min<unsigned>(host_threads(total, 4096), kIgnoreRegions);
+    run_threads(nt3, [&](unsigned tid) {
+      for (size_t g = 0; g < total; g++) {
+        const Folded& fo = folded[g];
+        const uint32_t region = (uint32_t)(fo.key >> (64 - kIgnoreRegionBits));
+        if (region % nt3 != tid) continue;
+        IgnoreSlot* tab = P.table.data() + (size_t)region * R;
+        const uint32_t* rp = runes.data() + fo.off;
+        for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
+          IgnoreSlot& sl = tab[sidx];
+          if (sl.hash == 0) { sl = IgnoreSlot{fo.key, fo.flag, fo.off, fo.len, 0}; break; }
+          if (sl.hash == fo.key && sl.len == fo.len && std::equal(rp, rp + fo.len, runes.data() + sl.off)) { sl.flags |= fo.flag; break; }
+        }
+      }
+    });
+    const uint32_t cap = R * kIgnoreRegions;
     size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
     if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
       if (t->ign_blob) CU(cudaFree(t->ign_blob));
@@ -717,9 +759,9 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
     P.d_prefix = (const uint32_t*)((char*)t->ign_blob + tb + rb);
   }
-  // result arrays, and the host copy of the name features, while the GPU is still busy
+  // the result shell: its arrays are the device tree's pinned buffers
   {
-    if (dt->pending) { m2k_result_free(dt->pending); dt->pending = nullptr; }
+    if (dt->pending) { m2k_result* old = dt->pending; dt->pending = nullptr; m2k_result_free(old); }
     const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
     m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
     r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
@@ -738,8 +780,8 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   }
   P.ms_host = (float)(now_ms() - h0);
   if (getenv("M2K_DEBUG_TIMING"))
-    fprintf(stderr, "[m2k] prepare: find %.2f ms, order %.2f ms, parse %.2f ms, table+upload %.2f ms (%zu files, %zu+%zu entries)\n",
-            h1 - h0, h2 - h1, h3 - h2, now_ms() - h3, nfiles, P.ign_dirs.size(), P.ign_contents.size());
+    fprintf(stderr, "[m2k] prepare: find %.2f ms, order %.2f ms, parse %.2f ms, table+upload %.2f ms (%zu files, %zu entries)\n",
+            h1 - h0, h2 - h1, h3 - h2, now_ms() - h3, nfiles, total);
   P.ready = true;
   return M2K_OK;
 }
@@ -800,8 +842,8 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   double v0 = now_ms();
   for (uint32_t d = 0; d < nd; d++)
     if (r->dir_state[d] == M2K_DIR_SERVICE) r->service_dirs[r->n_services++] = d;
-  r->n_ignore_dirs = (uint32_t)P.ign_dirs.size(); r->ignore_dirs = dup_list(P.ign_dirs);
-  r->n_ignore_contents = (uint32_t)P.ign_contents.size(); r->ignore_contents = dup_list(P.ign_contents);
+  r->ignore_dirs = list_from_arenas(P.arenas, 1, &r->n_ignore_dirs);
+  r->ignore_contents = list_from_arenas(P.arenas, 2, &r->n_ignore_contents);
   C->phase_ms[6] = (float)(now_ms() - v0);
   P.ready = false;
   r->ms_h2d = dt->ms_h2d;

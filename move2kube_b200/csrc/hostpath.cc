@@ -12,14 +12,12 @@
 
 namespace m2k {
 
-// filepath.Clean for Unix paths: lexical only.
-std::string path_clean(const std::string& p) {
-  if (p.empty()) return ".";
+// filepath.Clean for Unix paths: lexical only.  Writes into out (capacity >= n + 2), returns the length.
+size_t path_clean_buf(const char* p, size_t n, char* out) {
+  if (n == 0) { out[0] = '.'; return 1; }
   const bool rooted = p[0] == '/';
-  const size_t n = p.size();
-  std::string out;
-  out.reserve(n + 1);
-  if (rooted) out += '/';
+  size_t w = 0;
+  if (rooted) out[w++] = '/';
   const size_t floor0 = rooted ? 1 : 0;
   size_t dotdot = floor0;  // output below this index is a run of leading ".." components: never popped
   size_t i = floor0;
@@ -31,22 +29,30 @@ std::string path_clean(const std::string& p) {
     if (len == 1 && p[i] == '.') {
       // skip
     } else if (len == 2 && p[i] == '.' && p[i + 1] == '.') {
-      if (out.size() > dotdot) {  // drop the last component
-        size_t k = out.size() - 1;
+      if (w > dotdot) {  // drop the last component
+        size_t k = w - 1;
         while (k > dotdot && out[k] != '/') k--;
-        out.resize(k);
+        w = k;
       } else if (!rooted) {
-        if (!out.empty()) out += '/';
-        out += "..";
-        dotdot = out.size();
+        if (w) out[w++] = '/';
+        out[w++] = '.'; out[w++] = '.';
+        dotdot = w;
       }
     } else {
-      if (out.size() > floor0) out += '/';
-      out.append(p, i, len);
+      if (w > floor0) out[w++] = '/';
+      memcpy(out + w, p + i, len);
+      w += len;
     }
     i = j;
   }
-  return out.empty() ? "." : out;
+  if (w == 0) out[w++] = '.';
+  return w;
+}
+
+std::string path_clean(const std::string& p) {
+  std::string out(p.size() + 2, '\0');
+  out.resize(path_clean_buf(p.data(), p.size(), &out[0]));
+  return out;
 }
 
 // filepath.Join of two elements: empty elements are dropped, the result is cleaned.
@@ -122,7 +128,19 @@ static void trim_space(const uint8_t*& b, const uint8_t*& e) {
 // file's directory.
 void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64_t len, std::vector<std::string>* ignore_dirs,
                        std::vector<std::string>* ignore_contents) {
-  const std::string dir = path_dir(file_path);
+  PathArena a;
+  parse_ignore_file_arena(path_dir(file_path), data, len, &a);
+  for (size_t i = 0; i < a.size(); i++) {
+    std::string sp(a.chars.data() + a.off[i], a.off[i + 1] - a.off[i]);
+    (a.flag[i] == 2 ? ignore_contents : ignore_dirs)->push_back(sp);
+  }
+}
+
+// Same, appending the cleaned paths to an arena (no allocation per line).  `dir` is the cleaned
+// directory of the file (filepath.Dir of its Walk path); flag 1 = ignoreDirectories, 2 = ignoreContents.
+void parse_ignore_file_arena(const std::string& dir, const uint8_t* data, uint64_t len, PathArena* out) {
+  if (out->off.empty()) out->off.push_back(0);
+  std::string tmp;
   uint64_t pos = 0;
   while (pos < len) {
     const uint8_t* nl = static_cast<const uint8_t*>(memchr(data + pos, '\n', len - pos));
@@ -132,13 +150,20 @@ void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64
     const uint8_t* e = data + end;
     if (e > b && e[-1] == '\r') e--;
     trim_space(b, e);
-    std::string line(reinterpret_cast<const char*>(b), (size_t)(e - b));
-    if (!line.empty() && line.back() == '*') {
-      line.pop_back();
-      ignore_contents->push_back(path_join(dir, line));
-    } else {
-      ignore_dirs->push_back(path_join(dir, line));
+    uint8_t flag = 1;
+    if (e > b && e[-1] == '*') { e--; flag = 2; }
+    // filepath.Join(dir, line): empty elements are dropped, then Clean
+    tmp.assign(dir);
+    if (e > b) {
+      if (!tmp.empty()) tmp += '/';
+      tmp.append(reinterpret_cast<const char*>(b), (size_t)(e - b));
     }
+    size_t at = out->chars.size();
+    out->chars.resize(at + tmp.size() + 2);
+    size_t n = tmp.empty() ? 0 : path_clean_buf(tmp.data(), tmp.size(), out->chars.data() + at);
+    out->chars.resize(at + n);
+    out->off.push_back((uint32_t)out->chars.size());
+    out->flag.push_back(flag);
     pos = end + 1;
   }
 }

@@ -727,8 +727,9 @@ __global__ void __launch_bounds__(128) k_walk_local(uint32_t n_dirs, const uint3
       }
     }
     uint64_t key = hash_finish(h);
+    const IgnoreSlot* region = a.table + (size_t)(key >> (64 - kIgnoreRegionBits)) * (a.table_mask + 1);
     for (uint32_t s = (uint32_t)key & a.table_mask;; s = (s + 1) & a.table_mask) {
-      IgnoreSlot sl = a.table[s];
+      IgnoreSlot sl = region[s];
       if (sl.hash == 0) break;
       if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, sl.len)) { ign = sl.flags; break; }
     }

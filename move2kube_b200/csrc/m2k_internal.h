@@ -35,6 +35,8 @@ struct NameSig {
 };
 constexpr int kMaxNameSigs = 32;
 
+// the ignore table is 16 independent linear-probing regions selected by the top bits of the key
+constexpr uint32_t kIgnoreRegionBits = 4, kIgnoreRegions = 1u << kIgnoreRegionBits;
 struct IgnoreSlot { uint64_t hash; uint32_t flags; uint32_t off; uint32_t len; uint32_t _pad; };  // off/len: folded runes of the entry
 
 // a tree (metadata replicated) plus the bytes of file ids [file_begin, file_end) resident in HBM
@@ -119,6 +121,16 @@ void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
 void set_global_error(const char* msg);  // api.cu: what m2k_global_error() returns on this thread
 
 // ---- host helpers (hostpath.cc) ----
+// cleaned paths packed into one character array: entry i is chars[off[i] .. off[i+1])
+struct PathArena {
+  std::vector<char> chars;
+  std::vector<uint32_t> off;
+  std::vector<uint8_t> flag;
+  bool missing = false;
+  size_t size() const { return flag.size(); }
+};
+size_t path_clean_buf(const char* p, size_t n, char* out);
+void parse_ignore_file_arena(const std::string& dir, const uint8_t* data, uint64_t len, PathArena* out);
 std::string path_clean(const std::string& p);
 std::string path_join(const std::string& a, const std::string& b);
 std::string path_dir(const std::string& p);
