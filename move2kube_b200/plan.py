@@ -40,6 +40,38 @@ class Service:
         return True
 
 
+def service_to_plan_dict(s: "Service", root_dir: str, assets_path: str) -> dict:
+    """One service the way WritePlan stores it (types/plan/planutils.go:164-201): the yaml keys of
+    plan.go:202-215, with the `m2kpath` fields made relative (planutils.go:239-268) -- source and build
+    artifacts to the plan's rootDir, Dockerfile/S2I target options to `m2kassets/...` when they live under
+    the assets directory (builder names of CNB options are not paths and stay as they are)."""
+    import os
+
+    def rel_root(p):
+        try:
+            return os.path.relpath(p, root_dir)
+        except ValueError:
+            return p
+
+    def rel_opt(p):
+        if s.ContainerBuildType not in (DockerFileContainerBuildTypeValue, ReuseDockerFileContainerBuildTypeValue,
+                                        S2IContainerBuildTypeValue):
+            return p
+        ap = os.path.abspath(assets_path)
+        if os.path.abspath(p).startswith(ap + os.sep):
+            return os.path.join("m2kassets", os.path.relpath(os.path.abspath(p), ap))
+        return rel_root(p)
+
+    return {
+        "serviceName": s.ServiceName, "serviceRelPath": s.ServiceRelPath, "image": s.Image,
+        "translationType": s.TranslationType, "containerBuildType": s.ContainerBuildType,
+        "sourceType": list(s.SourceTypes), "targetOptions": [rel_opt(o) for o in s.ContainerizationTargetOptions],
+        "sourceArtifacts": {k: [rel_root(x) for x in v] for k, v in s.SourceArtifacts.items()},
+        "buildArtifacts": {k: [rel_root(x) for x in v] for k, v in s.BuildArtifacts.items()},
+        "updateContainerBuildPipeline": s.UpdateContainerBuildPipeline, "updateDeployPipeline": s.UpdateDeployPipeline,
+    }
+
+
 def NewService(servicename: str, translationtype: str) -> Service:
     """plan.go:217-230."""
     return Service(ServiceName=servicename, Image=servicename + ":latest", TranslationType=translationtype,

@@ -193,8 +193,29 @@ def userscript_spec():
     return {"name": "userscript", "entries": e}
 
 
+def reference_plans(out_dir):
+    """The reference's own golden YAML plans for this path, as JSON (services only):
+    internal/move2kube/testdata/expectedplanfornodejsapp.yaml        <- planner_test.go:99-128
+    internal/source/testdata/expectedservicesfor*.yaml               <- any2kube_test.go:97-286"""
+    import yaml
+    files = {
+        "planfornodejsapp": ("internal/move2kube/testdata/expectedplanfornodejsapp.yaml", "samples_nodejs"),
+        "servicesfornodejsapp": ("internal/source/testdata/expectedservicesfornodejsapp.yaml", "samples_nodejs"),
+        "servicesfornodejsappwithm2kignorecase1": ("internal/source/testdata/expectedservicesfornodejsappwithm2kignorecase1.yaml", "ignorecase1"),
+        "servicesforjavamavenappwithm2kignorecase2": ("internal/source/testdata/expectedservicesforjavamavenappwithm2kignorecase2.yaml", "ignorecase2"),
+    }
+    out = {}
+    for key, (rel_path, tree) in files.items():
+        y = yaml.safe_load(open(os.path.join(REF, rel_path)))
+        out[key] = {"source": rel_path, "tree": tree, "services": y["spec"]["inputs"]["services"]}
+    with open(os.path.join(out_dir, "_reference_plans.json"), "w") as f:
+        json.dump(out, f, indent=1, sort_keys=True)
+    print("reference plans: %d" % len(out))
+
+
 def main():
     out_dir = HERE
+    reference_plans(out_dir)
     tmp = tempfile.mkdtemp(prefix="m2kgold-")
     try:
         s = treespec.spec_from_disk("samples", os.path.join(REF, "samples"))

@@ -11,6 +11,8 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 def load_goldens():
     out = []
     for p in sorted(glob.glob(os.path.join(GOLDEN_DIR, "*.json"))):
+        if os.path.basename(p).startswith("_"):
+            continue
         with open(p) as f:
             out.append(json.load(f))
     return out
@@ -107,3 +109,8 @@ def check(spec, flavor, view, res, root: bytes):
             got = os.fsdecode(os.path.relpath(view.file_rel[f], os.fsencode(rel)))
             assert got in cands
             assert all(v in cands for v in ms["script_said"].values())
+
+
+def reference_plans():
+    with open(os.path.join(GOLDEN_DIR, "_reference_plans.json")) as f:
+        return json.load(f)

@@ -139,3 +139,29 @@ def test_dockerfile_translator_finds_dockerfiles(tmp_path, assets):
     files, err = source.DockerfileTranslator().GetDockerfiles(str(d))
     assert err is None
     assert [os.path.relpath(f, str(d)) for f in files] == ["build.Dockerfile", "svc/Dockerfile"]
+
+
+@pytest.mark.parametrize("key", ["planfornodejsapp", "servicesfornodejsapp", "servicesfornodejsappwithm2kignorecase1",
+                                 "servicesforjavamavenappwithm2kignorecase2"])
+def test_against_the_reference_golden_plans(tmp_path, assets, monkeypatch, key):
+    """The reference's OWN golden YAML files for this path (planner_test.go:99-128, any2kube_test.go:97-286),
+    field by field in the plan's wire format.  They were recorded with Docker available, so the CNB
+    provider hook stands in for the builders' detector; the three any2kube goldens were recorded without the
+    assets directory (only the CNB option), the planner golden with it."""
+    ref = gc.reference_plans()[key]
+    spec = GOLDENS[ref["tree"]]
+    root = treespec.materialize(spec, str(tmp_path / ref["tree"]))
+    if key != "planfornodejsapp":
+        monkeypatch.setattr(containerizer, "AssetsPath", str(tmp_path / "no-assets"))
+    # stand-in for the builder images' detector: what the goldens pin is that both builders accept a
+    # directory holding package.json / pom.xml (SURVEY.md section 8c) and nothing else in these trees
+    monkeypatch.setattr(containerizer.CNBContainerizer, "provider", staticmethod(
+        lambda path, builder: any(os.path.isfile(os.path.join(path, m)) for m in ("package.json", "pom.xml"))))
+    containerizer.CNBContainerizer._cache.clear()
+    services, err = source.Any2KubeTranslator().GetServiceOptions(root, plantypes.NewPlan())
+    assert err is None
+    got = {}
+    for s in services:
+        got.setdefault(s.ServiceName, []).append(plantypes.service_to_plan_dict(s, root, containerizer.AssetsPath))
+    assert got == ref["services"]
+    containerizer.CNBContainerizer._cache.clear()
