@@ -23,16 +23,19 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, defines=(), out=None):
+    """defines/out: build a tuning variant next to the product library (tools/scan_variants.py)."""
+    out = out or OUT
+    if out == OUT and not force and not needs_build():
         return OUT
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-shared", "-o", OUT] + sources() + ["-lpthread"]
+           "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-shared", "-o", out] + ["-D" + d for d in defines] + \
+        sources() + ["-lpthread"]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
     subprocess.check_call(cmd)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

@@ -119,8 +119,21 @@ void launch_name_features(Ctx* c, DevTree* t) {
 //     and does the exact byte count for the (rare) runs of >= 4095 free units.
 // Algorithmic traffic: every content byte read once + 4 B written per 64 KiB.
 // ---------------------------------------------------------------------------------------------
-constexpr int kScanRows = 8;        // rows (512 B each) loaded before use
-constexpr int kScanThreads = 256;
+// tunables (tools/scan_variants.py builds and times alternatives; these defaults won on B200)
+#ifndef M2K_SCAN_ROWS
+#define M2K_SCAN_ROWS 8
+#endif
+#ifndef M2K_SCAN_THREADS
+#define M2K_SCAN_THREADS 256
+#endif
+#ifndef M2K_SCAN_MINBLOCKS
+#define M2K_SCAN_MINBLOCKS 4
+#endif
+#ifndef M2K_SCAN_WAVES
+#define M2K_SCAN_WAVES 8
+#endif
+constexpr int kScanRows = M2K_SCAN_ROWS;        // rows (512 B each) loaded before use
+constexpr int kScanThreads = M2K_SCAN_THREADS;
 
 __device__ __forceinline__ uint32_t has_newline(uint4 v) {
   const uint32_t nl = 0x0A0A0A0Au, ones = 0x01010101u;
@@ -178,7 +191,7 @@ __device__ __noinline__ bool first_word_rules_out_dockerfile(uint4 v) {
   return false;
 }
 
-__global__ void __launch_bounds__(kScanThreads, 4) k_scan_bytes(
+__global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes(
     uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first,
     const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, uint32_t file_begin,
     const uint8_t* __restrict__ bytes, uint64_t shard_byte0, uint32_t* __restrict__ chunk_rec) {
@@ -264,7 +277,7 @@ void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec) {
   if (!t->n_chunks) return;
   uint32_t warps_per_block = kScanThreads / 32;
   uint32_t want = (t->n_chunks + warps_per_block - 1) / warps_per_block;
-  uint32_t cap = (uint32_t)c->sm_count * 4 * 8;  // resident blocks x 8 waves of items per warp slot
+  uint32_t cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS * M2K_SCAN_WAVES;  // resident blocks x waves
   uint32_t blocks = want < cap ? want : cap;
   k_scan_bytes<<<blocks, kScanThreads, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
                                                        t->file_len, t->file_begin, t->bytes, t->shard_byte0, chunk_rec);

@@ -9,7 +9,7 @@ import os
 from . import _abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libm2kdetect.so")
+LIB_PATH = os.environ.get("M2K_LIB") or os.path.join(HERE, "libm2kdetect.so")  # M2K_LIB: a tuning variant
 
 _lib = None
 

@@ -150,7 +150,8 @@ def test_against_the_reference_golden_plans(tmp_path, assets, monkeypatch, key):
     assets directory (only the CNB option), the planner golden with it."""
     ref = gc.reference_plans()[key]
     spec = GOLDENS[ref["tree"]]
-    root = treespec.materialize(spec, str(tmp_path / ref["tree"]))
+    # the service is named after the directory: samples/nodejs in the reference
+    root = treespec.materialize(spec, str(tmp_path / ("nodejs" if ref["tree"] == "samples_nodejs" else ref["tree"])))
     if key != "planfornodejsapp":
         monkeypatch.setattr(containerizer, "AssetsPath", str(tmp_path / "no-assets"))
     # stand-in for the builder images' detector: what the goldens pin is that both builders accept a
