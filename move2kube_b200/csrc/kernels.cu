@@ -130,7 +130,7 @@ void launch_name_features(Ctx* c, DevTree* t) {
 #define M2K_SCAN_MINBLOCKS 4
 #endif
 #ifndef M2K_SCAN_WAVES
-#define M2K_SCAN_WAVES 8
+#define M2K_SCAN_WAVES 32
 #endif
 constexpr int kScanRows = M2K_SCAN_ROWS;        // rows (512 B each) loaded before use
 constexpr int kScanThreads = M2K_SCAN_THREADS;
