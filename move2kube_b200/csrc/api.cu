@@ -24,7 +24,6 @@ constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2k
 struct IgnorePrep {
   bool ready = false;
   std::vector<PathArena> arenas;  // cleaned entries in the reference's list order; the last arena = preContainerized
-  std::vector<IgnoreSlot> table;
   uint32_t table_mask = M2K_NONE, prefix_len = 0;
   uint64_t depth1_state = 0;
   uint8_t root_ignore = 0;
@@ -32,7 +31,7 @@ struct IgnorePrep {
   const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
   float ms_host = 0.f;
   void reset() {
-    ready = false; arenas.clear(); table.clear(); table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
+    ready = false; arenas.clear(); table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
     d_table = nullptr; d_runes = d_prefix = nullptr; ms_host = 0.f;
   }
 };
@@ -690,18 +689,9 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     }
   });
   P.root_ignore = (uint8_t)root_flags.load();
-  std::vector<uint32_t> runes;
-  {
-    size_t tot = 0;
-    std::vector<size_t> base(nt2);
-    for (unsigned k = 0; k < nt2; k++) { base[k] = tot; tot += rune_parts[k].size(); }
-    runes.resize(tot);
-    run_threads(nt2, [&](unsigned k) {
-      if (!rune_parts[k].empty()) memcpy(runes.data() + base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
-      size_t lo = total * k / nt2, hi = total * (k + 1) / nt2;
-      for (size_t g = lo; g < hi; g++) folded[g].off += (uint32_t)base[k];
-    });
-  }
+  size_t n_runes = 0;
+  std::vector<size_t> rune_base(nt2);
+  for (unsigned k = 0; k < nt2; k++) { rune_base[k] = n_runes; n_runes += rune_parts[k].size(); }
   // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
   std::string prefix1 = clean_root;
   if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
@@ -715,27 +705,11 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     for (size_t g = 0; g < total; g++) region_count[folded[g].key >> (64 - kIgnoreRegionBits)]++;
     uint32_t maxc = 1;
     for (uint32_t c : region_count) maxc = std::max(maxc, c);
-    uint32_t R = 2;
-    while (R < maxc * 2) R <<= 1;
-    P.table.assign((size_t)R * kIgnoreRegions, IgnoreSlot{0, 0, 0, 0, 0});
+    uint32_t R = 4;
+    while ((uint64_t)R * 3 < (uint64_t)maxc * 4) R <<= 1;  // load factor <= 0.75 in the fullest region
     P.table_mask = R - 1;
-    const unsigned nt3 = std::min<unsigned>(host_threads(total, 4096), kIgnoreRegions);
-    run_threads(nt3, [&](unsigned tid) {
-      for (size_t g = 0; g < total; g++) {
-        const Folded& fo = folded[g];
-        const uint32_t region = (uint32_t)(fo.key >> (64 - kIgnoreRegionBits));
-        if (region % nt3 != tid) continue;
-        IgnoreSlot* tab = P.table.data() + (size_t)region * R;
-        const uint32_t* rp = runes.data() + fo.off;
-        for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
-          IgnoreSlot& sl = tab[sidx];
-          if (sl.hash == 0) { sl = IgnoreSlot{fo.key, fo.flag, fo.off, fo.len, 0}; break; }
-          if (sl.hash == fo.key && sl.len == fo.len && std::equal(rp, rp + fo.len, runes.data() + sl.off)) { sl.flags |= fo.flag; break; }
-        }
-      }
-    });
     const uint32_t cap = R * kIgnoreRegions;
-    size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * runes.size(), pb = 4 * prefix_runes.size();
+    const size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * n_runes, pb = 4 * prefix_runes.size();
     if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
       if (t->ign_blob) CU(cudaFree(t->ign_blob));
       t->ign_blob = nullptr; t->ign_blob_cap = 0;
@@ -743,17 +717,41 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
       CU(cudaMalloc(&t->ign_blob, want));
       t->ign_blob_cap = want;
     }
-    // staged through a pinned buffer kept with the device tree: a copy from pageable memory would
-    // make this call wait for the byte scan that is queued ahead of it on the stream
+    // table and runes are built in place in a pinned staging buffer kept with the device tree (a copy
+    // from pageable memory would make this call wait for the byte scan queued ahead of it)
     if (tb + rb + pb > dt->h_ign_cap) {
       if (dt->h_ign) cudaFreeHost(dt->h_ign);
       dt->h_ign = nullptr; dt->h_ign_cap = 0;
       CU(cudaHostAlloc(&dt->h_ign, (tb + rb + pb) * 2, cudaHostAllocDefault));
       dt->h_ign_cap = (tb + rb + pb) * 2;
     }
-    memcpy(dt->h_ign, P.table.data(), tb);
-    if (rb) memcpy((char*)dt->h_ign + tb, runes.data(), rb);
+    IgnoreSlot* table = static_cast<IgnoreSlot*>(dt->h_ign);
+    uint32_t* runes = reinterpret_cast<uint32_t*>((char*)dt->h_ign + tb);
+    run_threads(nt2, [&](unsigned k) {
+      if (!rune_parts[k].empty()) memcpy(runes + rune_base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
+      size_t lo = total * k / nt2, hi = total * (k + 1) / nt2;
+      for (size_t g = lo; g < hi; g++) folded[g].off += (uint32_t)rune_base[k];
+    });
     if (pb) memcpy((char*)dt->h_ign + tb + rb, prefix_runes.data(), pb);
+    const unsigned nt3 = std::min<unsigned>(host_threads(total, 2048), kIgnoreRegions);
+    run_threads(nt3, [&](unsigned tid) {
+      for (uint32_t region = tid; region < kIgnoreRegions; region += nt3) memset(table + (size_t)region * R, 0, sizeof(IgnoreSlot) * R);
+      for (size_t g = 0; g < total; g++) {
+        const Folded& fo = folded[g];
+        const uint32_t region = (uint32_t)(fo.key >> (64 - kIgnoreRegionBits));
+        if (region % nt3 != tid) continue;
+        IgnoreSlot* tab = table + (size_t)region * R;
+        const uint32_t* rp = runes + fo.off;
+        for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
+          IgnoreSlot& sl = tab[sidx];
+          if (sl.hash == 0) { sl = IgnoreSlot{fo.key, fo.off, slot_pack(fo.len, fo.flag)}; break; }
+          if (sl.hash == fo.key && slot_len(sl.len_flags) == fo.len && std::equal(rp, rp + fo.len, runes + sl.off)) {
+            sl.len_flags |= slot_pack(0, fo.flag);
+            break;
+          }
+        }
+      }
+    });
     CU(cudaMemcpyAsync(t->ign_blob, dt->h_ign, tb + rb + pb, cudaMemcpyHostToDevice, s));
     P.d_table = (const IgnoreSlot*)t->ign_blob;
     P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
@@ -776,6 +774,8 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     r->dir_ignore = b; b += nd;
     r->file_flags = b;
     r->entry_feat = dt->h_entry_feat;
+    r->ignore_dirs = list_from_arenas(P.arenas, 1, &r->n_ignore_dirs);
+    r->ignore_contents = list_from_arenas(P.arenas, 2, &r->n_ignore_contents);
     dt->pending = r;
   }
   P.ms_host = (float)(now_ms() - h0);
@@ -842,8 +842,7 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   double v0 = now_ms();
   for (uint32_t d = 0; d < nd; d++)
     if (r->dir_state[d] == M2K_DIR_SERVICE) r->service_dirs[r->n_services++] = d;
-  r->ignore_dirs = list_from_arenas(P.arenas, 1, &r->n_ignore_dirs);
-  r->ignore_contents = list_from_arenas(P.arenas, 2, &r->n_ignore_contents);
+  // (the two ignore lists were filled in by m2k_prepare, under the byte scan)
   C->phase_ms[6] = (float)(now_ms() - v0);
   P.ready = false;
   r->ms_h2d = dt->ms_h2d;

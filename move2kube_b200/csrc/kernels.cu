@@ -744,7 +744,7 @@ __global__ void __launch_bounds__(128) k_walk_local(uint32_t n_dirs, const uint3
     for (uint32_t s = (uint32_t)key & a.table_mask;; s = (s + 1) & a.table_mask) {
       IgnoreSlot sl = region[s];
       if (sl.hash == 0) break;
-      if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, sl.len)) { ign = sl.flags; break; }
+      if (sl.hash == key && path_equals_entry(a, d, a.runes + sl.off, slot_len(sl.len_flags))) { ign = slot_flags(sl.len_flags); break; }
     }
   }
   a.dir_ignore[d] = (uint8_t)ign;

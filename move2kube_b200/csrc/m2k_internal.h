@@ -37,7 +37,10 @@ constexpr int kMaxNameSigs = 32;
 
 // the ignore table is 16 independent linear-probing regions selected by the top bits of the key
 constexpr uint32_t kIgnoreRegionBits = 4, kIgnoreRegions = 1u << kIgnoreRegionBits;
-struct IgnoreSlot { uint64_t hash; uint32_t flags; uint32_t off; uint32_t len; uint32_t _pad; };  // off/len: folded runes of the entry
+struct IgnoreSlot { uint64_t hash; uint32_t off; uint32_t len_flags; };  // folded runes [off, off+len); flags in the top 3 bits
+__host__ __device__ inline uint32_t slot_pack(uint32_t len, uint32_t flags) { return len | (flags << 29); }
+__host__ __device__ inline uint32_t slot_len(uint32_t lf) { return lf & 0x1FFFFFFFu; }
+__host__ __device__ inline uint32_t slot_flags(uint32_t lf) { return lf >> 29; }
 
 // a tree (metadata replicated) plus the bytes of file ids [file_begin, file_end) resident in HBM
 struct DevTree {
