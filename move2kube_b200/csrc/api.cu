@@ -8,6 +8,9 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include <unordered_map>
 
@@ -559,12 +562,61 @@ static unsigned host_threads(size_t work_items, size_t per_thread) {
   return nt;
 }
 
+// A small persistent team of host threads for the parse / fold / insert phases of m2k_prepare:
+// spawning up to 32 threads four times per pass cost more than the work itself.  Created on first
+// use, kept for the life of the process (never joined: the workers sleep on a condition variable).
+class HostTeam {
+ public:
+  static HostTeam& get() { static HostTeam* t = new HostTeam(); return *t; }
+  void run(unsigned nt, const std::function<void(unsigned)>& fn) {
+    if (nt <= 1) { fn(0); return; }
+    if (nt > workers_ + 1) nt = workers_ + 1;
+    {
+      std::lock_guard<std::mutex> lk(m_);
+      job_ = &fn; active_ = nt - 1; remaining_ = nt - 1; gen_++;
+    }
+    cv_.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lk(m_);
+    done_.wait(lk, [&] { return remaining_ == 0; });
+    job_ = nullptr;
+  }
+  unsigned size() const { return workers_ + 1; }
+
+ private:
+  HostTeam() {
+    unsigned hw = std::thread::hardware_concurrency();
+    if (hw == 0) hw = 4;
+    workers_ = std::min(hw, 32u) - 1;
+    for (unsigned i = 1; i <= workers_; i++) std::thread([this, i] { loop(i); }).detach();
+  }
+  void loop(unsigned id) {
+    uint64_t seen = 0;
+    for (;;) {
+      const std::function<void(unsigned)>* job = nullptr;
+      {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (id <= active_) job = job_;
+      }
+      if (!job) continue;
+      (*job)(id);
+      std::lock_guard<std::mutex> lk(m_);
+      if (--remaining_ == 0) done_.notify_one();
+    }
+  }
+  std::mutex m_;
+  std::condition_variable cv_, done_;
+  const std::function<void(unsigned)>* job_ = nullptr;
+  unsigned workers_ = 0, active_ = 0, remaining_ = 0;
+  uint64_t gen_ = 0;
+};
+
 template <typename F>
 static void run_threads(unsigned nt, F&& fn) {
-  std::vector<std::thread> th;
-  for (unsigned i = 1; i < nt; i++) th.emplace_back(fn, i);
-  fn(0u);
-  for (auto& x : th) x.join();
+  std::function<void(unsigned)> f = fn;
+  HostTeam::get().run(nt, f);
 }
 
 static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* params) {
