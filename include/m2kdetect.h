@@ -232,6 +232,13 @@ int m2k_file_flags_set(m2k_ctx* ctx, m2k_devtree* dt, const uint8_t* d_src);
  * parse the .m2kignore files the name kernel found and upload the lookup table -- while the byte scan
  * is still running on the GPU.  m2k_finalize does it itself when this was not called. */
 int m2k_prepare(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
+/* diagnostic, no counterpart in the reference and no device needed: runs only the HOST half of
+ * m2k_prepare (order the rule files like filepath.Walk, parse, Clean/Join, fold, build the table, the
+ * two lists) `reps` times on a tree whose rule files are readable on the host, and reports the best
+ * time of each part in ms_best[6] = {all, order, parse, fold, table, lists}.  It produces no
+ * detection result: it exists so that this serial stretch of a multi-GPU pass can be timed alone. */
+int m2k_host_prepare_probe(const m2k_tree* tree, const m2k_detect_params* params, uint32_t reps, double* ms_best,
+                           uint32_t* n_rule_files, uint32_t* n_rules);
 /* phase C: subtree OR, predicate combine, ignore join, prune; copies results to the host */
 int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params, m2k_result** out);
 void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt);

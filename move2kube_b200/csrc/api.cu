@@ -24,17 +24,51 @@ struct m2k_ctx { Ctx c; };
 constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2kignore, user detect scripts) listed by the device
 
 // what m2k_prepare / m2k_finalize derive from the .m2kignore files (host side of a2 / a4)
+struct Folded { uint64_t key; uint32_t off, len, flag; };  // one ignore entry: hash of its folded runes, where they are
+
+// grow-only host buffer the ignore table is built in.  Pinned in the product: a copy from pageable
+// memory would make m2k_prepare wait for the byte scan queued ahead of it.
+struct Staging {
+  void* p = nullptr;
+  size_t cap = 0;
+  bool pinned = true;
+  // room for `bytes`; the first `keep` bytes survive a reallocation
+  bool reserve(size_t bytes, size_t keep) {
+    if (bytes <= cap) return true;
+    const size_t want = bytes * 2;
+    void* q = nullptr;
+    if (pinned) { if (cudaHostAlloc(&q, want, cudaHostAllocDefault) != cudaSuccess) return false; }
+    else if (!(q = malloc(want))) return false;
+    if (keep) memcpy(q, p, keep);
+    release();
+    p = q; cap = want;
+    return true;
+  }
+  void release() {
+    if (p) { if (pinned) cudaFreeHost(p); else free(p); }
+    p = nullptr; cap = 0;
+  }
+};
+
 struct IgnorePrep {
   bool ready = false;
-  std::vector<PathArena> arenas;  // cleaned entries in the reference's list order; the last arena = preContainerized
+  // cleaned entries in the reference's list order; the last arena = preContainerized.  The vectors
+  // below keep their capacity from pass to pass (fresh megabytes cost more in page faults than the work)
+  std::vector<PathArena> arenas;
+  std::vector<uint32_t> ign_entries;
+  std::vector<Folded> folded;
   uint32_t table_mask = M2K_NONE, prefix_len = 0;
   uint64_t depth1_state = 0;
   uint8_t root_ignore = 0;
+  // layout of the staged blob: folded runes, the folded depth-1 prefix, then (16-byte aligned) the table
+  size_t blob_bytes = 0, off_prefix = 0, off_table = 0;
   const IgnoreSlot* d_table = nullptr;
   const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
   float ms_host = 0.f;
+  double ms_part[5] = {0, 0, 0, 0, 0};  // order, parse, fold, table, lists
   void reset() {
-    ready = false; arenas.clear(); table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
+    ready = false; table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
+    blob_bytes = off_prefix = off_table = 0;
     d_table = nullptr; d_runes = d_prefix = nullptr; ms_host = 0.f;
   }
 };
@@ -44,10 +78,9 @@ struct m2k_devtree {
   float ms_h2d = 0.f;
   uint32_t* h_entry_feat = nullptr;  // pinned
   uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
-  void* h_ign = nullptr;             // pinned staging of the ignore table (grow-only)
+  Staging stage;                     // pinned staging of the ignore table (grow-only)
   m2k_result* pending = nullptr;     // result shell made by m2k_prepare
   uint8_t* h_results = nullptr;      // pinned: every per-directory / per-file result array (see result_layout)
-  size_t h_ign_cap = 0;
   bool content = true;
   IgnorePrep prep;
 };
@@ -146,6 +179,8 @@ extern "C" int m2k_ctx_create(int device, m2k_ctx** out) {
   CUX(cudaSetDevice(device));
   CUX(cudaStreamCreateWithFlags(&C->stream, cudaStreamNonBlocking));
   for (auto& ev : C->ev) CUX(cudaEventCreate(&ev));
+  CUX(cudaStreamCreateWithFlags(&C->copy_stream, cudaStreamNonBlocking));
+  for (cudaEvent_t* ev : {&C->ev_names, &C->ev_feat, &C->ev_blob, &C->ev_fork, &C->ev_join}) CUX(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
   CUX(cudaDeviceGetAttribute(&C->sm_count, cudaDevAttrMultiProcessorCount, device));
   CUX(cudaMalloc(&C->d_fold_from, sizeof(m2k_casefold_from)));
   CUX(cudaMalloc(&C->d_fold_to, sizeof(m2k_casefold_to)));
@@ -165,9 +200,12 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   Ctx* C = &ctx->c;
   cudaSetDevice(C->device);
   if (C->stream) cudaStreamSynchronize(C->stream);
+  if (C->copy_stream) cudaStreamSynchronize(C->copy_stream);
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join}) if (ev) cudaEventDestroy(ev);
   if (C->stream) cudaStreamDestroy(C->stream);
+  if (C->copy_stream) cudaStreamDestroy(C->copy_stream);
   delete ctx;
 }
 
@@ -263,7 +301,7 @@ static void devtree_release(DevTree* t) {
 static void free_devtree_shell(m2k_devtree* dt) {
   if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
   if (dt->h_special) cudaFreeHost(dt->h_special);
-  if (dt->h_ign) cudaFreeHost(dt->h_ign);
+  dt->stage.release();
   if (dt->h_results) cudaFreeHost(dt->h_results);
   if (dt->pending) { m2k_result* p = dt->pending; dt->pending = nullptr; p->owner = nullptr; m2k_result_free(p); }
   delete dt;
@@ -271,7 +309,7 @@ static void free_devtree_shell(m2k_devtree* dt) {
 
 extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (!dt) return;
-  if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); }
+  if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); cudaStreamSynchronize(ctx->c.copy_stream); }
   devtree_release(&dt->t);
   free_devtree_shell(dt);
 }
@@ -401,6 +439,7 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaSetDevice(C->device));
   cudaStream_t s = C->stream;
   const bool content = !(params && params->skip_content);
+  CU(cudaStreamWaitEvent(s, C->ev_feat, 0));  // a previous pass's copy of the name features may still be reading them
   CU(cudaMemsetAsync(t->dir_direct, 0, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_first_war, 0xFF, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
@@ -410,9 +449,13 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   dt->prep.ready = false;
   CU(cudaEventRecord(C->ev[8], s));
   launch_name_features(C, t);
-  // the host needs the name features (which entries are .m2kignore files) while the byte scan runs
-  CU(cudaMemcpyAsync(dt->h_special, t->special, 4ull * (kSpecialCap + 1), cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, s));
+  // the host needs the name features (which entries are .m2kignore files) while the byte scan runs:
+  // they go down on the copy stream, so the byte scan starts right behind the name kernel
+  CU(cudaEventRecord(C->ev_names, s));
+  CU(cudaStreamWaitEvent(C->copy_stream, C->ev_names, 0));
+  CU(cudaMemcpyAsync(dt->h_special, t->special, 4ull * (kSpecialCap + 1), cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaEventRecord(C->ev_feat, C->copy_stream));
   CU(cudaEventRecord(C->ev[2], s));
   dt->content = content;
   if (content) {
@@ -482,33 +525,15 @@ extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t*
 // ---- phase C --------------------------------------------------------------------------------
 namespace {
 
-// entries in filepath.Walk order: climb to the common directory, then compare entry indices there
-bool walk_before(const m2k_tree* t, uint32_t a, uint32_t b) {
-  if (a == b) return false;
-  // chains of (entry) from the entry up to the root's children
-  auto chain = [&](uint32_t e, std::vector<uint32_t>* out) {
-    out->clear();
-    for (;;) {
-      out->push_back(e);
-      uint32_t d = t->entry_dir[e];
-      if (d == 0) break;
-      e = t->dir_entry[d];
-    }
-    std::reverse(out->begin(), out->end());
-  };
-  std::vector<uint32_t> ca, cb;
-  chain(a, &ca); chain(b, &cb);
-  size_t n = std::min(ca.size(), cb.size());
-  for (size_t i = 0; i < n; i++) if (ca[i] != cb[i]) return ca[i] < cb[i];
-  return ca.size() < cb.size();  // an ancestor directory comes before its contents
-}
-
 const uint8_t* host_file_bytes(const m2k_tree* t, uint32_t f, uint64_t* len) {
   *len = t->file_len[f];
-  // synthetic trees keep their rule files as literals (their bytes may live on another rank's shard)
+  // synthetic trees keep their rule files as literals (their bytes may live on another rank's shard);
+  // the generator numbers files in increasing order, so literal_file is sorted
   const TreeOwner* o = static_cast<const TreeOwner*>(t->owner);
-  if (o) for (size_t k = 0; k < o->literal_file.size(); k++)
-    if (o->literal_file[k] == f) return reinterpret_cast<const uint8_t*>(o->literal_data[k].data());
+  if (o && !o->literal_file.empty()) {
+    auto it = std::lower_bound(o->literal_file.begin(), o->literal_file.end(), f);
+    if (it != o->literal_file.end() && *it == f) return reinterpret_cast<const uint8_t*>(o->literal_data[it - o->literal_file.begin()].data());
+  }
   if (t->bytes) return t->bytes + t->file_off[f];
   return nullptr;
 }
@@ -619,60 +644,28 @@ static void run_threads(unsigned nt, F&& fn) {
   HostTeam::get().run(nt, f);
 }
 
-static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* params) {
-  DevTree* t = &dt->t;
-  IgnorePrep& P = dt->prep;
-  const m2k_tree* tree = t->host;
-  cudaStream_t s = C->stream;
-  CU(cudaEventSynchronize(C->ev[2]));  // name features and the special-entry list are on the host now
-  double h0 = now_ms();
-  P.reset();
+// The host half of m2k_prepare: P.ign_entries (the .m2kignore entries, any order) -> the two cleaned
+// lists (P.arenas) and the staged blob (folded runes, depth-1 prefix, hash table) in S.  No CUDA
+// calls except the staging allocation.  Returns 0, or an M2K_ERR_* with *err set.
+static int prepare_host(const m2k_tree* tree, const m2k_detect_params* params, IgnorePrep& P, Staging& S, std::string* err) {
+  double h1 = now_ms();
   const std::string root = tree->root_path ? tree->root_path : "";
   const std::string clean_root = path_clean(root);
-  // the .m2kignore files: from the compacted list of special entries, or a scan of all features if it overflowed
-  std::vector<uint32_t> ign_entries;
-  const uint32_t n_special = dt->h_special[0];
-  if (n_special <= kSpecialCap) {
-    for (uint32_t i = 0; i < n_special; i++) {
-      uint32_t e = dt->h_special[1 + i];
-      if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
-    }
-  } else {
-    for (uint32_t e = 0; e < t->n_entries; e++) if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) ign_entries.push_back(e);
-  }
-  double h1 = now_ms();
-  // filepath.Walk order: compare the chains of entry indices from the root down (one flat array)
+  std::vector<uint32_t>& ign_entries = P.ign_entries;
+  sort_walk_order(tree, &ign_entries);  // getIgnorePaths reads the files in the order GetFilesByName found them
   const size_t nfiles = ign_entries.size();
-  std::vector<uint32_t> chain_off(nfiles + 1, 0), chain;
-  chain.reserve(nfiles * 8);
-  for (size_t i = 0; i < nfiles; i++) {
-    size_t at = chain.size();
-    for (uint32_t e = ign_entries[i];;) {
-      chain.push_back(e);
-      uint32_t d = tree->entry_dir[e];
-      if (d == 0) break;
-      e = tree->dir_entry[d];
-    }
-    std::reverse(chain.begin() + at, chain.end());
-    chain_off[i + 1] = (uint32_t)chain.size();
-  }
-  std::vector<uint32_t> order(nfiles);
-  for (size_t i = 0; i < nfiles; i++) order[i] = (uint32_t)i;
-  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
-    return std::lexicographical_compare(chain.begin() + chain_off[x], chain.begin() + chain_off[x + 1],
-                                        chain.begin() + chain_off[y], chain.begin() + chain_off[y + 1]);
-  });
   double h2 = now_ms();
   // parse the files in parallel: thread k takes a contiguous run of files (in Walk order) into its own
   // arena, so the arenas in thread order are the reference's two lists in order
   const unsigned nt = host_threads(nfiles, 64);
-  P.arenas.assign(nt + 1, PathArena());  // the last arena holds the preContainerized paths
+  P.arenas.resize(nt + 1);  // the last arena holds the preContainerized paths
+  for (PathArena& A : P.arenas) { A.chars.clear(); A.off.clear(); A.flag.clear(); A.missing = false; }
   run_threads(nt, [&](unsigned tid) {
     PathArena& A = P.arenas[tid];
     A.off.push_back(0);
     size_t lo = nfiles * tid / nt, hi = nfiles * (tid + 1) / nt;
     for (size_t k = lo; k < hi; k++) {
-      uint32_t e = ign_entries[order[k]];
+      uint32_t e = ign_entries[k];
       uint32_t f = tree->entry_child[e];
       if ((tree->entry_type[e] >> 4) != M2K_T_REG || f == M2K_NONE) continue;  // os.Open / read fails: no lines
       uint64_t len;
@@ -692,58 +685,24 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
       A.flag.push_back(4);
     }
   }
-  size_t total = 0;
-  std::vector<size_t> abase(P.arenas.size() + 1, 0);
+  size_t total = 0, total_chars = 0;
+  std::vector<size_t> abase(P.arenas.size() + 1, 0), cbase(P.arenas.size() + 1, 0);
   for (size_t k = 0; k < P.arenas.size(); k++) {
-    if (P.arenas[k].missing) return fail(C, M2K_ERR_ARG, ".m2kignore content is not available on the host (tree->bytes is NULL)");
+    if (P.arenas[k].missing) { *err = ".m2kignore content is not available on the host (tree->bytes is NULL)"; return M2K_ERR_ARG; }
     total += P.arenas[k].size();
+    total_chars += P.arenas[k].chars.size();
     abase[k + 1] = total;
+    cbase[k + 1] = total_chars;
   }
   double h3 = now_ms();
   // exact hash table over the case-folded entries; flags: 1 ignoreDirectories, 2 ignoreContents,
-  // 4 preContainerized.  Fold + hash in parallel, then insert in parallel into 16 regions selected by
-  // the top bits of the key (each region is its own linear-probing table, so threads never meet).
+  // 4 preContainerized.  Fold + hash in parallel, straight into the staging buffer: an entry's runes go
+  // where its characters are in the concatenated arenas (a rune is at least one byte), so no thread
+  // needs another's count.  Then insert in parallel into 16 regions selected by the top bits of the
+  // key (each region is its own linear-probing table, so threads never meet).
   const uint64_t seed0 = 0xcbf29ce484222325ull;
-  struct Folded { uint64_t key; uint32_t off, len; uint32_t flag; };
-  std::vector<Folded> folded(total);
-  const unsigned nt2 = host_threads(total, 1024);
-  std::vector<std::vector<uint32_t>> rune_parts(nt2);
   std::vector<uint32_t> root_runes;
   fold_runes(root, &root_runes);
-  std::atomic<uint32_t> root_flags{0};
-  auto entry_at = [&](size_t g, const char** p, size_t* n, uint32_t* flag) {
-    size_t k = std::upper_bound(abase.begin(), abase.end(), g) - abase.begin() - 1;
-    const PathArena& A = P.arenas[k];
-    size_t i = g - abase[k];
-    *p = A.chars.data() + A.off[i];
-    *n = A.off[i + 1] - A.off[i];
-    *flag = A.flag[i];
-  };
-  run_threads(nt2, [&](unsigned tid) {
-    size_t lo = total * tid / nt2, hi = total * (tid + 1) / nt2;
-    std::vector<uint32_t>& out = rune_parts[tid];
-    out.reserve((hi - lo) * 48);
-    for (size_t g = lo; g < hi; g++) {
-      const char* p; size_t n; uint32_t flag;
-      entry_at(g, &p, &n, &flag);
-      const uint32_t off = (uint32_t)out.size();
-      uint64_t h = seed0;
-      for (size_t i = 0; i < n;) {
-        uint32_t w;
-        uint32_t r = fold_rune(decode_rune(reinterpret_cast<const uint8_t*>(p) + i, n - i, &w), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N);
-        out.push_back(r);
-        h = hash_step(h, r);
-        i += w;
-      }
-      const uint32_t len = (uint32_t)out.size() - off;
-      folded[g] = {hash_finish(h), off, len, flag};
-      if (len == root_runes.size() && std::equal(root_runes.begin(), root_runes.end(), out.begin() + off)) root_flags |= flag;
-    }
-  });
-  P.root_ignore = (uint8_t)root_flags.load();
-  size_t n_runes = 0;
-  std::vector<size_t> rune_base(nt2);
-  for (unsigned k = 0; k < nt2; k++) { rune_base[k] = n_runes; n_runes += rune_parts[k].size(); }
   // folded prefix shared by all depth-1 directories: Clean(root) + "/" (Join semantics)
   std::string prefix1 = clean_root;
   if (prefix1 == ".") prefix1 = ""; else if (prefix1 != "/") prefix1 += "/";
@@ -752,40 +711,63 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
   P.depth1_state = seed0;
   for (uint32_t rr : prefix_runes) P.depth1_state = hash_step(P.depth1_state, rr);
   P.prefix_len = (uint32_t)prefix_runes.size();
+  P.root_ignore = 0;
+  double h4 = h3, h5 = h3;
   if (total) {
+    if (total_chars >= (1ull << 29)) { *err = "the ignore rules hold more than 2^29 characters"; return M2K_ERR_LIMIT; }
+    const size_t rb = 4 * total_chars, pb = 4 * prefix_runes.size();
+    P.off_prefix = rb;
+    P.off_table = (rb + pb + 15) & ~(size_t)15;
+    // first guess of the table size (regions evenly filled); corrected once the keys are known
+    uint32_t R = 4;
+    while ((uint64_t)R * 3 * kIgnoreRegions < (uint64_t)total * 5) R <<= 1;
+    if (!S.reserve(P.off_table + sizeof(IgnoreSlot) * R * kIgnoreRegions, 0)) { *err = "out of pinned host memory for the ignore table"; return M2K_ERR_NOMEM; }
+    P.folded.resize(total);
+    std::vector<Folded>& folded = P.folded;
+    uint32_t* runes = static_cast<uint32_t*>(S.p);
+    const unsigned nt2 = host_threads(total, 1024);
+    std::atomic<uint32_t> root_flags{0};
+    run_threads(nt2, [&](unsigned tid) {
+      size_t lo = total * tid / nt2, hi = total * (tid + 1) / nt2;
+      size_t k = std::upper_bound(abase.begin(), abase.end(), lo) - abase.begin() - 1;
+      for (size_t g = lo; g < hi; g++) {
+        while (g >= abase[k + 1]) k++;
+        const PathArena& A = P.arenas[k];
+        const size_t i = g - abase[k];
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(A.chars.data()) + A.off[i];
+        const size_t n = A.off[i + 1] - A.off[i];
+        const uint32_t off = (uint32_t)(cbase[k] + A.off[i]);
+        uint32_t* out = runes + off;
+        uint32_t len = 0;
+        uint64_t h = seed0;
+        for (size_t j = 0; j < n;) {
+          uint32_t r;
+          if (p[j] < 0x80) { r = p[j]; if (r - 'A' < 26u) r += 32; j++; }  // same as fold_rune's ASCII branch
+          else { uint32_t w; r = fold_rune(decode_rune(p + j, n - j, &w), m2k_casefold_from, m2k_casefold_to, M2K_CASEFOLD_N); j += w; }
+          out[len++] = r;
+          h = hash_step(h, r);
+        }
+        folded[g] = {hash_finish(h), off, len, A.flag[i]};
+        if (len == root_runes.size() && std::equal(root_runes.begin(), root_runes.end(), out)) root_flags |= A.flag[i];
+      }
+    });
+    P.root_ignore = (uint8_t)root_flags.load();
+    h4 = now_ms();
     uint32_t region_count[kIgnoreRegions] = {0};
     for (size_t g = 0; g < total; g++) region_count[folded[g].key >> (64 - kIgnoreRegionBits)]++;
     uint32_t maxc = 1;
     for (uint32_t c : region_count) maxc = std::max(maxc, c);
-    uint32_t R = 4;
+    R = 4;
     while ((uint64_t)R * 3 < (uint64_t)maxc * 4) R <<= 1;  // load factor <= 0.75 in the fullest region
     P.table_mask = R - 1;
-    const uint32_t cap = R * kIgnoreRegions;
-    const size_t tb = sizeof(IgnoreSlot) * cap, rb = 4 * n_runes, pb = 4 * prefix_runes.size();
-    if (tb + rb + pb + 16 > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
-      if (t->ign_blob) CU(cudaFree(t->ign_blob));
-      t->ign_blob = nullptr; t->ign_blob_cap = 0;
-      size_t want = (tb + rb + pb + 16) * 2;
-      CU(cudaMalloc(&t->ign_blob, want));
-      t->ign_blob_cap = want;
-    }
-    // table and runes are built in place in a pinned staging buffer kept with the device tree (a copy
-    // from pageable memory would make this call wait for the byte scan queued ahead of it)
-    if (tb + rb + pb > dt->h_ign_cap) {
-      if (dt->h_ign) cudaFreeHost(dt->h_ign);
-      dt->h_ign = nullptr; dt->h_ign_cap = 0;
-      CU(cudaHostAlloc(&dt->h_ign, (tb + rb + pb) * 2, cudaHostAllocDefault));
-      dt->h_ign_cap = (tb + rb + pb) * 2;
-    }
-    IgnoreSlot* table = static_cast<IgnoreSlot*>(dt->h_ign);
-    uint32_t* runes = reinterpret_cast<uint32_t*>((char*)dt->h_ign + tb);
-    run_threads(nt2, [&](unsigned k) {
-      if (!rune_parts[k].empty()) memcpy(runes + rune_base[k], rune_parts[k].data(), 4 * rune_parts[k].size());
-      size_t lo = total * k / nt2, hi = total * (k + 1) / nt2;
-      for (size_t g = lo; g < hi; g++) folded[g].off += (uint32_t)rune_base[k];
-    });
-    if (pb) memcpy((char*)dt->h_ign + tb + rb, prefix_runes.data(), pb);
+    const size_t tb = sizeof(IgnoreSlot) * R * kIgnoreRegions;
+    P.blob_bytes = P.off_table + tb;
+    if (!S.reserve(P.blob_bytes, P.off_table)) { *err = "out of pinned host memory for the ignore table"; return M2K_ERR_NOMEM; }
+    runes = static_cast<uint32_t*>(S.p);
+    if (pb) memcpy((char*)S.p + P.off_prefix, prefix_runes.data(), pb);
+    IgnoreSlot* table = reinterpret_cast<IgnoreSlot*>((char*)S.p + P.off_table);
     const unsigned nt3 = std::min<unsigned>(host_threads(total, 2048), kIgnoreRegions);
+    const uint32_t mask = P.table_mask;
     run_threads(nt3, [&](unsigned tid) {
       for (uint32_t region = tid; region < kIgnoreRegions; region += nt3) memset(table + (size_t)region * R, 0, sizeof(IgnoreSlot) * R);
       for (size_t g = 0; g < total; g++) {
@@ -794,7 +776,7 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
         if (region % nt3 != tid) continue;
         IgnoreSlot* tab = table + (size_t)region * R;
         const uint32_t* rp = runes + fo.off;
-        for (uint32_t sidx = (uint32_t)fo.key & P.table_mask;; sidx = (sidx + 1) & P.table_mask) {
+        for (uint32_t sidx = (uint32_t)fo.key & mask;; sidx = (sidx + 1) & mask) {
           IgnoreSlot& sl = tab[sidx];
           if (sl.hash == 0) { sl = IgnoreSlot{fo.key, fo.off, slot_pack(fo.len, fo.flag)}; break; }
           if (sl.hash == fo.key && slot_len(sl.len_flags) == fo.len && std::equal(rp, rp + fo.len, runes + sl.off)) {
@@ -804,11 +786,48 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
         }
       }
     });
-    CU(cudaMemcpyAsync(t->ign_blob, dt->h_ign, tb + rb + pb, cudaMemcpyHostToDevice, s));
-    P.d_table = (const IgnoreSlot*)t->ign_blob;
-    P.d_runes = (const uint32_t*)((char*)t->ign_blob + tb);
-    P.d_prefix = (const uint32_t*)((char*)t->ign_blob + tb + rb);
+    h5 = now_ms();
   }
+  P.ms_part[0] = h2 - h1; P.ms_part[1] = h3 - h2; P.ms_part[2] = h4 - h3; P.ms_part[3] = h5 - h4;
+  return M2K_OK;
+}
+
+static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* params) {
+  DevTree* t = &dt->t;
+  IgnorePrep& P = dt->prep;
+  const m2k_tree* tree = t->host;
+  CU(cudaEventSynchronize(C->ev_feat));  // name features and the special-entry list are on the host now
+  CU(cudaEventSynchronize(C->ev_blob));  // the staging buffer is free again
+  double h0 = now_ms();
+  P.reset();
+  // the .m2kignore files: from the compacted list of special entries, or a scan of all features if it overflowed
+  P.ign_entries.clear();
+  const uint32_t n_special = dt->h_special[0];
+  if (n_special <= kSpecialCap) {
+    for (uint32_t i = 0; i < n_special; i++) {
+      uint32_t e = dt->h_special[1 + i];
+      if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) P.ign_entries.push_back(e);
+    }
+  } else {
+    for (uint32_t e = 0; e < t->n_entries; e++) if (dt->h_entry_feat[e] & (1u << M2K_N_IGNOREFILE)) P.ign_entries.push_back(e);
+  }
+  std::string err;
+  if (int rc = prepare_host(tree, params, P, dt->stage, &err)) return fail(C, rc, "%s", err.c_str());
+  if (P.blob_bytes) {
+    if (P.blob_bytes > t->ign_blob_cap) {  // grow-only buffer kept with the device tree
+      if (t->ign_blob) CU(cudaFree(t->ign_blob));
+      t->ign_blob = nullptr; t->ign_blob_cap = 0;
+      CU(cudaMalloc(&t->ign_blob, P.blob_bytes * 2));
+      t->ign_blob_cap = P.blob_bytes * 2;
+    }
+    // on the copy stream: queued on `s` it would only start after the byte scan
+    CU(cudaMemcpyAsync(t->ign_blob, dt->stage.p, P.blob_bytes, cudaMemcpyHostToDevice, C->copy_stream));
+    CU(cudaEventRecord(C->ev_blob, C->copy_stream));
+    P.d_runes = (const uint32_t*)t->ign_blob;
+    P.d_prefix = (const uint32_t*)((char*)t->ign_blob + P.off_prefix);
+    P.d_table = (const IgnoreSlot*)((char*)t->ign_blob + P.off_table);
+  }
+  double h6 = now_ms();
   // the result shell: its arrays are the device tree's pinned buffers
   {
     if (dt->pending) { m2k_result* old = dt->pending; dt->pending = nullptr; m2k_result_free(old); }
@@ -830,11 +849,48 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     r->ignore_contents = list_from_arenas(P.arenas, 2, &r->n_ignore_contents);
     dt->pending = r;
   }
+  P.ms_part[4] = now_ms() - h6;
   P.ms_host = (float)(now_ms() - h0);
   if (getenv("M2K_DEBUG_TIMING"))
-    fprintf(stderr, "[m2k] prepare: find %.2f ms, order %.2f ms, parse %.2f ms, table+upload %.2f ms (%zu files, %zu entries)\n",
-            h1 - h0, h2 - h1, h3 - h2, now_ms() - h3, nfiles, total);
+    fprintf(stderr, "[m2k] prepare %.2f ms: order %.2f, parse %.2f, fold %.2f, table %.2f, upload+lists %.2f (%zu files, %zu entries)\n",
+            P.ms_host, P.ms_part[0], P.ms_part[1], P.ms_part[2], P.ms_part[3], P.ms_part[4], P.ign_entries.size(), P.folded.size());
   P.ready = true;
+  return M2K_OK;
+}
+
+extern "C" int m2k_host_prepare_probe(const m2k_tree* tree, const m2k_detect_params* params, uint32_t reps, double* ms_best,
+                                      uint32_t* n_rule_files, uint32_t* n_rules) {
+  if (!tree || !ms_best) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  // stand-in for the name kernel's list of rule files (not timed): a plain scan of the names
+  std::vector<uint32_t> found;
+  for (uint32_t e = 0; e < tree->n_entries; e++) {
+    uint32_t a = tree->entry_name_off[e], b = tree->entry_name_off[e + 1];
+    if (b - a == 10 && !memcmp(tree->names + a, ".m2kignore", 10) && (tree->entry_type[e] & 0xF) != M2K_T_DIR) found.push_back(e);
+  }
+  IgnorePrep P;
+  Staging S;
+  S.pinned = false;
+  for (int k = 0; k < 6; k++) ms_best[k] = 1e30;
+  int rc = M2K_OK;
+  std::string err;
+  for (uint32_t it = 0; it < (reps ? reps : 1) && rc == M2K_OK; it++) {
+    double t0 = now_ms();
+    P.reset();
+    P.ign_entries = found;
+    rc = prepare_host(tree, params, P, S, &err);
+    double t1 = now_ms();
+    uint32_t n1 = 0, n2 = 0;
+    char** l1 = list_from_arenas(P.arenas, 1, &n1);
+    char** l2 = list_from_arenas(P.arenas, 2, &n2);
+    double t2 = now_ms();
+    free(l1); free(l2);
+    const double v[6] = {t2 - t0, P.ms_part[0], P.ms_part[1], P.ms_part[2], P.ms_part[3], t2 - t1};
+    for (int k = 0; k < 6; k++) ms_best[k] = std::min(ms_best[k], v[k]);
+  }
+  if (n_rule_files) *n_rule_files = (uint32_t)found.size();
+  if (n_rules) *n_rules = (uint32_t)P.folded.size();
+  S.release();
+  if (rc) return fail(nullptr, rc, "%s", err.c_str());
   return M2K_OK;
 }
 
@@ -871,16 +927,23 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   r->ms_host_ignore = P.ms_host;
   r->n_services = 0;
 
+  // what is final before the walk goes to the host on the copy stream while the walk kernels run
+  CU(cudaEventRecord(C->ev_fork, s));
+  CU(cudaStreamWaitEvent(C->copy_stream, C->ev_fork, 0));
+  CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
+  CU(cudaEventRecord(C->ev_join, C->copy_stream));
+  CU(cudaStreamWaitEvent(s, C->ev_blob, 0));  // the ignore table m2k_prepare sent up
   CU(cudaEventRecord(C->ev[11], s));
   launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore);
   CU(cudaEventRecord(C->ev[5], s));
-  CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(r->dir_state, t->dir_state, nd, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(r->dir_ignore, t->dir_ignore, nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamWaitEvent(s, C->ev_join, 0));
+  CU(cudaStreamWaitEvent(s, C->ev_feat, 0));  // r->entry_feat
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "detection kernels failed: %s", cudaGetErrorString(werr));
@@ -949,7 +1012,7 @@ extern "C" int m2k_list_entries(const m2k_tree* tree, uint32_t feature_bit, cons
   if (!tree || !entry_feat || feature_bit > 31) return M2K_ERR_ARG;
   std::vector<uint32_t> v;
   for (uint32_t e = 0; e < tree->n_entries; e++) if (entry_feat[e] >> feature_bit & 1) v.push_back(e);
-  std::sort(v.begin(), v.end(), [&](uint32_t a, uint32_t b) { return walk_before(tree, a, b); });
-  for (size_t i = 0; i < v.size() && i < cap; i++) outv[i] = v[i];
+  sort_walk_order(tree, &v);
+  for (size_t i = 0; outv && i < v.size() && i < cap; i++) outv[i] = v[i];
   return (int)v.size();
 }

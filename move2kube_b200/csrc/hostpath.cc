@@ -227,4 +227,39 @@ void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out) {
   }
 }
 
+// Puts a set of entry ids into filepath.Walk order without walking the tree.  Directories are numbered
+// in Walk order, so an entry's position is fixed by the NEXT directory the walk enters after it:
+// for a file that is the first real sub-directory listed after it in its own directory, or, when
+// there is none, whatever follows its directory's subtree (dir_end).  Files that share that next
+// directory are visited deepest directory first (the walk is unwinding), then by name; a directory
+// entry comes after all of them.  Cost: one pass over the matched directories' listings + a sort.
+void sort_walk_order(const m2k_tree* t, std::vector<uint32_t>* ents) {
+  std::vector<uint32_t>& v = *ents;
+  std::sort(v.begin(), v.end());
+  v.erase(std::unique(v.begin(), v.end()), v.end());
+  struct Key { uint32_t next, unwind, e; };
+  std::vector<Key> keys(v.size());
+  auto real_dir = [&](uint32_t e) { return (t->entry_type[e] & 0xF) == M2K_T_DIR && t->entry_child[e] != M2K_NONE; };
+  uint32_t cur_dir = M2K_NONE, limit = 0, cur_next = 0;
+  for (size_t k = v.size(); k-- > 0;) {  // entries are sorted by (directory, name): go backwards inside each directory
+    const uint32_t e = v[k], d = t->entry_dir[e];
+    if (d != cur_dir) { cur_dir = d; limit = t->dir_first_entry[d + 1]; cur_next = t->dir_end[d]; }
+    if (real_dir(e)) {
+      cur_next = t->entry_child[e];
+      keys[k] = {cur_next, 0xFFFFFFFFu, e};
+    } else {
+      for (uint32_t i = e + 1; i < limit; i++)
+        if (real_dir(i)) { cur_next = t->entry_child[i]; break; }
+      keys[k] = {cur_next, t->n_dirs - 1 - d, e};
+    }
+    limit = e;
+  }
+  std::sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) {
+    if (a.next != b.next) return a.next < b.next;
+    if (a.unwind != b.unwind) return a.unwind < b.unwind;
+    return a.e < b.e;
+  });
+  for (size_t k = 0; k < v.size(); k++) v[k] = keys[k].e;
+}
+
 }  // namespace m2k

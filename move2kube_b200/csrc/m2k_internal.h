@@ -96,6 +96,10 @@ struct Ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[12] = {};
+  // second stream for the small copies that would otherwise sit between kernels of `stream` (name
+  // features to the host, the ignore table to the device, early result arrays), and its ordering events
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_names = nullptr, ev_feat = nullptr, ev_blob = nullptr, ev_fork = nullptr, ev_join = nullptr;
   float phase_ms[8] = {};  // names, scan, combine, dockerfile, finalize kernels, host ignore, host verify, d2h
   int sm_count = 0;
   uint64_t launches = 0;
@@ -143,6 +147,7 @@ void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64
                        std::vector<std::string>* ignore_dirs, std::vector<std::string>* ignore_contents);
 std::string tree_dir_path(const m2k_tree* t, uint32_t d);
 void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out);  // filepath.Walk order of all entries
+void sort_walk_order(const m2k_tree* t, std::vector<uint32_t>* ents);    // a set of entry ids into filepath.Walk order
 
 // ---- tree ownership (packer.cc / synth.cc) ----
 struct TreeOwner {

@@ -27,7 +27,7 @@ EXPORTS = [
     "m2k_pack_tree", "m2k_tree_free", "m2k_pinned_alloc", "m2k_pinned_free", "m2k_synth_tree", "m2k_synth_fill_host", "m2k_detect", "m2k_result_free",
     "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_file_flags_get", "m2k_file_flags_set", "m2k_prepare", "m2k_finalize",
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
-    "m2k_list_entries", "m2k_scan_flags_noalloc",
+    "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
 ]
 
 
@@ -82,6 +82,7 @@ def load():
     L.m2k_equal_fold.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.m2k_list_entries.argtypes = [TP, C.c_uint32, _abi.u32p, _abi.u32p, C.c_uint32]
     L.m2k_scan_flags_noalloc.argtypes = [C.c_int, vp, vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp]
+    L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
         if fn.restype is C.c_int and name not in ("m2k_abi_version", "m2k_equal_fold", "m2k_list_entries"):

@@ -158,3 +158,76 @@ def test_path_helpers_follow_go(oracle):
     for a, b in [(b"/R/K", "/r/K".encode()), (b"ss", "ß".encode()), (b"a\xffb", b"A\xfeB"), (b"I", "ı".encode()),
                  ("ſ".encode(), b"S"), (b"abc", b"ab")]:
         assert lib.equal_fold(a, b) == gopath.equal_fold(a, b) == oracle.equal_fold(a, b)
+
+
+def _walk_order(a):
+    """filepath.Walk order of all entry ids, straight from the packed arrays (the definition: a
+    directory's entries in name order, descending into each real directory right after naming it)."""
+    out = []
+
+    def visit(d):
+        for e in range(a["dir_first_entry"][d], a["dir_first_entry"][d + 1]):
+            out.append(e)
+            if (a["entry_type"][e] & 0xF) == _abi.T_DIR and a["entry_child"][e] != _abi.NONE:
+                visit(a["entry_child"][e])
+    visit(0)
+    return out
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_list_entries_is_in_walk_order(seed):
+    """m2k_list_entries (GetFilesByName / GetFilesByExt, utils.go:47-120) sorts a subset of entries
+    into Walk order from the directory numbering alone; checked against the plain recursive walk."""
+    import random
+    rng = random.Random(seed)
+    tp = lib.synth_tree_host(small_synth(seed=seed, n_files=3000, n_dirs=400, total=1 << 20), host_bytes=False)
+    try:
+        a = _tree_arrays(tp)
+        ne = a["n"][1]
+        order = _walk_order(a)
+        assert sorted(order) == list(range(ne))
+        for frac in (0.002, 0.05, 0.5, 1.0):
+            feat = (C.c_uint32 * ne)()
+            chosen = set()
+            for e in range(ne):
+                if rng.random() < frac:
+                    feat[e] = 1
+                    chosen.add(e)
+            got = lib.list_entries(tp, 0, feat)
+            assert got == [e for e in order if e in chosen]
+    finally:
+        lib.tree_free_host(tp)
+
+
+def test_host_prepare_probe_runs_without_a_device():
+    tp = lib.synth_tree_host(small_synth(seed=5, n_files=2000, n_dirs=300, total=1 << 20), host_bytes=False)
+    try:
+        ms = (C.c_double * 6)()
+        nf, nr = C.c_uint32(), C.c_uint32()
+        assert lib.load().m2k_host_prepare_probe(tp, None, 2, ms, C.byref(nf), C.byref(nr)) == 0
+        assert nf.value >= 1 and nr.value >= 1 and all(0 <= v < 1e4 for v in ms)
+    finally:
+        lib.tree_free_host(tp)
+
+
+@pytest.mark.parametrize("name", ["nasty", "samples", "multiignores", "random007"])
+def test_list_entries_walk_order_on_packed_trees(tmp_path, name):
+    """Same check on trees packed from the filesystem (symlinks, dot names, directories that sort
+    between files)."""
+    import random
+    spec = next(g for g in GOLDENS if g["name"] == name)
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / name)))
+    tp = lib.pack_tree_host(root)
+    try:
+        a = _tree_arrays(tp)
+        ne = a["n"][1]
+        order = _walk_order(a)
+        rng = random.Random(11)
+        for frac in (0.3, 1.0):
+            feat = (C.c_uint32 * max(ne, 1))()
+            chosen = {e for e in range(ne) if rng.random() < frac}
+            for e in chosen:
+                feat[e] = 1
+            assert lib.list_entries(tp, 0, feat) == [e for e in order if e in chosen]
+    finally:
+        lib.tree_free_host(tp)
