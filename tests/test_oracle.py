@@ -52,3 +52,29 @@ def test_oracle_on_the_real_samples_tree(oracle):
     assert got == ["docker-compose/api/Dockerfile", "docker-compose/web/Dockerfile", "dockerfile/Dockerfile"]
     oracle.lib().m2ko_result_free(res)
     oracle.lib().m2ko_tree_free(tree)
+
+
+ASSETS_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "m2kassets")
+
+
+@pytest.mark.skipif(not os.path.isdir(ASSETS_DIR), reason="oracle/_ref/m2kassets (the reference's scripts) not unpacked")
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_c_oracle_agrees_with_the_reference_scripts_on_generator_trees(oracle, tmp_path, seed):
+    """The bench generator's trees, materialised on disk: the reference's own detect scripts (driven by
+    the restated Go control flow) and the plain-C oracle must take the same decision for every
+    directory -- this is what lets the C oracle stand in for the scripts at bench scale (config B is
+    checked the same way by oracle/script_baseline.py --workload B)."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(ASSETS_DIR), ".."))
+    import script_baseline as sb
+    from move2kube_b200 import _abi, lib
+    p = _abi.SynthParams(seed=seed, n_files=500, n_dirs=80, max_depth=6, n_ignore_files=3, total_bytes=3_000_000)
+    tp = lib.synth_tree_host(p, host_bytes=True)
+    root = os.fsencode(str(tmp_path / "tree"))
+    sb.materialize(tp, root)
+    lib.tree_free_host(tp)
+    _, services, err, trace, ign_d, ign_c = sb.script_pass(root)
+    assert err is None and len(trace) >= 5
+    _, tree, res = sb.c_oracle_pass(root)
+    bad, lists_ok = sb.compare(root, trace, services, ign_d, ign_c, tree, res)
+    assert bad == [] and lists_ok
