@@ -29,30 +29,8 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 
 def materialize(tp, dst: bytes):
     """Write a packed synthetic tree (host bytes present) to the directory `dst`."""
-    t = tp.contents
-    names = C.string_at(t.names, t.n_name_bytes)
-    noff = t.entry_name_off[0:t.n_entries + 1]
-    dir_path = [b""] * t.n_dirs
-    dir_path[0] = dst
-    os.makedirs(dst, exist_ok=True)
-    n_bytes = 0
-    for d in range(t.n_dirs):
-        base = dir_path[d]
-        for e in range(t.dir_first_entry[d], t.dir_first_entry[d + 1]):
-            p = base + b"/" + names[noff[e]:noff[e + 1]]
-            ty = t.entry_type[e] & 0xF
-            child = t.entry_child[e]
-            if ty == 2:
-                os.mkdir(p)
-                dir_path[child] = p
-            elif ty == 1:
-                off, ln = t.file_off[child], t.file_len[child]
-                with open(p, "wb") as f:
-                    f.write(C.string_at(C.addressof(t.bytes.contents) + off, ln))
-                n_bytes += ln
-            else:
-                raise SystemExit("synthetic trees hold only files and directories")
-    return n_bytes
+    from move2kube_b200 import synthfs
+    return synthfs.materialize(tp, dst)
 
 
 def script_pass(root: bytes, flavor="bash"):
