@@ -91,7 +91,11 @@ enum {
   M2K_FILE_HAS_MAIN = 1,    /* bytes contain "__main__"              (python detect scripts :21/:22) */
   M2K_FILE_LONG_LINE = 2,   /* some line >= 65536 bytes (bufio.Scanner ErrTooLong) */
   M2K_FILE_FROM_FIRST = 4,  /* first non-ARG instruction is FROM and matches dockerfile2kube.go:131 */
-  M2K_FILE_DOCKERFILE = 8   /* isDockerFile() == true                (dockerfile2kube.go:117-144) */
+  M2K_FILE_DOCKERFILE = 8,  /* isDockerFile() == true                (dockerfile2kube.go:117-144) */
+  M2K_FILE_UNDECIDED = 16   /* only for a file that m2k_upload_chunks spread over several GPUs: HAS_MAIN and
+                               LONG_LINE are final, but FROM_FIRST / DOCKERFILE could not be settled from the
+                               pieces (the file starts like a Dockerfile and has no long line, so its body
+                               needs validating as a whole): scan that one file with m2k_upload(f, f+1) */
 };
 
 /* ---- what the walk did with a directory (any2kube.go:58-98) ---- */
@@ -216,6 +220,26 @@ void m2k_result_free(m2k_result* r);
 
 /* -- staged form (bench, multi-GPU): a shard = file ids [file_begin, file_end) -- */
 int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out);
+/* -- a shard as a range of 64 KiB chunks, so that one multi-GB file can be spread over several GPUs
+ * (SURVEY.md section 8e).  Chunks are numbered over the whole tree: files in id order, each
+ * ceil(file_len / 65536) chunks (m2k_chunk_count = the total).  A shard may begin and end inside a
+ * file; it then also holds the 16 bytes on the far side of the cut.  m2k_plan_shards picks
+ * n_ranks + 1 cut points of near-equal bytes that fall inside a file only when the file has at least
+ * `split_min_bytes` bytes (smaller files go whole to one side).  The parts of a cut file are
+ * summarised per shard (m2k_pieces: 64 bytes, device to device), gathered in rank order and stitched
+ * by m2k_merge_pieces on the rank that finalises; see M2K_FILE_UNDECIDED for the one case left open. */
+uint64_t m2k_chunk_count(const m2k_tree* tree);
+int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t* chunk_cuts /* [n_ranks+1] */);
+int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t chunk_begin, uint64_t chunk_end, m2k_devtree** out);
+int m2k_pieces(m2k_ctx* ctx, m2k_devtree* dt, void* d_dst /* 64 bytes */);
+int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all_pieces /* n_ranks x 64 bytes, rank order */, uint32_t n_ranks);
+/* which file holds global chunk `chunk`, and which of its chunks that is (a cut at chunk_in_file != 0 splits the file) */
+int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* file, uint32_t* chunk_in_file);
+/* one file's flags on the device, read back (synchronises); and, before m2k_finalize, the flags a
+ * separate pass over that one file found for a file left M2K_FILE_UNDECIDED (also records the
+ * Dockerfile bit of its directory) */
+int m2k_file_flag(m2k_ctx* ctx, m2k_devtree* dt, uint32_t file, uint8_t* out);
+int m2k_settle_file(m2k_ctx* ctx, m2k_devtree* dt, uint32_t file, uint32_t flags);
 int m2k_synth_fill_device(m2k_ctx* ctx, m2k_devtree* dt, uint64_t seed);
 /* phase A: name features + byte scan + Dockerfile check over the resident shard */
 int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* params);
@@ -254,7 +278,7 @@ void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
  * For hosts that cannot call cudaMalloc where they call this library: inside work they are
  * capturing or replaying, under a device-memory arena that is handed out once and then locked, or
  * under a fixed memory quota.  The caller owns every buffer; the scan's only scratch, the per-chunk
- * record table, is a fixed 1 MiB array in the library image (held by every GPU that loads the
+ * record table, is a fixed 2 MiB array in the library image (held by every GPU that loads the
  * library until exit), which limits one call to 262144 chunks of 64 KiB (16 GiB of content): more
  * is refused with M2K_ERR_LIMIT.  All pointers are DEVICE pointers on `device`:
  *   d_bytes        file contents; each file starts at a multiple of 16, is zero padded to 16 bytes,

@@ -18,7 +18,7 @@ S2I_NAMES = ["golang", "java", "nodejs", "php", "python", "ruby"]
 N_DF, N_S2I = len(DF_NAMES), len(S2I_NAMES)
 DF_MASK, S2I_MASK = 0x00000FFF, 0x0003F000
 
-FILE_HAS_MAIN, FILE_LONG_LINE, FILE_FROM_FIRST, FILE_DOCKERFILE = 1, 2, 4, 8
+FILE_HAS_MAIN, FILE_LONG_LINE, FILE_FROM_FIRST, FILE_DOCKERFILE, FILE_UNDECIDED = 1, 2, 4, 8, 16
 
 (DIR_NOT_VISITED, DIR_PRECONTAINERIZED, DIR_IGNORED_PRUNE, DIR_IGNORED_DESCEND, DIR_NOMATCH_PRUNE,
  DIR_NOMATCH_DESCEND, DIR_SERVICE, DIR_WALK_ERROR) = range(8)

@@ -293,7 +293,7 @@ static void devtree_release(DevTree* t) {
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
                   t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
                   t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
-                  t->cand_esc, t->stripe_state, t->ign_blob, t->special};
+                  t->cand_esc, t->stripe_state, t->ign_blob, t->special, t->pieces};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -317,10 +317,13 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
 template <typename T>
 static cudaError_t dev_alloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
 
-extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out) {
-  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+static inline uint64_t file_chunks(const m2k_tree* tree, uint32_t f) { return (tree->file_len[f] + kChunkBytes - 1) / kChunkBytes; }
+
+// the shard: files [file_begin, file_end), of which the first starts `first_skip` chunks in and the
+// last ends at chunk `last_end` of that file (M2K_NONE: at its end)
+static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, uint32_t first_skip, uint32_t last_end,
+                       m2k_devtree** out) {
   Ctx* C = &ctx->c;
-  if (!tree || !out || file_begin > file_end || file_end > tree->n_files) return fail(C, M2K_ERR_ARG, "m2k_upload: bad argument");
   *out = nullptr;
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
@@ -328,7 +331,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   struct Guard { m2k_devtree* d; bool keep = false; ~Guard() { if (!keep) { devtree_release(&d->t); free_devtree_shell(d); } } } guard{dt};
   t->host = tree;
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
-  t->file_begin = file_begin; t->file_end = file_end;
+  t->file_begin = file_begin; t->file_end = file_end; t->first_skip = first_skip; t->last_end = last_end;
   const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files, ns = file_end - file_begin;
   // levels (host): directories grouped by depth for the bottom-up / top-down sweeps
   std::vector<uint32_t> level_dirs(nd ? nd : 1);
@@ -344,17 +347,28 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   uint64_t nchunks = 0, content = 0;
   for (uint32_t i = 0; i < ns; i++) {
     chunk_first[i] = (uint32_t)nchunks;
-    uint64_t len = tree->file_len[file_begin + i];
-    nchunks += (len + kChunkBytes - 1) / kChunkBytes;
-    content += len;
+    const uint64_t len = tree->file_len[file_begin + i];
+    const uint64_t c_lo = i == 0 ? first_skip : 0;
+    const uint64_t c_hi = (i + 1 == ns && last_end != M2K_NONE) ? last_end : file_chunks(tree, file_begin + i);
+    nchunks += c_hi - c_lo;
+    const uint64_t b_lo = c_lo * kChunkBytes, b_hi = std::min<uint64_t>(len, c_hi * kChunkBytes);
+    content += b_hi - b_lo;
   }
   chunk_first[ns] = (uint32_t)nchunks;
   if (nchunks > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard has too many 64 KiB chunks (%llu)", (unsigned long long)nchunks);
   t->n_chunks = (uint32_t)nchunks;
   t->shard_content = content;
-  t->shard_byte0 = ns ? tree->file_off[file_begin] : 0;
-  uint64_t shard_end = ns ? (tree->file_off[file_end - 1] + ((tree->file_len[file_end - 1] + 15) & ~15ull)) : 0;
-  t->shard_bytes = shard_end - t->shard_byte0 + 16;
+  // resident bytes: the shard's chunks, plus 16 bytes on the far side of a cut through a file (a
+  // "__main__" may straddle the cut), plus 16 zero bytes at the very end
+  uint64_t r0 = 0, r1 = 0;
+  if (ns) {
+    r0 = tree->file_off[file_begin] + (uint64_t)first_skip * kChunkBytes - (first_skip ? 16 : 0);
+    const uint32_t fl = file_end - 1;
+    r1 = last_end != M2K_NONE ? tree->file_off[fl] + (uint64_t)last_end * kChunkBytes + 16
+                              : tree->file_off[fl] + ((tree->file_len[fl] + 15) & ~15ull);
+  }
+  t->shard_byte0 = r0;
+  t->shard_bytes = r1 - r0 + 16;
 
   CU(dev_alloc(&t->dir_parent, nd)); CU(dev_alloc(&t->dir_entry, nd)); CU(dev_alloc(&t->dir_depth, nd));
   CU(dev_alloc(&t->level_dirs, nd)); CU(dev_alloc(&t->dir_flags, nd));
@@ -363,7 +377,7 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(dev_alloc(&t->file_entry, nf)); CU(dev_alloc(&t->file_off, nf)); CU(dev_alloc(&t->file_len, nf));
   CU(dev_alloc(&t->chunk_first, (size_t)ns + 1));
   CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
-  CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne));
+  CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne)); CU(dev_alloc(&t->pieces, 2));
   {
     uint64_t cap = (t->shard_bytes + kDfStripe - 1) / kDfStripe + ns + 1;  // stripes over every file body, rounded up per file
     if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile stripe table");
@@ -401,6 +415,58 @@ extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begi
   CU(cudaEventElapsedTime(&dt->ms_h2d, C->ev[0], C->ev[1]));
   guard.keep = true;
   *out = dt;
+  return M2K_OK;
+}
+
+extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out) {
+  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+  if (!tree || !out || file_begin > file_end || file_end > tree->n_files) return fail(&ctx->c, M2K_ERR_ARG, "m2k_upload: bad argument");
+  return upload_impl(ctx, tree, file_begin, file_end, 0, M2K_NONE, out);
+}
+
+extern "C" uint64_t m2k_chunk_count(const m2k_tree* tree) {
+  uint64_t n = 0;
+  if (tree) for (uint32_t f = 0; f < tree->n_files; f++) n += file_chunks(tree, f);
+  return n;
+}
+
+extern "C" int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t chunk_begin, uint64_t chunk_end, m2k_devtree** out) {
+  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+  if (!tree || !out || chunk_begin > chunk_end) return fail(&ctx->c, M2K_ERR_ARG, "m2k_upload_chunks: bad argument");
+  // locate the two ends in the global chunk numbering (files in id order, ceil(len / 64 KiB) chunks each)
+  uint32_t f0 = 0, fl = 0, first_skip = 0, last_end = M2K_NONE;
+  bool have0 = false, have1 = false;
+  uint64_t at = 0;
+  for (uint32_t f = 0; f < tree->n_files && !have1; f++) {
+    const uint64_t nc = file_chunks(tree, f);
+    if (nc == 0) continue;
+    if (!have0 && chunk_begin < at + nc) { have0 = true; f0 = f; first_skip = (uint32_t)(chunk_begin - at); }
+    if (have0 && chunk_end <= at + nc) { have1 = true; fl = f; last_end = chunk_end - at == nc ? M2K_NONE : (uint32_t)(chunk_end - at); }
+    at += nc;
+  }
+  if (chunk_begin == chunk_end) return upload_impl(ctx, tree, 0, 0, 0, M2K_NONE, out);
+  if (!have0 || !have1) return fail(&ctx->c, M2K_ERR_ARG, "m2k_upload_chunks: chunk range [%llu, %llu) is outside the tree's %llu chunks",
+                                    (unsigned long long)chunk_begin, (unsigned long long)chunk_end, (unsigned long long)m2k_chunk_count(tree));
+  return upload_impl(ctx, tree, f0, fl + 1, first_skip, last_end, out);
+}
+
+extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t* chunk_cuts) {
+  if (!tree || !n_ranks || !chunk_cuts) return fail(nullptr, M2K_ERR_ARG, "m2k_plan_shards: bad argument");
+  const uint64_t total = m2k_chunk_count(tree);
+  chunk_cuts[0] = 0;
+  uint32_t f = 0;
+  uint64_t at = 0;  // first chunk of file f
+  for (uint32_t r = 1; r < n_ranks; r++) {
+    const uint64_t target = (uint64_t)((unsigned __int128)total * r / n_ranks);
+    while (f < tree->n_files && at + file_chunks(tree, f) <= target) { at += file_chunks(tree, f); f++; }
+    uint64_t cut = target;
+    if (f < tree->n_files && target > at) {  // the target falls inside file f
+      const uint64_t nc = file_chunks(tree, f);
+      if (tree->file_len[f] < split_min_bytes) cut = (target - at) * 2 < nc ? at : at + nc;  // small file: nearer boundary
+    }
+    chunk_cuts[r] = std::max(cut, chunk_cuts[r - 1]);
+  }
+  chunk_cuts[n_ranks] = total;
   return M2K_OK;
 }
 
@@ -510,6 +576,55 @@ extern "C" int m2k_file_flags_set(m2k_ctx* ctx, m2k_devtree* dt, const uint8_t* 
   CU(cudaSetDevice(C->device));
   CU(cudaMemcpyAsync(dt->t.file_flags, d_src, dt->t.n_files, cudaMemcpyDeviceToDevice, C->stream));
   return M2K_OK;
+}
+
+// the (at most two) files this shard holds only part of: 2 x 32 bytes, device to device
+extern "C" int m2k_pieces(m2k_ctx* ctx, m2k_devtree* dt, void* d_dst) {
+  if (!ctx || !dt || !d_dst) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  if (dt->content) CU(cudaMemcpyAsync(d_dst, dt->t.pieces, 2 * sizeof(PieceSummary), cudaMemcpyDeviceToDevice, C->stream));
+  else CU(cudaMemsetAsync(d_dst, 0xFF, 2 * sizeof(PieceSummary), C->stream));
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+extern "C" int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all_pieces, uint32_t n_ranks) {
+  if (!ctx || !dt || !d_all_pieces || !n_ranks) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  launch_merge_pieces(C, &dt->t, static_cast<const PieceSummary*>(d_all_pieces), 2 * n_ranks);
+  CU(cudaGetLastError());
+  return M2K_OK;
+}
+
+extern "C" int m2k_file_flag(m2k_ctx* ctx, m2k_devtree* dt, uint32_t f, uint8_t* out) {
+  if (!ctx || !dt || !out || f >= dt->t.n_files) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaMemcpyAsync(out, dt->t.file_flags + f, 1, cudaMemcpyDeviceToHost, C->stream));
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+extern "C" int m2k_settle_file(m2k_ctx* ctx, m2k_devtree* dt, uint32_t f, uint32_t flags) {
+  if (!ctx || !dt || f >= dt->t.n_files || (flags & ~0xFu)) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  launch_settle_file(C, &dt->t, f, flags);
+  CU(cudaGetLastError());
+  return M2K_OK;
+}
+
+extern "C" int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* file, uint32_t* chunk_in_file) {
+  if (!tree || !file || !chunk_in_file) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  uint64_t at = 0;
+  for (uint32_t f = 0; f < tree->n_files; f++) {
+    const uint64_t nc = file_chunks(tree, f);
+    if (chunk < at + nc) { *file = f; *chunk_in_file = (uint32_t)(chunk - at); return M2K_OK; }
+    at += nc;
+  }
+  return fail(nullptr, M2K_ERR_ARG, "chunk %llu is past the tree's %llu chunks", (unsigned long long)chunk, (unsigned long long)at);
 }
 
 extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks) {

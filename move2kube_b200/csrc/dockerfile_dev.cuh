@@ -377,8 +377,12 @@ __device__ inline bool directive_ok(File& f, uint64_t lb, uint64_t le, bool* pro
 // `body` can no longer change the answer except by a parse error, which the striped validation
 // below looks for in parallel.  `long_line`: the byte scan found a line of >= 65536 bytes (Parse
 // fails; it also keeps this thread from walking such a line).
-__device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64_t* body, uint32_t* esc) {
+// `touched_end` (optional): set when the verdict rests on the last line present in [0, n) -- for a
+// caller that holds only a prefix of the file, the verdict is then not final.
+__device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64_t* body, uint32_t* esc, bool* touched_end = nullptr) {
   if (long_line || n == 0) return false;
+  bool at_end = false;
+  struct Note { bool* dst; bool* src; __device__ ~Note() { if (dst) *dst = *src; } } note{touched_end, &at_end};
   File f{p, n, '\\'};
   bool processing_complete = false, escape_seen = false;
   uint64_t pos = 0;
@@ -407,6 +411,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
       }
     }
     pos = phys_line(f, lb, &le);
+    if (pos >= n) at_end = true;
     if (first_line) { if (le - lb >= 3 && p[lb] == 0xEF && p[lb + 1] == 0xBB && p[lb + 2] == 0xBF) lb += 3; first_line = false; }
     while (lb < le) { uint32_t w, r = decode_rune(p + lb, le - lb, &w); if (!is_space_rune(r)) break; lb += w; }  // trimWhitespace
     if (!directive_ok(f, lb, le, &processing_complete, &escape_seen)) return false;
@@ -414,10 +419,11 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
     bool more = trim_continuation(f, lb, &le);
     if (!more && le == lb) continue;
     LCur start{lb, le, pos, more};
-    int kind;
-    if (!node_from_line(f, start, &kind)) return false;
     LCur endc = start;
     while (lc_get(f, endc) >= 0) {}
+    if (endc.next_line >= n) at_end = true;
+    int kind;
+    if (!node_from_line(f, start, &kind)) return false;
     pos = endc.next_line;
     if (kind == 2) continue;  // ARG: keep looking
     if (kind != 1 || !from_regex(f, start)) return false;
@@ -425,6 +431,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
     *esc = f.esc;
     return true;
   }
+  at_end = true;
   return false;  // file with no instructions (or only ARG)
 }
 

@@ -142,6 +142,29 @@ __device__ __forceinline__ uint32_t has_newline(uint4 v) {
   return t & 0x80808080u;
 }
 
+// exact per-byte test: bit 7 of every byte of w that is '\n'
+__device__ __forceinline__ uint32_t nl_bits(uint32_t w) {
+  uint32_t x = w ^ 0x0A0A0A0Au;
+  return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+}
+// byte index (0..15) of the first / last newline of a unit that has one
+__device__ __noinline__ uint32_t first_nl_byte(uint4 v) {
+  uint32_t m;
+  if ((m = nl_bits(v.x))) return (uint32_t)(__ffs(m) - 1) >> 3;
+  if ((m = nl_bits(v.y))) return 4 + ((uint32_t)(__ffs(m) - 1) >> 3);
+  if ((m = nl_bits(v.z))) return 8 + ((uint32_t)(__ffs(m) - 1) >> 3);
+  m = nl_bits(v.w);
+  return 12 + ((uint32_t)(__ffs(m) - 1) >> 3);
+}
+__device__ __noinline__ uint32_t last_nl_byte(uint4 v) {
+  uint32_t m;
+  if ((m = nl_bits(v.w))) return 12 + ((31u - (uint32_t)__clz(m)) >> 3);
+  if ((m = nl_bits(v.z))) return 8 + ((31u - (uint32_t)__clz(m)) >> 3);
+  if ((m = nl_bits(v.y))) return 4 + ((31u - (uint32_t)__clz(m)) >> 3);
+  m = nl_bits(v.x);
+  return (31u - (uint32_t)__clz(m)) >> 3;
+}
+
 __device__ __forceinline__ bool main_word(uint32_t w) {
   // little-endian words of "__ma" "_mai" "main" "ain_"
   return w == 0x616D5F5Fu || w == 0x69616D5Fu || w == 0x6E69616Du || w == 0x5F6E6961u;
@@ -194,7 +217,7 @@ __device__ __noinline__ bool first_word_rules_out_dockerfile(uint4 v) {
 __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes(
     uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first,
     const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, uint32_t file_begin,
-    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, uint32_t* __restrict__ chunk_rec) {
+    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, uint32_t first_skip, ChunkRec* __restrict__ chunk_rec) {
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t warps_per_block = kScanThreads / 32;
   const uint32_t n_warps = gridDim.x * warps_per_block;
@@ -204,15 +227,16 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
     while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (chunk_first[mid] <= item) lo = mid; else hi = mid; }
     const uint32_t f = file_begin + lo;
     const uint64_t flen = file_len[f];
-    const uint64_t start = (uint64_t)(item - chunk_first[lo]) * kChunkBytes;
-    const uint8_t* fbase = bytes + (file_off[f] - shard_byte0);
-    const uint64_t range = flen - start < kChunkBytes ? flen - start : kChunkBytes;
-    const uint32_t n_units = (uint32_t)((range + 15) >> 4);
+    // the shard may begin `first_skip` chunks into its first file (the rest of it is on another GPU)
+    const uint64_t start = (uint64_t)(item - chunk_first[lo] + (lo == 0 ? first_skip : 0u)) * kChunkBytes;
+    const uint8_t* fbase = bytes + (file_off[f] - shard_byte0);  // may point before the shard; only [start - 16, ...) is touched
+    const uint32_t range = (uint32_t)(flen - start < kChunkBytes ? flen - start : kChunkBytes);
+    const uint32_t n_units = (range + 15) >> 4;
     const uint4* src = reinterpret_cast<const uint4*>(fbase + start);
     // Inside one 64 KiB chunk a newline-free run that is closed on both sides is shorter than 64 KiB,
-    // so only the first and the last newline of the chunk matter: newlines are looked for until the
-    // first one is found, and again in the last batch of rows.
-    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0, not_df = 0;
+    // so only the first and the last newline of the chunk matter: the first is looked for until it is
+    // found, the last in the final batch of rows (walking back from there in the rare case it has none).
+    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0, not_df = 0;  // byte offsets inside the chunk
     for (uint32_t u0 = 0; u0 < n_units; u0 += 32 * kScanRows) {
       uint4 v[kScanRows];
 #pragma unroll
@@ -221,7 +245,6 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
         v[r] = u < n_units ? ldg_stream(src + u) : make_uint4(0, 0, 0, 0);
       }
       if (start == 0 && u0 == 0 && lane == 0) not_df = first_word_rules_out_dockerfile(v[0]) ? 1u : 0u;
-      const bool want_nl = lead == M2K_NONE || u0 + 32 * kScanRows >= n_units;  // warp-uniform
       bool hit_any = false;
 #pragma unroll
       for (int r = 0; r < kScanRows; r++)
@@ -238,49 +261,62 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
         }
         if (__any_sync(FULL, ok)) found = 1;
       }
-      if (want_nl) {
+      if (lead == M2K_NONE) {  // warp-uniform: first newline, rows in order
 #pragma unroll
         for (int r = 0; r < kScanRows; r++) {
-          uint32_t ubase = u0 + r * 32;
-          uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);  // rows past the end are zero: no newline
-          if (B) {
-            if (lead == M2K_NONE) lead = ubase + (uint32_t)__ffs(B) - 1;
-            last_nl = ubase + 31 - (uint32_t)__clz(B);
+          if (lead == M2K_NONE) {
+            uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);  // rows past the end are zero: no newline
+            if (B) {
+              int l = __ffs(B) - 1;
+              lead = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, first_nl_byte(v[r]), l);
+            }
+          }
+        }
+      }
+      if (u0 + 32 * kScanRows >= n_units) {  // warp-uniform: last newline, rows in reverse
+#pragma unroll
+        for (int r = kScanRows - 1; r >= 0; r--) {
+          if (last_nl == M2K_NONE) {
+            uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);
+            if (B) {
+              int l = 31 - __clz(B);
+              last_nl = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, last_nl_byte(v[r]), l);
+            }
           }
         }
       }
     }
     uint32_t trail;
     if (lead == M2K_NONE) {
-      lead = trail = n_units;  // no newline in the whole chunk
+      lead = trail = range;  // no newline in the whole chunk
     } else {
-      const uint32_t last_batch0 = ((n_units - 1) / (32 * kScanRows)) * (32 * kScanRows);
-      if (last_nl == M2K_NONE || last_nl < last_batch0) {
-        // the last batch has no newline (rare): walk back row by row; the unit `lead` stops the search
-        uint32_t ubase = last_batch0;
-        last_nl = M2K_NONE;
+      if (last_nl == M2K_NONE) {
+        // the last batch has no newline (rare): walk back row by row; the newline at `lead` stops the search
+        uint32_t ubase = ((n_units - 1) / (32 * kScanRows)) * (32 * kScanRows);
         while (last_nl == M2K_NONE) {
           ubase -= 32;
           uint4 w = ldg_stream(src + ubase + lane);
           uint32_t B = __ballot_sync(FULL, has_newline(w) != 0);
-          if (B) last_nl = ubase + 31 - (uint32_t)__clz(B);
+          if (B) {
+            int l = 31 - __clz(B);
+            last_nl = (ubase + l) * 16 + __shfl_sync(FULL, last_nl_byte(w), l);
+          }
         }
       }
-      trail = n_units - 1 - last_nl;
+      trail = range - 1 - last_nl;
     }
-    const uint32_t q = trail;
-    if (lane == 0) chunk_rec[item] = rec_pack(lead, q, found) | (not_df << 27);
+    if (lane == 0) chunk_rec[item] = rec_pack(lead, trail, found, not_df);
   }
 }
 
-void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec) {
+void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec) {
   if (!t->n_chunks) return;
   uint32_t warps_per_block = kScanThreads / 32;
   uint32_t want = (t->n_chunks + warps_per_block - 1) / warps_per_block;
   uint32_t cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS * M2K_SCAN_WAVES;  // resident blocks x waves
   uint32_t blocks = want < cap ? want : cap;
   k_scan_bytes<<<blocks, kScanThreads, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
-                                                       t->file_len, t->file_begin, t->bytes, t->shard_byte0, chunk_rec);
+                                                       t->file_len, t->file_begin, t->bytes, t->shard_byte0, t->first_skip, chunk_rec);
   c->launches++;
 }
 
@@ -289,85 +325,91 @@ void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec) {
 // more than 128 chunks).  Produces HAS_MAIN and
 // LONG_LINE, and the per-directory content partials for "__main__" in a file named *py.
 // ---------------------------------------------------------------------------------------------
-struct RunAcc {            // monoid over a span of 16-byte units
-  uint64_t units;          // units in the span
-  uint64_t lead, trail;    // newline-free units at both ends (== units when all free)
-  uint32_t longf;          // an exact check inside the span found a line >= 64 KiB
+struct RunAcc {            // monoid over a span of bytes of one file
+  uint64_t bytes;          // bytes in the span
+  uint64_t lead, trail;    // bytes before the first / after the last newline (== bytes when there is none)
+  uint32_t longf;          // a line closed inside the span has >= 64 KiB
 };
 
-// exact length in bytes of the newline-free run that covers units [u0, u0 + nq) of the file
-__device__ bool run_is_long(const uint8_t* file, uint64_t len, uint64_t u0, uint64_t nq) {
-  uint64_t b = u0 * 16, e = (u0 + nq) * 16;
-  if (e > len) e = len;
-  while (b > 0 && file[b - 1] != '\n') b--;
-  while (e < len && file[e] != '\n') e++;
-  // bufio.Scanner drops nothing here: the '\r' of "\r\n" counts toward the token length
-  return e - b >= kLongLine;
+__device__ __forceinline__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b) {
+  if (a.bytes == 0) return b;
+  if (b.bytes == 0) return a;
+  RunAcc r;
+  r.bytes = a.bytes + b.bytes;
+  r.longf = a.longf | b.longf;
+  const bool a_free = a.lead == a.bytes, b_free = b.lead == b.bytes;
+  r.lead = a_free ? a.bytes + b.lead : a.lead;
+  r.trail = b_free ? b.bytes + a.trail : b.trail;
+  if (!a_free && !b_free && a.trail + b.lead >= kLongLine) r.longf = 1;  // a line closed on both sides
+  return r;
 }
 
-__device__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b, const uint8_t* file, uint64_t len, uint64_t a_start_unit) {
-  if (a.units == 0) return b;
-  if (b.units == 0) return a;
-  RunAcc r;
-  r.units = a.units + b.units;
-  r.longf = a.longf | b.longf;
-  bool a_free = a.lead == a.units, b_free = b.lead == b.units;
-  r.lead = a_free ? a.units + b.lead : a.lead;
-  r.trail = b_free ? b.units + a.trail : b.trail;
-  if (!a_free && !b_free) {  // a run closed on both sides: decide it now
-    uint64_t mid = a.trail + b.lead;
-    if (mid >= kLongUnits && run_is_long(file, len, a_start_unit + a.units - a.trail, mid)) r.longf = 1;
-  }
-  return r;
+// LONG_LINE of a whole file: a closed line, or the open runs at the file's start / end
+__host__ __device__ __forceinline__ uint32_t acc_long(uint64_t bytes, uint64_t lead, uint64_t trail, uint32_t longf) {
+  if (longf) return 1;
+  if (lead >= kLongLine) return 1;  // also the file without any newline (lead == bytes)
+  return (lead != bytes && trail >= kLongLine) ? 1u : 0u;
 }
 
 constexpr uint32_t kCombineWarpChunks = 128;  // files with more chunks are folded by the whole warp
 
 struct CombineArgs {
-  uint32_t n_shard_files, file_begin;
-  const uint32_t* chunk_first; const uint32_t* chunk_rec;
-  const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
+  uint32_t n_shard_files, file_begin, first_skip, last_end;  // chunks of the first file before the shard; end chunk of the last file (M2K_NONE: all)
+  const uint32_t* chunk_first; const ChunkRec* chunk_rec;
+  const uint64_t* file_len;
   const uint32_t* file_entry; const uint32_t* entry_dir; const uint32_t* entry_name_off; const uint8_t* names;
   uint8_t* file_flags; uint32_t* dir_content; uint32_t* dir_main;
+  PieceSummary* pieces;  // [2]: the shard's first / last file when only part of it is here
 };
 
-// fold records [k0, k1) of one file; *has_main / *not_df accumulate the flag bits
-__device__ __forceinline__ RunAcc fold_records(const CombineArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t total_units,
-                                               const uint8_t* file, uint64_t len, uint32_t* has_main, uint32_t* not_df) {
+// fold records [k0, k1) (indices into the file's records present in this shard, the first of which
+// covers file bytes from `byte0`); *has_main / *not_df accumulate the flag bits
+__device__ __forceinline__ RunAcc fold_records(const CombineArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t byte0, uint64_t len,
+                                               uint32_t* has_main, uint32_t* not_df) {
   RunAcc acc{0, 0, 0, 0};
-  const uint64_t slice_start = (uint64_t)k0 * kUnitsPerChunk;
   for (uint32_t k = k0; k < k1; k++) {
-    uint32_t rec = a.chunk_rec[c0 + k];
-    uint64_t ustart = (uint64_t)k * kUnitsPerChunk;
-    uint64_t nu = total_units - ustart < kUnitsPerChunk ? total_units - ustart : kUnitsPerChunk;
-    RunAcc b{nu, rec_lead(rec), rec_trail(rec), 0};
+    ChunkRec rec = a.chunk_rec[c0 + k];
+    uint64_t bstart = byte0 + (uint64_t)k * kChunkBytes;
+    uint64_t nb = len - bstart < kChunkBytes ? len - bstart : kChunkBytes;
+    RunAcc b{nb, rec_lead(rec), rec_trail(rec), 0};
     *has_main |= rec_main(rec);
-    *not_df |= (rec >> 27) & 1u;
-    acc = acc_merge(acc, b, file, len, slice_start);
+    *not_df |= rec_not_df(rec);
+    acc = acc_merge(acc, b);
   }
   return acc;
 }
 
-__device__ __forceinline__ void finish_file(const CombineArgs& a, uint32_t f, const RunAcc& tot, const uint8_t* file, uint64_t len,
-                                            uint32_t has_main, uint32_t not_df) {
-  uint32_t longf = tot.longf;
-  if (!longf && tot.units) {
-    bool all_free = tot.lead == tot.units;
-    // runs open toward the file start / end
-    if (tot.lead >= kLongUnits && run_is_long(file, len, 0, tot.lead)) longf = 1;
-    if (!all_free && tot.trail >= kLongUnits && run_is_long(file, len, tot.units - tot.trail, tot.trail)) longf = 1;
+// "__main__" in a file whose path ends in "py": the per-directory content bit and the lowest such file id
+__device__ __forceinline__ void note_main_file(uint32_t f, const uint32_t* file_entry, const uint32_t* entry_dir, const uint32_t* entry_name_off,
+                                               const uint8_t* names, uint32_t* dir_content, uint32_t* dir_main) {
+  uint32_t e = file_entry[f];
+  uint32_t off = entry_name_off[e], nl = entry_name_off[e + 1] - off;
+  if (nl >= 2 && names[off + nl - 2] == 'p' && names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
+    uint32_t d = entry_dir[e];
+    atomicOr(&dir_content[d], 1u << M2K_C_MAIN_PY);
+    atomicMin(&dir_main[d], f);
   }
+}
+
+// i: index of the file in the shard.  A file all of whose chunks are here gets its final flags; the
+// part of a file that continues on another GPU becomes a piece summary for k_merge_pieces.
+__device__ __forceinline__ void finish_file(const CombineArgs& a, uint32_t i, uint32_t f, const RunAcc& tot, uint64_t len,
+                                            uint32_t has_main, uint32_t not_df) {
+  const bool cut_front = i == 0 && a.first_skip != 0;
+  const bool cut_back = i + 1 == a.n_shard_files && a.last_end != M2K_NONE;
+  if (cut_front || cut_back) {
+    PieceSummary ps;
+    ps.file = f;
+    ps.flags = (has_main ? PIECE_HAS_MAIN : 0u) | (tot.longf ? PIECE_LONG : 0u) | (cut_front ? 0u : PIECE_FIRST) | (not_df ? PIECE_NOT_DF : 0u);
+    ps.bytes = tot.bytes; ps.lead = tot.lead; ps.trail = tot.trail;
+    a.pieces[i == 0 ? 0 : 1] = ps;
+    a.file_flags[f] = 0;
+    return;
+  }
+  const uint32_t longf = acc_long(tot.bytes, tot.lead, tot.trail, tot.longf);
   // bit 7 is internal: "the first word already rules out a Dockerfile" (cleared again by k_df_head)
   a.file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0) | (longf ? M2K_FILE_LONG_LINE : 0) | (not_df ? 0x80 : 0));
-  if (has_main) {
-    uint32_t e = a.file_entry[f];
-    uint32_t off = a.entry_name_off[e], nl = a.entry_name_off[e + 1] - off;
-    if (nl >= 2 && a.names[off + nl - 2] == 'p' && a.names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
-      uint32_t d = a.entry_dir[e];
-      atomicOr(&a.dir_content[d], 1u << M2K_C_MAIN_PY);
-      atomicMin(&a.dir_main[d], f);
-    }
-  }
+  if (has_main) note_main_file(f, a.file_entry, a.entry_dir, a.entry_name_off, a.names, a.dir_content, a.dir_main);
 }
 
 __global__ void __launch_bounds__(256) k_file_combine(CombineArgs a) {
@@ -375,54 +417,51 @@ __global__ void __launch_bounds__(256) k_file_combine(CombineArgs a) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = i < a.n_shard_files;
   uint32_t f = 0, c0 = 0, nc = 0;
-  uint64_t len = 0;
-  const uint8_t* file = nullptr;
+  uint64_t len = 0, byte0 = 0;
   if (valid) {
     f = a.file_begin + i;
     len = a.file_len[f];
-    file = a.bytes + (a.file_off[f] - a.shard_byte0);
     c0 = a.chunk_first[i];
     nc = a.chunk_first[i + 1] - c0;
+    byte0 = i == 0 ? (uint64_t)a.first_skip * kChunkBytes : 0;
   }
-  const uint64_t total_units = (len + 15) >> 4;
   if (valid && nc <= kCombineWarpChunks) {  // the common case: one thread, a handful of records
     uint32_t has_main = 0, not_df = 0;
-    RunAcc tot = fold_records(a, c0, 0, nc, total_units, file, len, &has_main, &not_df);
-    finish_file(a, f, tot, file, len, has_main, not_df);
+    RunAcc tot = fold_records(a, c0, 0, nc, byte0, len, &has_main, &not_df);
+    finish_file(a, i, f, tot, len, has_main, not_df);
   }
   // files with many chunks (config D's multi-GiB files): the warp folds them together, one at a time
   uint32_t big = __ballot_sync(FULL, valid && nc > kCombineWarpChunks);
   while (big) {
     const int src = __ffs(big) - 1;
     big &= big - 1;
-    const uint32_t bf = __shfl_sync(FULL, f, src), bc0 = __shfl_sync(FULL, c0, src), bnc = __shfl_sync(FULL, nc, src);
-    const uint64_t blen = __shfl_sync(FULL, len, src);
-    const uint8_t* bfile = reinterpret_cast<const uint8_t*>(__shfl_sync(FULL, reinterpret_cast<unsigned long long>(file), src));
-    const uint64_t bunits = (blen + 15) >> 4;
+    const uint32_t bi = __shfl_sync(FULL, i, src), bf = __shfl_sync(FULL, f, src), bc0 = __shfl_sync(FULL, c0, src), bnc = __shfl_sync(FULL, nc, src);
+    const uint64_t blen = __shfl_sync(FULL, len, src), bbyte0 = __shfl_sync(FULL, byte0, src);
     const uint32_t per = (bnc + 31) / 32;
     const uint32_t k0 = lane * per < bnc ? lane * per : bnc, k1 = (lane + 1) * per < bnc ? (lane + 1) * per : bnc;
     uint32_t has_main = 0, not_df = 0;
-    RunAcc acc = fold_records(a, bc0, k0, k1, bunits, bfile, blen, &has_main, &not_df);
+    RunAcc acc = fold_records(a, bc0, k0, k1, bbyte0, blen, &has_main, &not_df);
     has_main = __any_sync(FULL, has_main);
     not_df = __any_sync(FULL, not_df);
     RunAcc tot{0, 0, 0, 0};
     for (int l = 0; l < 32; l++) {
       RunAcc b;
-      b.units = __shfl_sync(FULL, acc.units, l);
+      b.bytes = __shfl_sync(FULL, acc.bytes, l);
       b.lead = __shfl_sync(FULL, acc.lead, l);
       b.trail = __shfl_sync(FULL, acc.trail, l);
       b.longf = __shfl_sync(FULL, acc.longf, l);
-      if (lane == 0) tot = acc_merge(tot, b, bfile, blen, 0);
+      if (lane == 0) tot = acc_merge(tot, b);
     }
-    if (lane == 0) finish_file(a, bf, tot, bfile, blen, has_main, not_df);
+    if (lane == 0) finish_file(a, bi, bf, tot, blen, has_main, not_df);
   }
 }
 
-void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec) {
+void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
   uint32_t nf = t->file_end - t->file_begin;
+  cudaMemsetAsync(t->pieces, 0xFF, 2 * sizeof(PieceSummary), c->stream);  // file == M2K_NONE: unused slot
   if (!nf) return;
-  CombineArgs a{nf, t->file_begin, t->chunk_first, chunk_rec, t->file_off, t->file_len, t->bytes, t->shard_byte0,
-                t->file_entry, t->entry_dir, t->entry_name_off, t->names, t->file_flags, t->dir_content, t->dir_main};
+  CombineArgs a{nf, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec, t->file_len,
+                t->file_entry, t->entry_dir, t->entry_name_off, t->names, t->file_flags, t->dir_content, t->dir_main, t->pieces};
   k_file_combine<<<(nf + 255) / 256, 256, 0, c->stream>>>(a);
   c->launches++;
 }
@@ -441,7 +480,8 @@ void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec) {
 // host never waits for them.
 // ---------------------------------------------------------------------------------------------
 struct DfArgs {
-  uint32_t n_shard_files, file_begin;
+  uint32_t n_shard_files, file_begin, first_skip, last_end;
+  PieceSummary* pieces;
   const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
   const uint32_t* file_entry; const uint32_t* entry_dir;
   uint8_t* file_flags; uint32_t* dir_content;
@@ -459,10 +499,24 @@ __global__ void __launch_bounds__(128) k_df_head(DfArgs a) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.n_shard_files) return;
   uint32_t f = a.file_begin + i;
-  uint32_t flags = a.file_flags[f];
-  if (flags & 0x80) { a.file_flags[f] = (uint8_t)(flags & 0x7F); return; }  // ruled out by the scan kernel (first word)
   uint64_t body = 0, n = a.file_len[f];
   uint32_t esc = '\\';
+  const bool cut_front = i == 0 && a.first_skip != 0;
+  const bool cut_back = i + 1 == a.n_shard_files && a.last_end != M2K_NONE;
+  if (cut_front || cut_back) {
+    // only part of this file is here.  When that part starts the file, settle what its head can settle;
+    // the body of a FROM-first file cannot be validated from a piece (see k_merge_pieces).
+    PieceSummary* ps = &a.pieces[i == 0 ? 0 : 1];
+    if (!cut_front && !(ps->flags & PIECE_NOT_DF)) {
+      uint64_t n_here = (uint64_t)a.last_end * kChunkBytes;  // cut_back holds, so this is < n
+      bool touched_end = false;
+      bool from = df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n_here, false, &body, &esc, &touched_end);
+      ps->flags |= touched_end ? PIECE_HEAD_TRUNC : (from ? PIECE_HEAD_FROM : PIECE_HEAD_NOT_FROM);
+    }
+    return;
+  }
+  uint32_t flags = a.file_flags[f];
+  if (flags & 0x80) { a.file_flags[f] = (uint8_t)(flags & 0x7F); return; }  // ruled out by the scan kernel (first word)
   if (!df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n, (flags & M2K_FILE_LONG_LINE) != 0, &body, &esc)) return;
   a.file_flags[f] = (uint8_t)(flags | M2K_FILE_FROM_FIRST);
   uint32_t c = atomicAdd(&a.counters[0], 1u);
@@ -563,7 +617,7 @@ __global__ void __launch_bounds__(128) k_df_finish(DfArgs a) {
 void launch_dockerfile(Ctx* c, DevTree* t) {
   uint32_t nf = t->file_end - t->file_begin;
   if (!nf) return;
-  DfArgs a{nf, t->file_begin, t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir,
+  DfArgs a{nf, t->file_begin, t->first_skip, t->last_end, t->pieces, t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir,
            t->file_flags, t->dir_content, t->df_counters, t->cand_file, t->cand_body, t->cand_esc, t->cand_first, t->cand_err,
            t->stripe_state, t->stripe_cap};
   cudaMemsetAsync(t->df_counters, 0, 8, c->stream);
@@ -803,13 +857,75 @@ void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, cons
   c->launches++;
 }
 
+// Pieces of files that were scanned on several GPUs, in rank order (slot 0 then slot 1 of each rank;
+// unused slots have file == M2K_NONE): consecutive pieces of one file are stitched with the same
+// monoid the combine kernel uses.  One thread: there are at most two pieces per rank.
+// isDockerFile for such a file: the first word or the head (parsed on the GPU that holds the start of
+// the file) or a long line usually settles it; a FROM-first file without a long line would need its
+// body validated across GPUs, which no piece can do alone -- it is marked M2K_FILE_UNDECIDED and the
+// caller settles it with a pass over that one file (m2k_upload of [f, f+1)).
+struct MergePiecesArgs {
+  const uint64_t* file_len; const uint32_t* file_entry; const uint32_t* entry_dir; const uint32_t* entry_name_off; const uint8_t* names;
+  uint8_t* file_flags; uint32_t* dir_content; uint32_t* dir_main;
+};
+__global__ void k_merge_pieces(const PieceSummary* __restrict__ all, uint32_t n, MergePiecesArgs a) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  uint32_t k = 0;
+  while (k < n) {
+    if (all[k].file == M2K_NONE) { k++; continue; }
+    const uint32_t f = all[k].file;
+    RunAcc tot{0, 0, 0, 0};
+    uint32_t flags = 0;
+    bool first_seen = false;
+    for (; k < n; k++) {
+      const PieceSummary ps = all[k];
+      if (ps.file == M2K_NONE) continue;
+      if (ps.file != f) break;
+      if (tot.bytes == 0) first_seen = (ps.flags & PIECE_FIRST) != 0;
+      RunAcc b{ps.bytes, ps.lead, ps.trail, (ps.flags & PIECE_LONG) ? 1u : 0u};
+      tot = acc_merge(tot, b);
+      flags |= ps.flags;
+    }
+    uint32_t out;
+    if (!first_seen || tot.bytes != a.file_len[f]) {
+      out = M2K_FILE_UNDECIDED;  // pieces missing (a caller gathered fewer ranks than it sharded over)
+    } else {
+      const uint32_t longf = acc_long(tot.bytes, tot.lead, tot.trail, tot.longf);
+      out = ((flags & PIECE_HAS_MAIN) ? M2K_FILE_HAS_MAIN : 0u) | (longf ? M2K_FILE_LONG_LINE : 0u);
+      const bool settled_no = (flags & (PIECE_NOT_DF | PIECE_HEAD_NOT_FROM)) || longf;
+      if (!settled_no) out |= M2K_FILE_UNDECIDED;
+      if (flags & PIECE_HAS_MAIN) note_main_file(f, a.file_entry, a.entry_dir, a.entry_name_off, a.names, a.dir_content, a.dir_main);
+    }
+    a.file_flags[f] = (uint8_t)out;
+  }
+}
+
+__global__ void k_settle_file(uint32_t f, uint32_t flags, const uint32_t* __restrict__ file_entry, const uint32_t* __restrict__ entry_dir,
+                              uint8_t* __restrict__ file_flags, uint32_t* __restrict__ dir_content) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  file_flags[f] = (uint8_t)flags;
+  if (flags & M2K_FILE_DOCKERFILE) atomicOr(&dir_content[entry_dir[file_entry[f]]], 1u << M2K_C_DOCKERFILE);
+}
+void launch_settle_file(Ctx* c, DevTree* t, uint32_t f, uint32_t flags) {
+  k_settle_file<<<1, 32, 0, c->stream>>>(f, flags, t->file_entry, t->entry_dir, t->file_flags, t->dir_content);
+  c->launches++;
+}
+
+void launch_merge_pieces(Ctx* c, DevTree* t, const PieceSummary* all_pieces, uint32_t n_pieces) {
+  if (!n_pieces) return;
+  MergePiecesArgs a{t->file_len, t->file_entry, t->entry_dir, t->entry_name_off, t->names, t->file_flags, t->dir_content, t->dir_main};
+  k_merge_pieces<<<1, 32, 0, c->stream>>>(all_pieces, n_pieces, a);
+  c->launches++;
+}
+
 // ---------------------------------------------------------------------------------------------
 // synthetic content, generated in place in HBM (same function as the host fill, synth.h)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_synth_fill(
     uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first, const uint64_t* __restrict__ file_off,
     const uint64_t* __restrict__ file_len, uint32_t file_begin, const uint8_t* __restrict__ synth_class,
-    const uint64_t* __restrict__ synth_inject, uint64_t seed, uint8_t* __restrict__ bytes, uint64_t shard_byte0) {
+    const uint64_t* __restrict__ synth_inject, uint64_t seed, uint8_t* __restrict__ bytes, uint64_t shard_byte0,
+    uint32_t first_skip, uint32_t last_end) {
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t n_warps = gridDim.x * (blockDim.x / 32);
   for (uint32_t item = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5); item < n_chunks; item += n_warps) {
@@ -817,7 +933,7 @@ __global__ void __launch_bounds__(256) k_synth_fill(
     while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (chunk_first[mid] <= item) lo = mid; else hi = mid; }
     uint32_t f = file_begin + lo;
     uint64_t flen = file_len[f];
-    uint64_t ublock0 = (uint64_t)(item - chunk_first[lo]) * kUnitsPerChunk;
+    uint64_t ublock0 = (uint64_t)(item - chunk_first[lo] + (lo == 0 ? first_skip : 0u)) * kUnitsPerChunk;
     uint64_t total_units = (flen + 15) >> 4;
     uint32_t n_units = (uint32_t)(total_units - ublock0 < kUnitsPerChunk ? total_units - ublock0 : kUnitsPerChunk);
     uint64_t key = synth_file_key(seed, f);
@@ -829,6 +945,17 @@ __global__ void __launch_bounds__(256) k_synth_fill(
       synth_block16(key, cls, flen, inj, ublock0 + u, blk.b);
       dst[u] = blk.v;
     }
+    // a shard that is cut through a file also holds the 16 bytes on the far side of each cut
+    if (lane == 0 && item == 0 && first_skip != 0) {
+      union { uint8_t b[16]; uint4 v; } blk;
+      synth_block16(key, cls, flen, inj, ublock0 - 1, blk.b);
+      *(reinterpret_cast<uint4*>(bytes + (file_off[f] - shard_byte0)) + (ublock0 - 1)) = blk.v;
+    }
+    if (lane == 0 && item + 1 == n_chunks && last_end != M2K_NONE) {
+      union { uint8_t b[16]; uint4 v; } blk;
+      synth_block16(key, cls, flen, inj, ublock0 + n_units, blk.b);
+      dst[n_units] = blk.v;
+    }
   }
 }
 
@@ -838,7 +965,7 @@ void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed) {
   uint32_t cap = (uint32_t)c->sm_count * 8 * 4;
   k_synth_fill<<<want < cap ? want : cap, 256, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
                                                                 t->file_len, t->file_begin, t->synth_class, t->synth_inject, seed,
-                                                                t->bytes, t->shard_byte0);
+                                                                t->bytes, t->shard_byte0, t->first_skip, t->last_end);
   c->launches++;
 }
 

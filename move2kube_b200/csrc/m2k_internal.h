@@ -13,16 +13,39 @@ constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one war
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
 constexpr uint32_t kDfStripe = 1024;     // bytes of one stripe of the parallel Dockerfile validation
 constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
-constexpr uint32_t kLongUnits = (kLongLine - 30 + 15) / 16;  // newline-free 16-byte units a long line must contain (4095)
+// per-chunk record written by the byte-scan kernel: scratch memory, 8 bytes per 64 KiB chunk, exact
+// to the byte so that records of one file can be stitched anywhere (another kernel, another GPU)
+// without looking at the file again
+//   bits  0..16  lead : bytes before the first newline of the chunk (== bytes in the chunk when it has none)
+//   bits 17..33  trail: bytes after the last newline of the chunk  (== bytes in the chunk when it has none)
+//   bit  34      the chunk contains the start of a "__main__"
+//   bit  35      (first chunk of a file) the first word already rules out a Dockerfile
+typedef uint64_t ChunkRec;
+__host__ __device__ inline ChunkRec rec_pack(uint32_t lead, uint32_t trail, uint32_t has_main, uint32_t not_df) {
+  return (ChunkRec)lead | ((ChunkRec)trail << 17) | ((ChunkRec)has_main << 34) | ((ChunkRec)not_df << 35);
+}
+__host__ __device__ inline uint32_t rec_lead(ChunkRec r) { return (uint32_t)(r & 0x1FFFF); }
+__host__ __device__ inline uint32_t rec_trail(ChunkRec r) { return (uint32_t)((r >> 17) & 0x1FFFF); }
+__host__ __device__ inline uint32_t rec_main(ChunkRec r) { return (uint32_t)((r >> 34) & 1); }
+__host__ __device__ inline uint32_t rec_not_df(ChunkRec r) { return (uint32_t)((r >> 35) & 1); }
 
-// per-chunk record written by the byte-scan kernel: scratch memory, 4 bytes per 64 KiB chunk
-//   bits  0..12  lead : newline-free 16-byte units at the start of the chunk (== units in chunk when none has a newline)
-//   bits 13..25  trail: newline-free 16-byte units at the end of the chunk
-//   bit  26      the chunk contains the start of a "__main__"
-__host__ __device__ inline uint32_t rec_pack(uint32_t lead, uint32_t trail, uint32_t has_main) { return lead | (trail << 13) | (has_main << 26); }
-__host__ __device__ inline uint32_t rec_lead(uint32_t r) { return r & 0x1FFF; }
-__host__ __device__ inline uint32_t rec_trail(uint32_t r) { return (r >> 13) & 0x1FFF; }
-__host__ __device__ inline uint32_t rec_main(uint32_t r) { return (r >> 26) & 1; }
+// A shard is a range of 64 KiB chunks and may begin and end inside a (large) file.  The at most two
+// files it holds only part of are folded into piece summaries instead of final flags; the pieces of
+// a file are stitched in rank order after the exchange (k_merge_pieces).  32 bytes, exchanged as is.
+struct PieceSummary {
+  uint32_t file;         // file id; M2K_NONE = unused slot
+  uint32_t flags;        // PIECE_*
+  uint64_t bytes;        // content bytes of the file covered by this piece
+  uint64_t lead, trail;  // bytes before the first / after the last newline of the piece (== bytes when it has none)
+};
+enum : uint32_t {
+  PIECE_HAS_MAIN = 1, PIECE_LONG = 2,
+  PIECE_FIRST = 4,           // the piece starts at byte 0 of the file
+  PIECE_NOT_DF = 8,          // the first word rules out a Dockerfile
+  PIECE_HEAD_NOT_FROM = 16,  // the head was parsed within this piece: the first instruction is not FROM / parse error
+  PIECE_HEAD_FROM = 32,      // ... it is a FROM line: the body must be validated over the whole file
+  PIECE_HEAD_TRUNC = 64      // the head runs past this piece
+};
 
 // name signature table staged into shared memory by the name-feature kernel
 struct NameSig {
@@ -46,7 +69,10 @@ __host__ __device__ inline uint32_t slot_flags(uint32_t lf) { return lf >> 29; }
 struct DevTree {
   const m2k_tree* host = nullptr;
   uint32_t n_dirs = 0, n_entries = 0, n_files = 0, max_depth = 0;
-  uint32_t file_begin = 0, file_end = 0;  // shard
+  uint32_t file_begin = 0, file_end = 0;  // shard: the files it touches
+  uint32_t first_skip = 0;                // chunks of file `file_begin` that precede the shard (on another GPU)
+  uint32_t last_end = M2K_NONE;           // end chunk (within the file) of file `file_end - 1` when the shard stops inside it
+  PieceSummary* pieces = nullptr;         // [2] device
   uint64_t shard_bytes = 0;               // padded bytes resident
   uint64_t shard_content = 0;             // sum of file_len over the shard
   uint64_t shard_byte0 = 0;               // file_off[file_begin]
@@ -65,7 +91,7 @@ struct DevTree {
   uint8_t* synth_class = nullptr;
   uint64_t* synth_inject = nullptr;
   // work buffers
-  uint32_t* chunk_rec = nullptr;          // [n_chunks] scratch
+  ChunkRec* chunk_rec = nullptr;          // [n_chunks] scratch
   // isDockerFile scratch: candidate list and per-stripe line states (worst case: every file a candidate)
   uint32_t* df_counters = nullptr;        // [2]
   uint32_t *cand_file = nullptr, *cand_first = nullptr, *cand_err = nullptr;
@@ -112,8 +138,8 @@ struct Ctx {
 
 // ---- kernel launchers (kernels.cu) ----
 void launch_name_features(Ctx* c, DevTree* t);
-void launch_scan_bytes(Ctx* c, DevTree* t, uint32_t* chunk_rec);
-void launch_file_combine(Ctx* c, DevTree* t, const uint32_t* chunk_rec);
+void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec);
+void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec);
 void launch_dockerfile(Ctx* c, DevTree* t);
 void launch_subtree(Ctx* c, DevTree* t);
 void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor);
@@ -122,6 +148,8 @@ void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mas
 void fold_runes(const std::string& s, std::vector<uint32_t>* out);
 std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clean_root);
 void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, const uint32_t* all_main, uint32_t n_ranks);
+void launch_merge_pieces(Ctx* c, DevTree* t, const PieceSummary* all_pieces, uint32_t n_pieces);
+void launch_settle_file(Ctx* c, DevTree* t, uint32_t f, uint32_t flags);
 void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed);
 void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
 

@@ -5,10 +5,10 @@
 // service whose device memory is handed out once at start-up by its own arena and then locked, or a
 // process sharing the GPU under a fixed memory quota.  cudaMalloc there either fails, or stalls the
 // whole device while the driver maps memory.  Those callers own every buffer they pass in; the only
-// memory the scan needs beyond its inputs and outputs is the per-chunk record table (4 bytes per
+// memory the scan needs beyond its inputs and outputs is the per-chunk record table (8 bytes per
 // 64 KiB of content), and here that table lives in a fixed array inside the library image.
 //
-// The array costs kNoAllocMaxChunks * 4 bytes (1 MiB) on EVERY GPU that loads the library, until the
+// The array costs kNoAllocMaxChunks * 8 bytes (2 MiB) on EVERY GPU that loads the library, until the
 // process exits, whether or not this entry point is ever called.  That bounds one call to
 // kNoAllocMaxChunks chunks (16 GiB when every chunk is full); larger inputs are refused.
 //
@@ -28,48 +28,36 @@
 
 namespace m2k {
 
-constexpr uint32_t kNoAllocMaxChunks = 262144;  // 1 MiB of records
+constexpr uint32_t kNoAllocMaxChunks = 262144;  // 2 MiB of records
 
 // In host code this name is only a handle for the runtime, not an address a kernel can use.
-static __device__ __align__(256) uint32_t g_noalloc_records[kNoAllocMaxChunks];
+static __device__ __align__(256) ChunkRec g_noalloc_records[kNoAllocMaxChunks];
 
 constexpr int kMaxDevices = 64;
 static std::mutex g_setup_mutex;
-static uint32_t* g_records_ptr[kMaxDevices];  // device address of g_noalloc_records, per device
+static ChunkRec* g_records_ptr[kMaxDevices];  // device address of g_noalloc_records, per device
 static int g_sm_count[kMaxDevices];
 
-// Per-file flags from the chunk records: one thread per file walks its records in order, keeps the
-// count of newline-free 16-byte units since the last newline, and settles the (rare) runs of 4095 or
-// more units by counting bytes.  Device code may name the array directly.
+// Per-file flags from the chunk records: one thread per file walks its records in order and keeps
+// the bytes since the last newline; the records are exact to the byte, so the file itself is not
+// looked at again.  Device code may name the array directly.
 __global__ void __launch_bounds__(128) k_noalloc_file_flags(uint32_t n_files, const uint32_t* __restrict__ chunk_first,
-                                                             const uint64_t* __restrict__ file_off,
-                                                             const uint64_t* __restrict__ file_len,
-                                                             const uint8_t* __restrict__ bytes, uint8_t* __restrict__ file_flags) {
+                                                             const uint64_t* __restrict__ file_len, uint8_t* __restrict__ file_flags) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_files) return;
   const uint64_t len = file_len[f];
-  const uint8_t* file = bytes + file_off[f];
-  const uint64_t total_units = (len + 15) >> 4;
   uint32_t has_main = 0, is_long = 0;
-  uint64_t run = 0;  // newline-free units immediately before the current chunk
-  auto exact_long = [&](uint64_t first_unit, uint64_t units) {
-    uint64_t b = first_unit * 16, e = (first_unit + units) * 16;
-    if (e > len) e = len;
-    while (b > 0 && file[b - 1] != '\n') b--;
-    while (e < len && file[e] != '\n') e++;
-    return e - b >= kLongLine;
-  };
+  uint64_t run = 0;  // bytes since the last newline (or since the start of the file)
   for (uint32_t c = chunk_first[f], k = 0; c < chunk_first[f + 1]; c++, k++) {
-    const uint32_t rec = g_noalloc_records[c];
-    const uint64_t u0 = (uint64_t)k * kUnitsPerChunk;
-    const uint64_t nu = total_units - u0 < kUnitsPerChunk ? total_units - u0 : kUnitsPerChunk;
+    const ChunkRec rec = g_noalloc_records[c];
+    const uint64_t b0 = (uint64_t)k * kChunkBytes;
+    const uint64_t nb = len - b0 < kChunkBytes ? len - b0 : kChunkBytes;
     has_main |= rec_main(rec);
-    if (rec_lead(rec) == nu) { run += nu; continue; }  // no newline in this chunk
-    const uint64_t closed = run + rec_lead(rec);
-    if (closed >= kLongUnits && exact_long(u0 - run, closed)) is_long = 1;
+    if (rec_lead(rec) == nb) { run += nb; continue; }  // no newline in this chunk
+    if (run + rec_lead(rec) >= kLongLine) is_long = 1;
     run = rec_trail(rec);
   }
-  if (run >= kLongUnits && exact_long(total_units - run, run)) is_long = 1;
+  if (run >= kLongLine) is_long = 1;
   file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0) | (is_long ? M2K_FILE_LONG_LINE : 0));
 }
 
@@ -103,7 +91,7 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
     // set-up, once per device, with that device current
     std::lock_guard<std::mutex> lock(g_setup_mutex);
     if (!g_records_ptr[device]) {
-      uint32_t* ptr = nullptr;
+      ChunkRec* ptr = nullptr;
       e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_records);
       if (e != cudaSuccess || !ptr)
         return noalloc_fail(M2K_ERR_CUDA, "cudaGetSymbolAddress(record table) on device %d: %s", device, cudaGetErrorString(e));
@@ -132,7 +120,7 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
   t.bytes = const_cast<uint8_t*>(d_bytes);
   t.shard_byte0 = 0;
   launch_scan_bytes(&c, &t, g_records_ptr[device]);
-  k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, d_chunk_first, d_file_off, d_file_len, d_bytes, d_file_flags);
+  k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, d_chunk_first, d_file_len, d_file_flags);
   e = cudaGetLastError();
   if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: kernel launch: %s", cudaGetErrorString(e));
   return M2K_OK;

@@ -28,6 +28,8 @@ EXPORTS = [
     "m2k_upload", "m2k_synth_fill_device", "m2k_scan", "m2k_partials", "m2k_merge_partials", "m2k_file_flags_get", "m2k_file_flags_set", "m2k_prepare", "m2k_finalize",
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
+    "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
+    "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file",
 ]
 
 
@@ -82,6 +84,15 @@ def load():
     L.m2k_equal_fold.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.m2k_list_entries.argtypes = [TP, C.c_uint32, _abi.u32p, _abi.u32p, C.c_uint32]
     L.m2k_scan_flags_noalloc.argtypes = [C.c_int, vp, vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp]
+    L.m2k_chunk_count.argtypes = [TP]
+    L.m2k_chunk_count.restype = C.c_uint64
+    L.m2k_plan_shards.argtypes = [TP, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.m2k_upload_chunks.argtypes = [vp, TP, C.c_uint64, C.c_uint64, C.POINTER(vp)]
+    L.m2k_pieces.argtypes = [vp, vp, vp]
+    L.m2k_merge_pieces.argtypes = [vp, vp, vp, C.c_uint32]
+    L.m2k_chunk_locate.argtypes = [TP, C.c_uint64, _abi.u32p, _abi.u32p]
+    L.m2k_file_flag.argtypes = [vp, vp, C.c_uint32, C.POINTER(C.c_uint8)]
+    L.m2k_settle_file.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -172,6 +183,25 @@ class Context:
         _check(self.L.m2k_upload(self.h, tree, file_begin, file_end, C.byref(h)), self.h)
         return h
 
+    def upload_chunks(self, tree, chunk_begin, chunk_end):
+        h = C.c_void_p()
+        _check(self.L.m2k_upload_chunks(self.h, tree, chunk_begin, chunk_end, C.byref(h)), self.h)
+        return h
+
+    def pieces(self, dt, dst_ptr):
+        _check(self.L.m2k_pieces(self.h, dt, dst_ptr), self.h)
+
+    def merge_pieces(self, dt, all_pieces_ptr, n_ranks):
+        _check(self.L.m2k_merge_pieces(self.h, dt, all_pieces_ptr, n_ranks), self.h)
+
+    def file_flag(self, dt, f) -> int:
+        out = C.c_uint8()
+        _check(self.L.m2k_file_flag(self.h, dt, f, C.byref(out)), self.h)
+        return out.value
+
+    def settle_file(self, dt, f, flags):
+        _check(self.L.m2k_settle_file(self.h, dt, f, flags), self.h)
+
     def synth_fill_device(self, dt, seed):
         _check(self.L.m2k_synth_fill_device(self.h, dt, seed), self.h)
 
@@ -241,6 +271,25 @@ def synth_tree_host(params: _abi.SynthParams, host_bytes=True):
 
 def tree_free_host(tree):
     load().m2k_tree_free(None, tree)
+
+
+def chunk_count(tree) -> int:
+    return load().m2k_chunk_count(tree)
+
+
+def plan_shards(tree, n_ranks, split_min_bytes=64 << 20):
+    """n_ranks + 1 chunk cut points of near-equal bytes; a file is cut only if it has at least
+    `split_min_bytes` bytes."""
+    cuts = (C.c_uint64 * (n_ranks + 1))()
+    _check(load().m2k_plan_shards(tree, n_ranks, split_min_bytes, cuts))
+    return list(cuts)
+
+
+def chunk_locate(tree, chunk):
+    """(file id, chunk index inside that file) of a global chunk number."""
+    f, k = C.c_uint32(), C.c_uint32()
+    _check(load().m2k_chunk_locate(tree, chunk, C.byref(f), C.byref(k)))
+    return f.value, k.value
 
 
 def path_clean(p: bytes) -> bytes:

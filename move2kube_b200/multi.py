@@ -10,6 +10,8 @@ directory-level phases run replicated.
 from bisect import bisect_left
 from itertools import accumulate
 
+from . import _abi, lib
+
 
 def shard_ranges(file_len, world):
     """Contiguous [begin, end) file-id ranges, one per rank, covering all files, near-equal in bytes.
@@ -36,3 +38,36 @@ def gather_partials(dist, mine, out=None):
         out = torch.empty((world,) + tuple(mine.shape), dtype=mine.dtype, device=mine.device)
     dist.all_gather_into_tensor(out.view(-1), mine.contiguous().view(-1))
     return out
+
+
+def split_files(tree, cuts):
+    """Files that the chunk cut points `cuts` (lib.plan_shards) divide between ranks."""
+    total = cuts[-1]
+    out = []
+    for c in cuts[1:-1]:
+        if 0 < c < total:
+            f, k = lib.chunk_locate(tree, c)
+            if k != 0 and f not in out:
+                out.append(f)
+    return out
+
+
+def settle_undecided(ctx, tree, dt, files, fill_seed=None):
+    """On the rank that finalises, after merge_pieces and before finalize: a file that was spread over
+    several GPUs and still looks like a Dockerfile (M2K_FILE_UNDECIDED) gets one pass of its own -- the
+    file is the unit again -- and its flags are written back.  Returns the files settled this way.
+    `fill_seed`: the tree's bytes live only on the device (synthetic trees)."""
+    settled = []
+    for f in files:
+        if not ctx.file_flag(dt, f) & _abi.FILE_UNDECIDED:
+            continue
+        one = ctx.upload(tree, f, f + 1)
+        try:
+            if fill_seed is not None:
+                ctx.synth_fill_device(one, fill_seed)
+            ctx.scan(one)
+            ctx.settle_file(dt, f, ctx.file_flag(one, f) & 0xF)
+        finally:
+            ctx.devtree_free(one)
+        settled.append(f)
+    return settled

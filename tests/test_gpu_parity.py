@@ -266,3 +266,137 @@ def test_very_deep_tree(ctx, oracle, tmp_path):
     oracle.lib().m2ko_result_free(ores)
     ctx.result_free(res)
     ctx.tree_free(tree)
+
+
+# ---- shards cut through files -------------------------------------------
+def run_chunk_sharded(ctx, tree, cuts, fill_seed=None):
+    """Emulates an N-rank pass on one GPU: every shard [cuts[r], cuts[r+1]) is uploaded and scanned on its
+    own, partials / file flags / pieces are exchanged the way the ranks exchange them (rank order),
+    and shard 0 merges, settles and finalises.  Returns (result, devtrees, settled files)."""
+    import torch
+    from move2kube_b200 import multi
+    n = len(cuts) - 1
+    nd, nf = tree.contents.n_dirs, tree.contents.n_files
+    dts = []
+    for r in range(n):
+        dt = ctx.upload_chunks(tree, cuts[r], cuts[r + 1])
+        if fill_seed is not None:
+            ctx.synth_fill_device(dt, fill_seed)
+        ctx.scan(dt)
+        dts.append(dt)
+    allc = torch.empty((n, nd), dtype=torch.int32, device="cuda")
+    allm = torch.empty((n, nd), dtype=torch.int32, device="cuda")
+    pieces = torch.empty((n, 64), dtype=torch.uint8, device="cuda")
+    flags = torch.zeros((nf,), dtype=torch.uint8, device="cuda")
+    one = torch.empty((nf,), dtype=torch.uint8, device="cuda")
+    for r, dt in enumerate(dts):
+        ctx.partials(dt, allc[r].data_ptr(), allm[r].data_ptr())
+        ctx.pieces(dt, pieces[r].data_ptr())
+        ctx.file_flags_get(dt, one.data_ptr())
+        torch.cuda.synchronize()
+        flags += one
+    torch.cuda.synchronize()
+    ctx.merge_partials(dts[0], allc.data_ptr(), allm.data_ptr(), n)
+    ctx.file_flags_set(dts[0], flags.data_ptr())
+    ctx.merge_pieces(dts[0], pieces.data_ptr(), n)
+    settled = multi.settle_undecided(ctx, tree, dts[0], multi.split_files(tree, cuts), fill_seed)
+    return ctx.finalize(dts[0]), dts, settled
+
+
+def assert_same_result(tree, got, want):
+    t, g, w = tree.contents, got.contents, want.contents
+    nd, nf = t.n_dirs, t.n_files
+    assert g.file_flags[0:nf] == w.file_flags[0:nf]
+    for name in ("dir_state", "dir_opts", "dir_main_file", "dir_subtree", "dir_direct", "dir_ignore"):
+        assert getattr(g, name)[0:nd] == getattr(w, name)[0:nd], name
+    assert g.service_dirs[0:g.n_services] == w.service_dirs[0:w.n_services]
+
+
+@pytest.mark.parametrize("world", [2, 3, 5])
+def test_chunk_shards_of_a_synthetic_tree_merge_to_the_whole(ctx, oracle, world):
+    """Multi-MiB files spread over several shards, bytes generated on the device shard by shard."""
+    p = _abi.SynthParams(seed=21, n_files=1500, n_dirs=90, max_depth=5, n_ignore_files=3, total_bytes=60 << 20,
+                         n_huge=3, huge_bytes=9 << 20, n_large=2, large_bytes=3 << 20)
+    tree = ctx.synth_tree(p, host_bytes=True)
+    try:
+        whole = ctx.detect(tree)
+        ores = oracle.detect(tree)
+        compare_with_oracle(oracle, tree, whole, ores)
+        oracle.lib().m2ko_result_free(ores)
+        cuts = lib.plan_shards(tree, world, 1 << 20)
+        from move2kube_b200 import multi
+        assert multi.split_files(tree, cuts), "the plan should cut through at least one large file"
+        for seed in (None, p.seed):  # bytes uploaded from the host / generated in HBM
+            res, dts, _ = run_chunk_sharded(ctx, tree, cuts, fill_seed=seed)
+            assert_same_result(tree, res, whole)
+            ctx.result_free(res)
+            for dt in dts:
+                ctx.devtree_free(dt)
+        ctx.result_free(whole)
+    finally:
+        ctx.tree_free(tree)
+
+
+def _big_file_tree(root):
+    """Files of a few 64 KiB chunks whose interesting bytes sit exactly on chunk boundaries."""
+    CH = 65536
+    os.makedirs(root / "app")
+    line = b"x = 1  # padding line of text\n"
+    def text(n):
+        return (line * (n // len(line) + 1))[:n - 1] + b"\n"
+    # "__main__" straddling the boundary between chunks 1 and 2 at every offset
+    for k in range(1, 8):
+        body = bytearray(text(5 * CH - 100))
+        body[2 * CH - k:2 * CH - k + 8] = b"__main__"
+        (root / "app" / ("m%d.py" % k)).write_bytes(bytes(body))
+    (root / "app" / "requirements.txt").write_bytes(b"flask\n")
+    # a line of exactly 65536 / 65535 bytes straddling a boundary
+    for name, n in (("long.txt", 65536), ("short.txt", 65535)):
+        (root / name).write_bytes(text(CH + 1000) + b"y" * n + b"\n" + text(2 * CH))
+    # one very long line covering several whole chunks
+    (root / "huge_line.bin").write_bytes(text(CH // 2) + b"z" * (3 * CH) + b"\n" + text(CH))
+    # no newline at all
+    (root / "nonl.bin").write_bytes(b"q" * (2 * CH + 17))
+    # a large valid Dockerfile, a large invalid one (error deep in the body), one whose head is longer than a chunk
+    run = b"RUN echo hello && \\\n    echo world\n"
+    (root / "Dockerfile.big").write_bytes(b"FROM alpine:3 AS base\n" + run * (3 * CH // len(run)))
+    (root / "Dockerfile.bad").write_bytes(b"FROM alpine:3\n" + run * (2 * CH // len(run)) + b"ENV onlykey\n" + run * 100)
+    (root / "Dockerfile.comments").write_bytes(b"# a comment line that is not a directive\n" * (CH // 20) + b"ARG V=1\nFROM alpine:$V\n" + run * 50)
+    (root / "notes.big").write_bytes(b"hello world, this is not a Dockerfile\n" * (4 * CH // 38))
+    (root / "blob.big").write_bytes(bytes([0x89, 0x50, 0x4E, 0x47, 0x0D, 0x0A]) + bytes((i * 7 + 3) % 251 for i in range(3 * CH)))
+    (root / "empty").write_bytes(b"")
+    return root
+
+
+def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path):
+    """Two shards with the cut at every chunk of the tree, and a few three-way cuts: "__main__", long
+    lines and Dockerfile heads that straddle the cut come out as in one pass."""
+    root = os.fsencode(str(_big_file_tree(tmp_path / "big")))
+    tree = ctx.pack_tree(root)
+    try:
+        whole = ctx.detect(tree)
+        ores = oracle.detect(tree)
+        compare_with_oracle(oracle, tree, whole, ores)
+        oracle.lib().m2ko_result_free(ores)
+        w = whole.contents
+        view = gc.TreeView(tree)
+        names = {os.path.basename(view.file_rel[f]): w.file_flags[f] for f in range(tree.contents.n_files)}
+        assert names[b"Dockerfile.big"] & _abi.FILE_DOCKERFILE and names[b"Dockerfile.comments"] & _abi.FILE_DOCKERFILE
+        assert not names[b"Dockerfile.bad"] & _abi.FILE_DOCKERFILE and names[b"Dockerfile.bad"] & _abi.FILE_FROM_FIRST
+        assert names[b"long.txt"] & _abi.FILE_LONG_LINE and not names[b"short.txt"] & _abi.FILE_LONG_LINE
+        assert all(names[b"m%d.py" % k] & _abi.FILE_HAS_MAIN for k in range(1, 8))
+        total = lib.chunk_count(tree)
+        plans = [[0, c, total] for c in range(1, total)] + [[0, total // 3, 2 * total // 3, total], [0, 1, total - 1, total],
+                                                            [0, total // 2, total // 2, total]]
+        settled_any = False
+        for cuts in plans:
+            res, dts, settled = run_chunk_sharded(ctx, tree, cuts)
+            settled_any = settled_any or bool(settled)
+            assert_same_result(tree, res, whole)
+            ctx.result_free(res)
+            for dt in dts:
+                ctx.devtree_free(dt)
+        assert settled_any  # the large Dockerfiles had to be settled by a pass of their own
+        ctx.result_free(whole)
+    finally:
+        ctx.tree_free(tree)

@@ -231,3 +231,35 @@ def test_list_entries_walk_order_on_packed_trees(tmp_path, name):
             assert lib.list_entries(tp, 0, feat) == [e for e in order if e in chosen]
     finally:
         lib.tree_free_host(tp)
+
+
+def test_plan_shards_cuts_only_large_files():
+    """m2k_plan_shards / m2k_chunk_locate: near-equal byte ranges whose cut points
+    fall inside a file only when the file is large enough to be worth spreading over GPUs."""
+    p = small_synth(seed=9, n_files=300, n_dirs=30, total=24 << 20, n_huge=2, huge_bytes=6 << 20)
+    tp = lib.synth_tree_host(p, host_bytes=False)
+    try:
+        t = tp.contents
+        lens = t.file_len[0:t.n_files]
+        chunks = [(n + 65535) // 65536 for n in lens]
+        total = sum(chunks)
+        assert lib.chunk_count(tp) == total
+        starts = [0]
+        for c in chunks:
+            starts.append(starts[-1] + c)
+        for world in (1, 2, 3, 5, 8):
+            for split_min in (1 << 20, 1 << 40):
+                cuts = lib.plan_shards(tp, world, split_min)
+                assert cuts[0] == 0 and cuts[-1] == total and cuts == sorted(cuts) and len(cuts) == world + 1
+                for c in cuts[1:-1]:
+                    if c in (0, total):
+                        continue
+                    f, k = lib.chunk_locate(tp, c)
+                    assert starts[f] + k == c and 0 <= k < chunks[f]
+                    if k:
+                        assert lens[f] >= split_min  # a cut inside a file: only a large one
+                if split_min == 1 << 20 and world > 1:
+                    sizes = [cuts[i + 1] - cuts[i] for i in range(world)]
+                    assert max(sizes) - min(sizes) <= 2 * ((1 << 20) // 65536) + 2  # balanced to within a small file
+    finally:
+        lib.tree_free_host(tp)
