@@ -231,6 +231,7 @@ int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t
 uint64_t m2k_chunk_count(const m2k_tree* tree);
 int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t* chunk_cuts /* [n_ranks+1] */);
 int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t chunk_begin, uint64_t chunk_end, m2k_devtree** out);
+uint64_t m2k_devtree_content_bytes(const m2k_devtree* dt); /* content bytes resident in this shard (the algorithmic bytes of its scan) */
 int m2k_pieces(m2k_ctx* ctx, m2k_devtree* dt, void* d_dst /* 64 bytes */);
 int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all_pieces /* n_ranks x 64 bytes, rank order */, uint32_t n_ranks);
 /* which file holds global chunk `chunk`, and which of its chunks that is (a cut at chunk_in_file != 0 splits the file) */

@@ -598,6 +598,8 @@ extern "C" int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all
   return M2K_OK;
 }
 
+extern "C" uint64_t m2k_devtree_content_bytes(const m2k_devtree* dt) { return dt ? dt->t.shard_content : 0; }
+
 extern "C" int m2k_file_flag(m2k_ctx* ctx, m2k_devtree* dt, uint32_t f, uint8_t* out) {
   if (!ctx || !dt || !out || f >= dt->t.n_files) return fail(nullptr, M2K_ERR_ARG, "bad argument");
   Ctx* C = &ctx->c;

@@ -29,7 +29,7 @@ EXPORTS = [
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
-    "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file",
+    "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes",
 ]
 
 
@@ -93,6 +93,8 @@ def load():
     L.m2k_chunk_locate.argtypes = [TP, C.c_uint64, _abi.u32p, _abi.u32p]
     L.m2k_file_flag.argtypes = [vp, vp, C.c_uint32, C.POINTER(C.c_uint8)]
     L.m2k_settle_file.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
+    L.m2k_devtree_content_bytes.argtypes = [vp]
+    L.m2k_devtree_content_bytes.restype = C.c_uint64
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -193,6 +195,9 @@ class Context:
 
     def merge_pieces(self, dt, all_pieces_ptr, n_ranks):
         _check(self.L.m2k_merge_pieces(self.h, dt, all_pieces_ptr, n_ranks), self.h)
+
+    def shard_content_bytes(self, dt) -> int:
+        return self.L.m2k_devtree_content_bytes(dt)
 
     def file_flag(self, dt, f) -> int:
         out = C.c_uint8()
