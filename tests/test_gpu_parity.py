@@ -323,15 +323,30 @@ def test_chunk_shards_of_a_synthetic_tree_merge_to_the_whole(ctx, oracle, world)
         ores = oracle.detect(tree)
         compare_with_oracle(oracle, tree, whole, ores)
         oracle.lib().m2ko_result_free(ores)
-        cuts = lib.plan_shards(tree, world, 1 << 20)
         from move2kube_b200 import multi
-        assert multi.split_files(tree, cuts), "the plan should cut through at least one large file"
-        for seed in (None, p.seed):  # bytes uploaded from the host / generated in HBM
-            res, dts, _ = run_chunk_sharded(ctx, tree, cuts, fill_seed=seed)
-            assert_same_result(tree, res, whole)
-            ctx.result_free(res)
-            for dt in dts:
-                ctx.devtree_free(dt)
+        t = tree.contents
+        chunks = [(n + 65535) // 65536 for n in t.file_len[0:t.n_files]]
+        starts = [0]
+        for c in chunks:
+            starts.append(starts[-1] + c)
+        total = starts[-1]
+        big = [f for f in range(t.n_files) if t.file_len[f] >= 1 << 20]
+        assert len(big) >= 5
+        plans = [lib.plan_shards(tree, world, 1 << 20)]
+        if world == 2:   # one cut in the middle of each large file
+            plans += [[0, starts[f] + chunks[f] // 2, total] for f in big]
+        if world == 3:   # both cuts inside the same large file: the middle shard is one piece of it
+            plans += [[0, starts[f] + chunks[f] // 3, starts[f] + 2 * chunks[f] // 3, total] for f in big[:2]]
+        n_split = 0
+        for cuts in plans:
+            n_split += len(multi.split_files(tree, cuts))
+            for seed in (None, p.seed):  # bytes uploaded from the host / generated in HBM
+                res, dts, _ = run_chunk_sharded(ctx, tree, cuts, fill_seed=seed)
+                assert_same_result(tree, res, whole)
+                ctx.result_free(res)
+                for dt in dts:
+                    ctx.devtree_free(dt)
+        assert world == 5 or n_split
         ctx.result_free(whole)
     finally:
         ctx.tree_free(tree)
