@@ -88,6 +88,9 @@ class RankExchange:
 
     def gather(self, ctx, dt):
         nd, m = self.nd, self.mine
+        # the library writes these tensors on its own stream: the previous pass's collectives (which a
+        # rank that does not finalise never waited for) must be done with them first
+        self.torch.cuda.current_stream().synchronize()
         ctx.partials(dt, m[0:nd].data_ptr(), m[nd:2 * nd].data_ptr())
         ctx.pieces(dt, m[2 * nd:].data_ptr())
         ctx.file_flags_get(dt, self.flags.data_ptr())

@@ -25,8 +25,17 @@ def main():
     t = tree.contents
     nd, nf = t.n_dirs, t.n_files
     ok = True
-    for split_min in (1 << 20, 1 << 40):      # large files cut between ranks / files kept whole
-        cuts = lib.plan_shards(tree, world, split_min)
+    lens = t.file_len[0:nf]
+    biggest = max(range(nf), key=lambda f: lens[f])
+    before = sum((n + 65535) // 65536 for n in lens[0:biggest])
+    total = lib.chunk_count(tree)
+    for split_min in (1 << 20, 1 << 40, 0):   # the planner with / without cutting large files; cuts forced through the largest file
+        if split_min:
+            cuts = lib.plan_shards(tree, world, split_min)
+        else:
+            nb = (lens[biggest] + 65535) // 65536
+            inner = sorted(before + nb * (r + 1) // (world + 1) for r in range(world - 1))
+            cuts = [0] + inner + [total]
         split = multi.split_files(tree, cuts)
         dt = ctx.upload_chunks(tree, cuts[rank], cuts[rank + 1])
         xch = multi.RankExchange(dist, torch, nd, nf, world)
@@ -40,12 +49,18 @@ def main():
                 res = ctx.finalize(dt)
                 whole = ctx.detect(tree)
                 g, w = res.contents, whole.contents
-                same = g.file_flags[0:nf] == w.file_flags[0:nf] and g.n_services == w.n_services
-                for name in ("dir_state", "dir_opts", "dir_main_file", "dir_subtree", "dir_direct", "dir_ignore"):
-                    same = same and getattr(g, name)[0:nd] == getattr(w, name)[0:nd]
-                same = same and g.service_dirs[0:g.n_services] == w.service_dirs[0:w.n_services]
+                diffs = []
+                for name, n in (("file_flags", nf), ("dir_state", nd), ("dir_opts", nd), ("dir_main_file", nd), ("dir_subtree", nd),
+                                ("dir_direct", nd), ("dir_ignore", nd), ("service_dirs", min(g.n_services, w.n_services))):
+                    a, b = getattr(g, name)[0:n], getattr(w, name)[0:n]
+                    if a != b:
+                        i = next(k for k in range(n) if a[k] != b[k])
+                        diffs.append("%s[%d]: %r != %r (%d differ)" % (name, i, a[i], b[i], sum(1 for k in range(n) if a[k] != b[k])))
+                same = not diffs and g.n_services == w.n_services
+                if diffs:
+                    print("DIFF", "; ".join(diffs), flush=True)
                 print("split_min=%d cut_files=%d services=%d same=%s" % (split_min, len(split), g.n_services, same), flush=True)
-                ok = ok and same and (split_min > (1 << 30) or len(split) > 0)
+                ok = ok and same and (split_min != 0 or len(split) > 0 or world == 1)
                 ctx.result_free(res)
                 ctx.result_free(whole)
         ctx.devtree_free(dt)
