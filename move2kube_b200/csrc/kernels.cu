@@ -114,10 +114,12 @@ void launch_name_features(Ctx* c, DevTree* t) {
 //     word equal to "__ma", "_mai", "main" or "ain_", so the streaming test is four compares per
 //     word; the rare hit is confirmed bytewise from global memory (file bounds respected).
 //   * line length (bufio.Scanner's 64 KiB cap inside dockerparser.Parse, dockerfile2kube.go:124): per
-//     16-byte unit "has a newline" (SWAR), ballot per row, and a warp-uniform count of consecutive
-//     newline-free units.  Only lead/trail counts leave the chunk; k_file_combine stitches chunks
-//     and does the exact byte count for the (rare) runs of >= 4095 free units.
-// Algorithmic traffic: every content byte read once + 4 B written per 64 KiB.
+//     16-byte unit "has a newline" (SWAR), ballot per row; only the chunk's first and last newline
+//     matter, and their positions are taken to the byte by the one lane that holds them.  What leaves
+//     the chunk is an 8-byte record (bytes before the first / after the last newline, flag bits):
+//     exact, so k_file_combine -- or another GPU, for a file cut between shards -- stitches records
+//     without ever reading the file again.
+// Algorithmic traffic: every content byte read once + 8 B written per 64 KiB.
 // ---------------------------------------------------------------------------------------------
 // tunables (tools/scan_variants.py builds and times alternatives; these defaults won on B200)
 #ifndef M2K_SCAN_ROWS

@@ -1,11 +1,12 @@
-"""Multi-GPU plumbing of the path: one process per GPU, files sharded, one tiny gather at the end.
+"""Multi-GPU plumbing of the path: one process per GPU, one tiny exchange at the end.
 
-Files are independent units: each rank scans a contiguous range of file ids
-chosen so that the ranges carry near-equal bytes; the directory table is replicated.  The only
-exchange is the per-directory partials -- a content bit mask (OR) and the lowest main-file id (MIN),
-2 x n_dirs uint32 per rank -- gathered with one all_gather (NCCL over NVLink on GPUs; NCCL has no
-bitwise-OR reduction, so gather + a merge kernel) and folded on every rank, after which the cheap
-directory-level phases run replicated.
+The unit of work is the 64 KiB chunk: each rank scans a contiguous range of
+chunks of near-equal bytes (lib.plan_shards / Context.upload_chunks); large files may be cut between
+ranks, everything else goes whole to one rank; the directory table is replicated.  The only exchange
+is the per-directory partials -- a content bit mask (OR) and the lowest main-file id (MIN) -- plus
+two 32-byte piece summaries per rank, gathered with one all_gather (NCCL over NVLink on GPUs; NCCL has
+no bitwise-OR reduction, so gather + merge kernels), and the per-file flag bytes (all_reduce).  The
+rank that consumes the result merges and runs the cheap directory-level phases.
 """
 from bisect import bisect_left
 from itertools import accumulate
