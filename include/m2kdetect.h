@@ -224,12 +224,17 @@ int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t
  * (SURVEY.md section 8e).  Chunks are numbered over the whole tree: files in id order, each
  * ceil(file_len / 65536) chunks (m2k_chunk_count = the total).  A shard may begin and end inside a
  * file; it then also holds the 16 bytes on the far side of the cut.  m2k_plan_shards picks
- * n_ranks + 1 cut points of near-equal bytes that fall inside a file only when the file has at least
+ * n_ranks + 1 cut points of near-equal cost (bytes + a fixed part per chunk) that fall inside a file only when the file has at least
  * `split_min_bytes` bytes (smaller files go whole to one side).  The parts of a cut file are
  * summarised per shard (m2k_pieces: 64 bytes, device to device), gathered in rank order and stitched
  * by m2k_merge_pieces on the rank that finalises; see M2K_FILE_UNDECIDED for the one case left open. */
 uint64_t m2k_chunk_count(const m2k_tree* tree);
-int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t* chunk_cuts /* [n_ranks+1] */);
+int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t root_extra_bytes,
+                    uint64_t* chunk_cuts /* [n_ranks+1] */);
+/* root_extra_bytes: shard 0 is made lighter by this much, because its rank also runs the
+ * directory-level phases and assembles the result (0 = equal shards); m2k_root_extra_bytes is the
+ * library's own estimate for a tree, from timings on B200 */
+uint64_t m2k_root_extra_bytes(const m2k_tree* tree);
 int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t chunk_begin, uint64_t chunk_end, m2k_devtree** out);
 uint64_t m2k_devtree_content_bytes(const m2k_devtree* dt); /* content bytes resident in this shard (the algorithmic bytes of its scan) */
 int m2k_pieces(m2k_ctx* ctx, m2k_devtree* dt, void* d_dst /* 64 bytes */);

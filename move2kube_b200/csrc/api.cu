@@ -450,23 +450,43 @@ extern "C" int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t ch
   return upload_impl(ctx, tree, f0, fl + 1, first_skip, last_end, out);
 }
 
-extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t* chunk_cuts) {
+// What a chunk costs the byte scan: its bytes, plus a fixed part (a warp's set-up, the file lookup,
+// the record) worth about 4 KiB of streaming -- measured on config D, where a million files of a
+// few hundred bytes take as long as ~5 GB of large ones.  Balancing bytes alone would hand one GPU
+// all the tiny files; balancing chunks alone would hand another all the multi-GiB ones.
+static constexpr uint64_t kChunkFixedCost = 4096;
+static inline uint64_t file_cost(const m2k_tree* tree, uint32_t f) { return tree->file_len[f] + kChunkFixedCost * file_chunks(tree, f); }
+
+extern "C" uint64_t m2k_root_extra_bytes(const m2k_tree* tree) {
+  // what the rank that assembles the result does besides scanning its shard -- name features, subtree /
+  // predicate / walk kernels, merges, result copies -- expressed as bytes of scanning: measured on
+  // B200 as about 0.3 ms + 0.14 ms per million entries, at 7 TB/s
+  if (!tree) return 0;
+  return (uint64_t)(7.0e9 * (0.3 + 0.14e-6 * (double)tree->n_entries));
+}
+
+extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t root_extra_bytes,
+                               uint64_t* chunk_cuts) {
   if (!tree || !n_ranks || !chunk_cuts) return fail(nullptr, M2K_ERR_ARG, "m2k_plan_shards: bad argument");
-  const uint64_t total = m2k_chunk_count(tree);
+  uint64_t total_cost = 0, total_chunks = 0;
+  for (uint32_t f = 0; f < tree->n_files; f++) { total_cost += file_cost(tree, f); total_chunks += file_chunks(tree, f); }
   chunk_cuts[0] = 0;
   uint32_t f = 0;
-  uint64_t at = 0;  // first chunk of file f
+  uint64_t at_cost = 0, at_chunk = 0;  // cost / chunks of the files before f
   for (uint32_t r = 1; r < n_ranks; r++) {
-    const uint64_t target = (uint64_t)((unsigned __int128)total * r / n_ranks);
-    while (f < tree->n_files && at + file_chunks(tree, f) <= target) { at += file_chunks(tree, f); f++; }
-    uint64_t cut = target;
-    if (f < tree->n_files && target > at) {  // the target falls inside file f
-      const uint64_t nc = file_chunks(tree, f);
-      if (tree->file_len[f] < split_min_bytes) cut = (target - at) * 2 < nc ? at : at + nc;  // small file: nearer boundary
+    // rank 0 is charged root_extra_bytes on top of its shard, so every cut moves left by that much
+    const unsigned __int128 ideal = ((unsigned __int128)total_cost + root_extra_bytes) * r / n_ranks;
+    const uint64_t target = ideal > root_extra_bytes ? (uint64_t)(ideal - root_extra_bytes) : 0;
+    while (f < tree->n_files && at_cost + file_cost(tree, f) <= target) { at_cost += file_cost(tree, f); at_chunk += file_chunks(tree, f); f++; }
+    uint64_t cut = at_chunk;
+    if (f < tree->n_files && target > at_cost) {  // the target falls inside file f
+      const uint64_t nc = file_chunks(tree, f), into = target - at_cost;
+      if (tree->file_len[f] >= split_min_bytes) cut = at_chunk + std::min<uint64_t>(nc, into / (kChunkBytes + kChunkFixedCost));
+      else cut = into * 2 < file_cost(tree, f) ? at_chunk : at_chunk + nc;  // small file: whole, to the nearer side
     }
     chunk_cuts[r] = std::max(cut, chunk_cuts[r - 1]);
   }
-  chunk_cuts[n_ranks] = total;
+  chunk_cuts[n_ranks] = total_chunks;
   return M2K_OK;
 }
 

@@ -29,7 +29,7 @@ EXPORTS = [
     "m2k_devtree_free", "m2k_scan_kernel_ms", "m2k_phase_ms", "m2k_launch_count", "m2k_stream", "m2k_path_clean", "m2k_equal_fold",
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
-    "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes",
+    "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
 ]
 
 
@@ -86,7 +86,9 @@ def load():
     L.m2k_scan_flags_noalloc.argtypes = [C.c_int, vp, vp, vp, vp, vp, C.c_uint32, C.c_uint32, vp]
     L.m2k_chunk_count.argtypes = [TP]
     L.m2k_chunk_count.restype = C.c_uint64
-    L.m2k_plan_shards.argtypes = [TP, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.m2k_plan_shards.argtypes = [TP, C.c_uint32, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.m2k_root_extra_bytes.argtypes = [TP]
+    L.m2k_root_extra_bytes.restype = C.c_uint64
     L.m2k_upload_chunks.argtypes = [vp, TP, C.c_uint64, C.c_uint64, C.POINTER(vp)]
     L.m2k_pieces.argtypes = [vp, vp, vp]
     L.m2k_merge_pieces.argtypes = [vp, vp, vp, C.c_uint32]
@@ -282,11 +284,15 @@ def chunk_count(tree) -> int:
     return load().m2k_chunk_count(tree)
 
 
-def plan_shards(tree, n_ranks, split_min_bytes=64 << 20):
-    """n_ranks + 1 chunk cut points of near-equal bytes; a file is cut only if it has at least
-    `split_min_bytes` bytes."""
+def plan_shards(tree, n_ranks, split_min_bytes=64 << 20, root_extra_bytes=0):
+    """n_ranks + 1 chunk cut points of near-equal cost; a file is cut only if it has at least
+    `split_min_bytes` bytes; shard 0 is lighter by `root_extra_bytes` (None: the library's estimate of
+    what the rank that assembles the result does besides scanning)."""
+    L = load()
+    if root_extra_bytes is None:
+        root_extra_bytes = L.m2k_root_extra_bytes(tree)
     cuts = (C.c_uint64 * (n_ranks + 1))()
-    _check(load().m2k_plan_shards(tree, n_ranks, split_min_bytes, cuts))
+    _check(L.m2k_plan_shards(tree, n_ranks, split_min_bytes, root_extra_bytes, cuts))
     return list(cuts)
 
 

@@ -259,7 +259,16 @@ def test_plan_shards_cuts_only_large_files():
                     if k:
                         assert lens[f] >= split_min  # a cut inside a file: only a large one
                 if split_min == 1 << 20 and world > 1:
-                    sizes = [cuts[i + 1] - cuts[i] for i in range(world)]
-                    assert max(sizes) - min(sizes) <= 2 * ((1 << 20) // 65536) + 2  # balanced to within a small file
+                    # balanced by cost (bytes + a fixed 4 KiB per chunk) to within a small file
+                    cost = [0]
+                    for n, c in zip(lens, chunks):
+                        cost.append(cost[-1] + n + 4096 * c)
+                    def cost_at(chunk):
+                        if chunk == total:
+                            return cost[-1]
+                        f, k = lib.chunk_locate(tp, chunk)
+                        return cost[f] + k * (65536 + 4096)
+                    sizes = [cost_at(cuts[i + 1]) - cost_at(cuts[i]) for i in range(world)]
+                    assert max(sizes) - min(sizes) <= 2 * ((1 << 20) + 4096 * 17)
     finally:
         lib.tree_free_host(tp)
