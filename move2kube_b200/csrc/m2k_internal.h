@@ -126,6 +126,9 @@ struct Ctx {
   // features to the host, the ignore table to the device, early result arrays), and its ordering events
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_names = nullptr, ev_feat = nullptr, ev_blob = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  // two pinned blocks through which bytes held in pageable host memory are streamed to the device
+  void* stage[2] = {nullptr, nullptr};
+  cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   float phase_ms[8] = {};  // names, scan, combine, dockerfile, finalize kernels, host ignore, host verify, d2h
   int sm_count = 0;
   uint64_t launches = 0;

@@ -48,12 +48,14 @@ class Detection:
         self.broot = os.fsencode(root)
         self.ctx = context()
         self.flavor = sh_flavor() if flavor is None else flavor
-        self.tree = self.ctx.pack_tree(self.broot, read_content=not skip_content)
+        # one-shot use: pack into ordinary memory (page-locking the whole tree would cost more than
+        # reading it); m2k_upload streams it to the device through the context's pinned staging blocks
+        self.tree = lib.pack_tree_host(self.broot, read_content=not skip_content)
         self.res = None
         try:
             self.res = self.ctx.detect(self.tree, self.flavor, [os.fsencode(p) for p in pre], skip_content)
         except Exception:
-            self.ctx.tree_free(self.tree)
+            lib.tree_free_host(self.tree)
             self.tree = None
             raise
         t, r = self.tree.contents, self.res.contents
@@ -100,7 +102,7 @@ class Detection:
             self.ctx.result_free(self.res)
             self.res = None
         if self.tree is not None:
-            self.ctx.tree_free(self.tree)
+            lib.tree_free_host(self.tree)
             self.tree = None
 
     # -- look-ups

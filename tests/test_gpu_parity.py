@@ -415,3 +415,19 @@ def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path):
         ctx.result_free(whole)
     finally:
         ctx.tree_free(tree)
+
+
+def test_pageable_tree_goes_through_the_staging_blocks(ctx, oracle):
+    """A tree whose bytes sit in ordinary (pageable) host memory is streamed to the device through the
+    context's two 32 MiB pinned blocks; 90 MB makes the blocks wrap around.  Same result as the oracle."""
+    p = synth_params(13, 2500, 150, 90 << 20)
+    tree = lib.synth_tree_host(p, host_bytes=True)  # no context: plain malloc
+    try:
+        for _ in range(2):
+            res = ctx.detect(tree)
+            ores = oracle.detect(tree)
+            compare_with_oracle(oracle, tree, res, ores)
+            oracle.lib().m2ko_result_free(ores)
+            ctx.result_free(res)
+    finally:
+        lib.tree_free_host(tree)
