@@ -65,6 +65,7 @@ struct IgnorePrep {
   const IgnoreSlot* d_table = nullptr;
   const uint32_t *d_runes = nullptr, *d_prefix = nullptr;
   float ms_host = 0.f;
+  uint32_t sh_flavor = M2K_SH_BASH;     // the /bin/sh flavour the early directory phases were run for
   double ms_part[5] = {0, 0, 0, 0, 0};  // order, parse, fold, table, lists
   void reset() {
     ready = false; table_mask = M2K_NONE; prefix_len = 0; depth1_state = 0; root_ignore = 0;
@@ -180,7 +181,14 @@ extern "C" int m2k_ctx_create(int device, m2k_ctx** out) {
   CUX(cudaStreamCreateWithFlags(&C->stream, cudaStreamNonBlocking));
   for (auto& ev : C->ev) CUX(cudaEventCreate(&ev));
   CUX(cudaStreamCreateWithFlags(&C->copy_stream, cudaStreamNonBlocking));
-  for (cudaEvent_t* ev : {&C->ev_names, &C->ev_feat, &C->ev_blob, &C->ev_fork, &C->ev_join}) CUX(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+  for (cudaEvent_t* ev : {&C->ev_names, &C->ev_feat, &C->ev_blob, &C->ev_fork, &C->ev_join, &C->ev_early}) CUX(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+  {
+    int least = 0, greatest = 0;
+    CUX(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    CUX(cudaStreamCreateWithPriority(&C->side_stream, cudaStreamNonBlocking, greatest));
+    CUX(cudaEventCreate(&C->ev_side0));
+    CUX(cudaEventCreate(&C->ev_side1));
+  }
   CUX(cudaDeviceGetAttribute(&C->sm_count, cudaDevAttrMultiProcessorCount, device));
   CUX(cudaMalloc(&C->d_fold_from, sizeof(m2k_casefold_from)));
   CUX(cudaMalloc(&C->d_fold_to, sizeof(m2k_casefold_to)));
@@ -201,9 +209,11 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   cudaSetDevice(C->device);
   if (C->stream) cudaStreamSynchronize(C->stream);
   if (C->copy_stream) cudaStreamSynchronize(C->copy_stream);
+  if (C->side_stream) cudaStreamSynchronize(C->side_stream);
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
-  for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join}) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
+  if (C->side_stream) cudaStreamDestroy(C->side_stream);
   for (int k = 0; k < 2; k++) { if (C->stage[k]) cudaFreeHost(C->stage[k]); if (C->stage_ev[k]) cudaEventDestroy(C->stage_ev[k]); }
   if (C->stream) cudaStreamDestroy(C->stream);
   if (C->copy_stream) cudaStreamDestroy(C->copy_stream);
@@ -310,7 +320,7 @@ static void free_devtree_shell(m2k_devtree* dt) {
 
 extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   if (!dt) return;
-  if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); cudaStreamSynchronize(ctx->c.copy_stream); }
+  if (ctx) { cudaSetDevice(ctx->c.device); cudaStreamSynchronize(ctx->c.stream); cudaStreamSynchronize(ctx->c.copy_stream); cudaStreamSynchronize(ctx->c.side_stream); }
   devtree_release(&dt->t);
   free_devtree_shell(dt);
 }
@@ -557,7 +567,8 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaSetDevice(C->device));
   cudaStream_t s = C->stream;
   const bool content = !(params && params->skip_content);
-  CU(cudaStreamWaitEvent(s, C->ev_feat, 0));  // a previous pass's copy of the name features may still be reading them
+  CU(cudaStreamWaitEvent(s, C->ev_feat, 0));   // a previous pass's copy of the name features may still be reading them
+  CU(cudaStreamWaitEvent(s, C->ev_early, 0));  // ... and its directory-level kernels the arrays cleared below
   CU(cudaMemsetAsync(t->dir_direct, 0, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_first_war, 0xFF, 4ull * t->n_dirs, s));
   CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
@@ -997,7 +1008,9 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
       CU(cudaMalloc(&t->ign_blob, P.blob_bytes * 2));
       t->ign_blob_cap = P.blob_bytes * 2;
     }
-    // on the copy stream: queued on `s` it would only start after the byte scan
+    // on the copy stream: queued on `s` it would only start after the byte scan (and not before an
+    // earlier walk, if there was one, has finished reading the table it replaces)
+    CU(cudaStreamWaitEvent(C->copy_stream, C->ev_early, 0));
     CU(cudaMemcpyAsync(t->ign_blob, dt->stage.p, P.blob_bytes, cudaMemcpyHostToDevice, C->copy_stream));
     CU(cudaEventRecord(C->ev_blob, C->copy_stream));
     P.d_runes = (const uint32_t*)t->ign_blob;
@@ -1025,6 +1038,28 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     r->ignore_dirs = list_from_arenas(P.arenas, 1, &r->n_ignore_dirs);
     r->ignore_contents = list_from_arenas(P.arenas, 2, &r->n_ignore_contents);
     dt->pending = r;
+  }
+  // The directory-level phases need the name features and the ignore table, nothing from the byte
+  // scan: queue them now, on the high-priority side stream, and send their results down.  What is
+  // left for m2k_finalize is the content bits and the main-file ids (k_content_up).
+  {
+    m2k_result* r = dt->pending;
+    const uint32_t nd = t->n_dirs;
+    cudaStream_t ss = C->side_stream;
+    P.sh_flavor = params ? params->sh_flavor : M2K_SH_BASH;
+    CU(cudaStreamWaitEvent(ss, C->ev_names, 0));
+    CU(cudaStreamWaitEvent(ss, C->ev_blob, 0));
+    CU(cudaEventRecord(C->ev_side0, ss));
+    launch_subtree(C, t, ss);
+    launch_combine_opts(C, t, P.sh_flavor, ss);
+    launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore, ss);
+    CU(cudaEventRecord(C->ev_side1, ss));
+    CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, ss));
+    CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, ss));
+    CU(cudaMemcpyAsync(r->dir_state, t->dir_state, nd, cudaMemcpyDeviceToHost, ss));
+    CU(cudaMemcpyAsync(r->dir_ignore, t->dir_ignore, nd, cudaMemcpyDeviceToHost, ss));
+    CU(cudaEventRecord(C->ev_early, ss));
+    CU(cudaGetLastError());
   }
   P.ms_part[4] = now_ms() - h6;
   P.ms_host = (float)(now_ms() - h0);
@@ -1087,38 +1122,28 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   if (!t->scanned) return fail(C, M2K_ERR_ARG, "m2k_finalize before m2k_scan");
   CU(cudaSetDevice(C->device));
   cudaStream_t s = C->stream;
-  const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
+  const uint32_t nd = t->n_dirs, nf = t->n_files;
   const uint32_t sh = params ? params->sh_flavor : M2K_SH_BASH;
-  // the result arrays (and the copy of the name features) were prepared under the byte scan when
-  // m2k_prepare ran; otherwise they are made now
-  // bottom-up and the predicate table do not depend on the ignore rules: queue them first
-  CU(cudaEventRecord(C->ev[4], s));
-  launch_subtree(C, t);
-  launch_combine_opts(C, t, sh);
-  CU(cudaEventRecord(C->ev[7], s));
-  if (!dt->prep.ready) { if (int rc = prepare_ignore(C, dt, params)) return rc; }
+  // m2k_prepare (under the byte scan) parsed the ignore rules and queued the directory-level phases on
+  // the side stream; when it was not called, or was called for the other /bin/sh flavour, that happens now
+  if (!dt->prep.ready || dt->prep.sh_flavor != sh) { if (int rc = prepare_ignore(C, dt, params)) return rc; }
   IgnorePrep& P = dt->prep;
   m2k_result* r = dt->pending;
   dt->pending = nullptr;
   struct RG { m2k_result* r; bool keep = false; ~RG() { if (!keep) m2k_result_free(r); } } rg{r};
   r->ms_host_ignore = P.ms_host;
   r->n_services = 0;
-
-  // what is final before the walk goes to the host on the copy stream while the walk kernels run
+  // what the byte scan adds: content bits and main-file ids up the tree, then the remaining arrays
+  CU(cudaStreamWaitEvent(s, C->ev_early, 0));
+  CU(cudaEventRecord(C->ev[4], s));
+  launch_content_up(C, t, s);
+  CU(cudaEventRecord(C->ev[5], s));
   CU(cudaEventRecord(C->ev_fork, s));
   CU(cudaStreamWaitEvent(C->copy_stream, C->ev_fork, 0));
   CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, C->copy_stream));
   CU(cudaEventRecord(C->ev_join, C->copy_stream));
-  CU(cudaStreamWaitEvent(s, C->ev_blob, 0));  // the ignore table m2k_prepare sent up
-  CU(cudaEventRecord(C->ev[11], s));
-  launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore);
-  CU(cudaEventRecord(C->ev[5], s));
-  CU(cudaMemcpyAsync(r->dir_state, t->dir_state, nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaMemcpyAsync(r->dir_ignore, t->dir_ignore, nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamWaitEvent(s, C->ev_join, 0));
   CU(cudaStreamWaitEvent(s, C->ev_feat, 0));  // r->entry_feat
   CU(cudaEventRecord(C->ev[6], s));
@@ -1126,11 +1151,11 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "detection kernels failed: %s", cudaGetErrorString(werr));
   if (int rc = collect_scan_timings(C, dt)) return rc;
   float ms_k1 = 0, ms_k2 = 0, ms_d = 0;
-  CU(cudaEventElapsedTime(&ms_k1, C->ev[4], C->ev[7]));
-  CU(cudaEventElapsedTime(&ms_k2, C->ev[11], C->ev[5]));
+  CU(cudaEventElapsedTime(&ms_k1, C->ev_side0, C->ev_side1));  // directory phases on the side stream (under the byte scan)
+  CU(cudaEventElapsedTime(&ms_k2, C->ev[4], C->ev[5]));
   CU(cudaEventElapsedTime(&ms_d, C->ev[5], C->ev[6]));
   r->ms_kernels = ms_k1 + ms_k2; r->ms_d2h = ms_d;
-  C->phase_ms[4] = ms_k1 + ms_k2; C->phase_ms[5] = r->ms_host_ignore; C->phase_ms[7] = ms_d;
+  C->phase_ms[4] = ms_k2; C->phase_ms[5] = r->ms_host_ignore; C->phase_ms[7] = ms_d;
   double v0 = now_ms();
   {
     // the directories that became services, in id (= Walk) order: eight states per step, since nearly

@@ -637,12 +637,26 @@ void launch_dockerfile(Ctx* c, DevTree* t) {
 // Kernel 5: subtree OR / MIN, bottom-up one level per launch (find's recursion, done once for all
 // directories instead of once per visited directory).
 // ---------------------------------------------------------------------------------------------
-__global__ void k_subtree_init(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, const uint32_t* __restrict__ dir_content,
-                               const uint32_t* __restrict__ dir_main, uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
+__global__ void k_subtree_init(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_subtree,
+                               uint32_t* __restrict__ dir_main_sub) {
   uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n_dirs) return;
-  dir_subtree[d] = dir_direct[d] | dir_content[d];
-  dir_main_sub[d] = dir_main[d];
+  dir_subtree[d] = dir_direct[d];   // name features; the content bits are added by k_content_up once the bytes are scanned
+  dir_main_sub[d] = M2K_NONE;
+}
+// The content results are sparse (directories holding a python main file or a Dockerfile): each such
+// directory pushes its bits and its lowest main-file id up its ancestor chain.
+__global__ void k_content_up(uint32_t n_dirs, const uint32_t* __restrict__ dir_parent, const uint32_t* __restrict__ dir_content,
+                             const uint32_t* __restrict__ dir_main, uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
+  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n_dirs) return;
+  const uint32_t bits = dir_content[d], mf = dir_main[d];
+  if (!bits && mf == M2K_NONE) return;
+  for (uint32_t x = d;; x = dir_parent[x]) {
+    if (bits) atomicOr(&dir_subtree[x], bits);
+    if (mf != M2K_NONE) atomicMin(&dir_main_sub[x], mf);
+    if (x == 0) break;
+  }
 }
 __global__ void k_subtree_level(const uint32_t* __restrict__ level_dirs, uint32_t n, const uint32_t* __restrict__ dir_parent,
                                 uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
@@ -655,18 +669,24 @@ __global__ void k_subtree_level(const uint32_t* __restrict__ level_dirs, uint32_
   if (m != M2K_NONE) atomicMin(&dir_main_sub[p], m);
 }
 
-void launch_subtree(Ctx* c, DevTree* t) {
+// name features up the tree (find's recursion): needs only the name kernel's output, so it runs on the
+// side stream while the bytes are still being scanned
+void launch_subtree(Ctx* c, DevTree* t, cudaStream_t st) {
   if (!t->n_dirs) return;
-  k_subtree_init<<<(t->n_dirs + 255) / 256, 256, 0, c->stream>>>(t->n_dirs, t->dir_direct, t->dir_content, t->dir_main,
-                                                                t->dir_subtree, t->dir_main_sub);
+  k_subtree_init<<<(t->n_dirs + 255) / 256, 256, 0, st>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_main_sub);
   c->launches++;
   for (uint32_t L = t->max_depth; L >= 1; L--) {
     uint32_t a = t->level_off[L], b = t->level_off[L + 1];
     if (b > a) {
-      k_subtree_level<<<(b - a + 255) / 256, 256, 0, c->stream>>>(t->level_dirs + a, b - a, t->dir_parent, t->dir_subtree, t->dir_main_sub);
+      k_subtree_level<<<(b - a + 255) / 256, 256, 0, st>>>(t->level_dirs + a, b - a, t->dir_parent, t->dir_subtree, t->dir_main_sub);
       c->launches++;
     }
   }
+}
+void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st) {
+  if (!t->n_dirs) return;
+  k_content_up<<<(t->n_dirs + 255) / 256, 256, 0, st>>>(t->n_dirs, t->dir_parent, t->dir_content, t->dir_main, t->dir_subtree, t->dir_main_sub);
+  c->launches++;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -704,9 +724,9 @@ __global__ void k_combine_opts(uint32_t n_dirs, const uint32_t* __restrict__ dir
   dir_opts[d] = m;
 }
 
-void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor) {
+void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor, cudaStream_t st) {
   if (!t->n_dirs) return;
-  k_combine_opts<<<(t->n_dirs + 255) / 256, 256, 0, c->stream>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_first_war,
+  k_combine_opts<<<(t->n_dirs + 255) / 256, 256, 0, st>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_first_war,
                                                                 t->entry_type, sh_flavor, t->dir_opts);
   c->launches++;
 }
@@ -825,14 +845,14 @@ __global__ void __launch_bounds__(128) k_walk_reach(uint32_t n_dirs, WalkArgs a)
 }
 
 void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
-                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore) {
+                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore, cudaStream_t st) {
   if (!t->n_dirs) return;
   WalkArgs a{t->dir_parent, t->dir_entry, t->dir_flags, t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to,
              table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore, t->dir_opts,
              t->dir_hash, t->dir_ignore, t->dir_state, t->dir_descend};
   uint32_t blocks = (t->n_dirs + 127) / 128;
-  k_walk_local<<<blocks, 128, 0, c->stream>>>(t->n_dirs, t->dir_depth, a);
-  k_walk_reach<<<blocks, 128, 0, c->stream>>>(t->n_dirs, a);
+  k_walk_local<<<blocks, 128, 0, st>>>(t->n_dirs, t->dir_depth, a);
+  k_walk_reach<<<blocks, 128, 0, st>>>(t->n_dirs, a);
   c->launches += 2;
 }
 

@@ -126,6 +126,12 @@ struct Ctx {
   // features to the host, the ignore table to the device, early result arrays), and its ordering events
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_names = nullptr, ev_feat = nullptr, ev_blob = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  // third stream, highest priority: the directory-level phases (name features up the tree, the 18
+  // predicates, the ignore join and the walk) depend on names only, so they run while the byte scan
+  // still owns the main stream; their blocks are placed as scan blocks retire
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_side0 = nullptr, ev_side1 = nullptr;  // timing on: the span of those kernels
+  cudaEvent_t ev_early = nullptr;                      // ... and their results are on the host
   // two pinned blocks through which bytes held in pageable host memory are streamed to the device
   void* stage[2] = {nullptr, nullptr};
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
@@ -144,10 +150,11 @@ void launch_name_features(Ctx* c, DevTree* t);
 void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec);
 void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec);
 void launch_dockerfile(Ctx* c, DevTree* t);
-void launch_subtree(Ctx* c, DevTree* t);
-void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor);
+void launch_subtree(Ctx* c, DevTree* t, cudaStream_t st);
+void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st);
+void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor, cudaStream_t st);
 void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
-                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore);
+                 const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore, cudaStream_t st);
 void fold_runes(const std::string& s, std::vector<uint32_t>* out);
 std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clean_root);
 void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, const uint32_t* all_main, uint32_t n_ranks);
