@@ -90,6 +90,36 @@ def test_dockerfile_known_answers(ctx, oracle, tmp_path):
     ctx.tree_free(tree)
 
 
+def test_dockerfile_known_answers_through_the_striped_path(ctx, oracle, tmp_path):
+    """Bodies of a few KiB are validated by the head thread itself; the same vectors followed by 12 KiB
+    of further lines (before and after a blank-line separator, and glued on directly, so that trailing
+    continuations run into them) go through the candidate list and the striped launches.  GPU against
+    the oracle on identical bytes."""
+    root = tmp_path / "kats_long"
+    root.mkdir()
+    pad = b"RUN echo a line of padding that is valid in any Dockerfile body\n" * 200
+    bad = b"RUN true\n" * 1400 + b"ENV missingvalue\n"
+    datas = {}
+    for i, (name, data, want) in enumerate(KATS):
+        datas["%03d_a_%s" % (i, name)] = data + pad
+        datas["%03d_b_%s" % (i, name)] = data + b"\n" + pad
+        datas["%03d_c_%s" % (i, name)] = data + b"\n" + bad
+    for k, v in datas.items():
+        (root / k).write_bytes(v)
+    tree = ctx.pack_tree(os.fsencode(str(root)))
+    res = ctx.detect(tree)
+    view = gc.TreeView(tree)
+    n_df = 0
+    for f in range(view.n_files):
+        name = os.fsdecode(view.file_rel[f])
+        fl = res.contents.file_flags[f]
+        assert fl == oracle.file_flags(datas[name]), name
+        n_df += bool(fl & _abi.FILE_DOCKERFILE)
+    assert n_df >= 20
+    ctx.result_free(res)
+    ctx.tree_free(tree)
+
+
 def _adversarial_files():
     """Content cases around the kernel's tiling: 16-byte units, 512-byte rows, 64 KiB chunks."""
     out = {}
