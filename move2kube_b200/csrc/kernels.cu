@@ -481,8 +481,6 @@ void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
 // Grids are fixed multiples of the SM count and read the candidate counts from device memory, so the
 // host never waits for them.
 // ---------------------------------------------------------------------------------------------
-constexpr uint64_t kDfDirectBytes = 8192;  // bodies up to this size are validated by the head thread itself
-
 struct DfArgs {
   uint32_t n_shard_files, file_begin, first_skip, last_end;
   PieceSummary* pieces;
@@ -522,15 +520,6 @@ __global__ void __launch_bounds__(128) k_df_head(DfArgs a) {
   uint32_t flags = a.file_flags[f];
   if (flags & 0x80) { a.file_flags[f] = (uint8_t)(flags & 0x7F); return; }  // ruled out by the scan kernel (first word)
   if (!df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n, (flags & M2K_FILE_LONG_LINE) != 0, &body, &esc)) return;
-  if (n - body <= kDfDirectBytes) {
-    // nearly every real Dockerfile: a body of a few KiB is checked right here by this thread, line by
-    // line, instead of going through the candidate list and the four striped launches
-    df::File fl = df_file(a, f, esc);
-    const bool ok = df::stripe_validate(fl, body, body, n, 0);
-    a.file_flags[f] = (uint8_t)(flags | M2K_FILE_FROM_FIRST | (ok ? M2K_FILE_DOCKERFILE : 0));
-    if (ok) atomicOr(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
-    return;
-  }
   a.file_flags[f] = (uint8_t)(flags | M2K_FILE_FROM_FIRST);
   uint32_t c = atomicAdd(&a.counters[0], 1u);
   a.cand_file[c] = f;

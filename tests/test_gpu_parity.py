@@ -91,10 +91,9 @@ def test_dockerfile_known_answers(ctx, oracle, tmp_path):
 
 
 def test_dockerfile_known_answers_through_the_striped_path(ctx, oracle, tmp_path):
-    """Bodies of a few KiB are validated by the head thread itself; the same vectors followed by 12 KiB
-    of further lines (before and after a blank-line separator, and glued on directly, so that trailing
-    continuations run into them) go through the candidate list and the striped launches.  GPU against
-    the oracle on identical bytes."""
+    """The known-answer vectors followed by 12 KiB of further lines (after a blank-line separator, and
+    glued on directly so that trailing continuations run into them): bodies of a dozen stripes, with
+    the vector's own lines in the first one.  GPU against the oracle on identical bytes."""
     root = tmp_path / "kats_long"
     root.mkdir()
     pad = b"RUN echo a line of padding that is valid in any Dockerfile body\n" * 200
