@@ -442,7 +442,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 // state from IN.  Stripes of the body compute their composed map (k_df_maps), a per-file scan turns
 // the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
 // lines that start inside it (k_df_validate).
-constexpr uint32_t kStripe = 1024;  // == kDfStripe (m2k_internal.h)
+constexpr uint32_t kStripe = 256;   // == kDfStripe (m2k_internal.h)
 
 __device__ inline uint32_t line_map(const File& f, uint64_t lb, uint64_t le) {
   // from IN: comment and blank lines are dropped and the continuation goes on

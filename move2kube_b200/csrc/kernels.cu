@@ -474,7 +474,7 @@ void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
 //   k_df_head     one thread per file: directives, comments, ARGs, first instruction.  Nearly every
 //                 file leaves after a few bytes; FROM-first files become candidates (scratch list).
 //   k_df_prefix   one block: exclusive prefix of the candidates' stripe counts.
-//   k_df_maps     one thread per 1 KiB stripe of candidate bodies: composed line-state map.
+//   k_df_maps     one thread per 256-byte stripe of candidate bodies: composed line-state map.
 //   k_df_scan     one thread per candidate: state at every stripe start.
 //   k_df_validate one thread per stripe: parse errors of the logical lines starting in it;
 //   k_df_finish   one thread per candidate: DOCKERFILE bit + per-directory content bit.

@@ -11,7 +11,7 @@ namespace m2k {
 
 constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
-constexpr uint32_t kDfStripe = 1024;     // bytes of one stripe of the parallel Dockerfile validation
+constexpr uint32_t kDfStripe = 256;      // bytes of one stripe of the parallel Dockerfile validation
 constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
 // per-chunk record written by the byte-scan kernel: scratch memory, 8 bytes per 64 KiB chunk, exact
 // to the byte so that records of one file can be stitched anywhere (another kernel, another GPU)
