@@ -302,7 +302,7 @@ static void devtree_release(DevTree* t) {
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->level_dirs, t->dir_flags, t->entry_dir, t->entry_name_off,
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
-                  t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_hash, t->dir_ignore, t->dir_state,
+                  t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_ignore, t->dir_state,
                   t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
                   t->cand_esc, t->stripe_state, t->ign_blob, t->special, t->pieces};
   for (void* p : ptrs) if (p) cudaFree(p);
@@ -430,7 +430,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   }
   CU(dev_alloc(&t->dir_direct, nd)); CU(dev_alloc(&t->dir_first_war, nd)); CU(dev_alloc(&t->dir_content, nd));
   CU(dev_alloc(&t->dir_main, nd)); CU(dev_alloc(&t->dir_subtree, nd)); CU(dev_alloc(&t->dir_main_sub, nd));
-  CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_hash, nd)); CU(dev_alloc(&t->dir_ignore, nd));
+  CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_ignore, nd));
   CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd)); CU(dev_alloc(&t->file_flags, nf));
 
   CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));

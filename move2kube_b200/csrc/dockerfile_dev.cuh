@@ -188,7 +188,6 @@ __device__ inline bool name_val_ok(const File& f, LCur c) {
   bool interior_ws = false, pending_ws = false, seen_nonspace = false;
   for (;;) {
     uint32_t ch = 0;
-    LCur before = c;
     bool have = lc_get_rune(f, c, &ch);
     if (have) {  // bookkeeping for tokenWhitespace.Split(TrimSpace(rest), 2)
       if (is_space_rune(ch)) { if (ascii_ws(ch) && seen_nonspace) pending_ws = true; }
@@ -238,7 +237,6 @@ __device__ inline bool name_val_ok(const File& f, LCur c) {
     }
     wlen++;
     if (ch == '=') weq = true;
-    (void)before;
   }
   if (words == 0) return true;
   if (!first_eq) return interior_ws;  // old form "KEY name value" needs a blank-separated value
@@ -273,9 +271,7 @@ __device__ inline bool run_then_tail(const File& f, LCur c, LCur* after) {
 __device__ inline bool from_match_here(const File& f, LCur c) {
   int b = lc_get(f, c);
   if (b < 0 || !re_s((uint32_t)b)) return false;
-  LCur start = c;
   for (;;) { LCur t = c; b = lc_get(f, t); if (b < 0) return false; if (!re_s((uint32_t)b)) break; c = t; }
-  (void)start;
   LCur after;
   if (run_then_tail(f, c, &after)) return true;
   // (\s+AS\s+[^\s]+)

@@ -208,25 +208,6 @@ std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clea
 
 // filepath.Walk order over all entries: a directory's entries in name order, descending into each
 // sub-directory right after its own entry.
-void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out) {
-  out->clear();
-  if (!t->n_dirs) return;
-  out->reserve(t->n_entries);
-  struct Frame { uint32_t e, end; };
-  std::vector<Frame> st;
-  st.push_back({t->dir_first_entry[0], t->dir_first_entry[1]});
-  while (!st.empty()) {
-    Frame& f = st.back();
-    if (f.e == f.end) { st.pop_back(); continue; }
-    uint32_t e = f.e++;
-    out->push_back(e);
-    if ((t->entry_type[e] & 0xF) == M2K_T_DIR) {
-      uint32_t d = t->entry_child[e];
-      if (!(t->dir_flags[d] & 1)) st.push_back({t->dir_first_entry[d], t->dir_first_entry[d + 1]});
-    }
-  }
-}
-
 // Puts a set of entry ids into filepath.Walk order without walking the tree.  Directories are numbered
 // in Walk order, so an entry's position is fixed by the NEXT directory the walk enters after it:
 // for a file that is the first real sub-directory listed after it in its own directory, or, when

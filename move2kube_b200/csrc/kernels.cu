@@ -748,7 +748,7 @@ struct WalkArgs {
   uint32_t prefix_len;
   uint64_t depth1_state; uint32_t root_ignore;
   const uint32_t* dir_opts;
-  uint64_t* dir_hash; uint8_t* dir_ignore; uint8_t* dir_state; uint8_t* dir_descend;
+  uint8_t* dir_ignore; uint8_t* dir_state; uint8_t* dir_descend;
 };
 
 // does the folded path of directory d equal entry runes E[0..L)?
@@ -849,7 +849,7 @@ void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mas
   if (!t->n_dirs) return;
   WalkArgs a{t->dir_parent, t->dir_entry, t->dir_flags, t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to,
              table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore, t->dir_opts,
-             t->dir_hash, t->dir_ignore, t->dir_state, t->dir_descend};
+             t->dir_ignore, t->dir_state, t->dir_descend};
   uint32_t blocks = (t->n_dirs + 127) / 128;
   k_walk_local<<<blocks, 128, 0, st>>>(t->n_dirs, t->dir_depth, a);
   k_walk_reach<<<blocks, 128, 0, st>>>(t->n_dirs, a);

@@ -110,7 +110,6 @@ struct DevTree {
   uint32_t* dir_subtree = nullptr;        // [n_dirs]
   uint32_t* dir_main_sub = nullptr;       // [n_dirs]
   uint32_t* dir_opts = nullptr;           // [n_dirs]
-  uint64_t* dir_hash = nullptr;           // [n_dirs]
   uint8_t* dir_ignore = nullptr;          // [n_dirs]
   uint8_t* dir_state = nullptr;           // [n_dirs]
   uint8_t* dir_descend = nullptr;         // [n_dirs]
@@ -184,7 +183,6 @@ uint64_t hash_fold(uint64_t h, const std::string& s);
 void parse_ignore_file(const std::string& file_path, const uint8_t* data, uint64_t len,
                        std::vector<std::string>* ignore_dirs, std::vector<std::string>* ignore_contents);
 std::string tree_dir_path(const m2k_tree* t, uint32_t d);
-void walk_order_entries(const m2k_tree* t, std::vector<uint32_t>* out);  // filepath.Walk order of all entries
 void sort_walk_order(const m2k_tree* t, std::vector<uint32_t>* ents);    // a set of entry ids into filepath.Walk order
 
 // ---- tree ownership (packer.cc / synth.cc) ----
