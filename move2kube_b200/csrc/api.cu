@@ -500,11 +500,12 @@ static constexpr uint64_t kChunkFixedCost = 4096;
 static inline uint64_t file_cost(const m2k_tree* tree, uint32_t f) { return tree->file_len[f] + kChunkFixedCost * file_chunks(tree, f); }
 
 extern "C" uint64_t m2k_root_extra_bytes(const m2k_tree* tree) {
-  // what the rank that assembles the result does besides scanning its shard -- name features, subtree /
-  // predicate / walk kernels, merges, result copies -- expressed as bytes of scanning: measured on
-  // B200 as about 0.3 ms + 0.14 ms per million entries, at 7 TB/s
+  // what the rank that assembles the result does on its main stream before the exchange, besides
+  // scanning its shard -- the name kernel, queueing and the blocks its side-stream kernels take from the
+  // scan -- expressed as bytes of scanning.  From the measured gap between rank 0 and the other ranks
+  // reaching the exchange on B200 (2 and 8 GPUs): about 0.06 ms per million entries, at 7 TB/s.
   if (!tree) return 0;
-  return (uint64_t)(7.0e9 * (0.3 + 0.14e-6 * (double)tree->n_entries));
+  return (uint64_t)(7.0e9 * (0.06e-6 * (double)tree->n_entries));
 }
 
 extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t root_extra_bytes,
