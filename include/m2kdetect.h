@@ -239,6 +239,14 @@ int m2k_upload_chunks(m2k_ctx* ctx, const m2k_tree* tree, uint64_t chunk_begin, 
 uint64_t m2k_devtree_content_bytes(const m2k_devtree* dt); /* content bytes resident in this shard (the algorithmic bytes of its scan) */
 int m2k_pieces(m2k_ctx* ctx, m2k_devtree* dt, void* d_dst /* 64 bytes */);
 int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all_pieces /* n_ranks x 64 bytes, rank order */, uint32_t n_ranks);
+/* the same exchange without any host synchronisation: this rank's contribution copied into the
+ * caller's device buffers (n_dirs uint32, n_dirs uint32, 64 bytes, n_files bytes), and the gathered
+ * data (rank-major arrays, the summed flags) merged from the caller's device buffers, all on the
+ * library's stream (m2k_stream).  The caller orders its collectives' stream against that stream with
+ * events and leaves the buffers alone until m2k_finalize has returned. */
+int m2k_export_async(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_content, uint32_t* d_main, void* d_pieces, uint8_t* d_flags);
+int m2k_import_async(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main,
+                     const void* d_all_pieces, const uint8_t* d_flags, uint32_t n_ranks);
 /* which file holds global chunk `chunk`, and which of its chunks that is (a cut at chunk_in_file != 0 splits the file) */
 int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* file, uint32_t* chunk_in_file);
 /* one file's flags on the device, read back (synchronises); and, before m2k_finalize, the flags a

@@ -693,6 +693,38 @@ extern "C" int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* 
   return fail(nullptr, M2K_ERR_ARG, "chunk %llu is past the tree's %llu chunks", (unsigned long long)chunk, (unsigned long long)at);
 }
 
+// The exchange of a sharded pass without a host synchronisation: everything this rank contributes is
+// copied (device to device) into the caller's buffers on the library's stream, and everything gathered
+// is merged from the caller's buffers on that stream.  The caller orders its own stream (the one its
+// collectives run on) against m2k_stream() with events -- and keeps the buffers alive and untouched
+// until the stream has passed the copies / merges (m2k_finalize synchronises it).
+extern "C" int m2k_export_async(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_content, uint32_t* d_main, void* d_pieces, uint8_t* d_flags) {
+  if (!ctx || !dt || !d_content || !d_main || !d_pieces || !d_flags) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  CU(cudaSetDevice(C->device));
+  cudaStream_t s = C->stream;
+  CU(cudaMemcpyAsync(d_content, t->dir_content, 4ull * t->n_dirs, cudaMemcpyDeviceToDevice, s));
+  CU(cudaMemcpyAsync(d_main, t->dir_main, 4ull * t->n_dirs, cudaMemcpyDeviceToDevice, s));
+  if (dt->content) CU(cudaMemcpyAsync(d_pieces, t->pieces, 2 * sizeof(PieceSummary), cudaMemcpyDeviceToDevice, s));
+  else CU(cudaMemsetAsync(d_pieces, 0xFF, 2 * sizeof(PieceSummary), s));
+  CU(cudaMemcpyAsync(d_flags, t->file_flags, t->n_files, cudaMemcpyDeviceToDevice, s));
+  return M2K_OK;
+}
+
+extern "C" int m2k_import_async(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main,
+                                const void* d_all_pieces, const uint8_t* d_flags, uint32_t n_ranks) {
+  if (!ctx || !dt || !d_all_content || !d_all_main || !d_all_pieces || !d_flags || !n_ranks) return fail(nullptr, M2K_ERR_ARG, "bad argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  CU(cudaSetDevice(C->device));
+  launch_merge_partials(C, t, d_all_content, d_all_main, n_ranks);
+  CU(cudaMemcpyAsync(t->file_flags, d_flags, t->n_files, cudaMemcpyDeviceToDevice, C->stream));
+  launch_merge_pieces(C, t, static_cast<const PieceSummary*>(d_all_pieces), 2 * n_ranks);
+  CU(cudaGetLastError());
+  return M2K_OK;
+}
+
 extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main, uint32_t n_ranks) {
   if (!ctx || !dt || !d_all_content || !d_all_main || !n_ranks) return fail(nullptr, M2K_ERR_ARG, "bad argument");
   Ctx* C = &ctx->c;

@@ -30,6 +30,7 @@ EXPORTS = [
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
+    "m2k_export_async", "m2k_import_async",
 ]
 
 
@@ -97,6 +98,8 @@ def load():
     L.m2k_settle_file.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
     L.m2k_devtree_content_bytes.argtypes = [vp]
     L.m2k_devtree_content_bytes.restype = C.c_uint64
+    L.m2k_export_async.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -197,6 +200,12 @@ class Context:
 
     def merge_pieces(self, dt, all_pieces_ptr, n_ranks):
         _check(self.L.m2k_merge_pieces(self.h, dt, all_pieces_ptr, n_ranks), self.h)
+
+    def export_async(self, dt, content_ptr, main_ptr, pieces_ptr, flags_ptr):
+        _check(self.L.m2k_export_async(self.h, dt, content_ptr, main_ptr, pieces_ptr, flags_ptr), self.h)
+
+    def import_async(self, dt, all_content_ptr, all_main_ptr, all_pieces_ptr, flags_ptr, n_ranks):
+        _check(self.L.m2k_import_async(self.h, dt, all_content_ptr, all_main_ptr, all_pieces_ptr, flags_ptr, n_ranks), self.h)
 
     def shard_content_bytes(self, dt) -> int:
         return self.L.m2k_devtree_content_bytes(dt)

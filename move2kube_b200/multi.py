@@ -78,34 +78,40 @@ class RankExchange:
     """The one exchange step of a sharded pass, on torch.distributed (NCCL on GPUs): every rank
     contributes its per-directory partials, its two piece summaries (one all_gather) and its per-file
     flags (all_reduce: the ranges are disjoint, so the byte-wise sum is the union); rank 0 -- the one
-    consumer of the result -- merges them into its device tree, ready for m2k_finalize."""
+    consumer of the result -- merges them into its device tree, ready for m2k_finalize.
 
-    def __init__(self, dist, torch, n_dirs, n_files, world, device="cuda"):
+    Nothing here waits on the host: the library's stream and torch's current stream (where the
+    collectives run) are ordered against each other with events, so a rank queues its whole pass
+    -- scan, export, collectives, merges -- and only m2k_finalize blocks."""
+
+    def __init__(self, dist, torch, n_dirs, n_files, world, ctx, device="cuda"):
         self.dist, self.torch, self.nd, self.world = dist, torch, n_dirs, world
+        self.lib_stream = torch.cuda.ExternalStream(ctx.stream())
         self.width = 2 * n_dirs + 16  # int32 words per rank: content mask, main-file id, 64 bytes of pieces
         self.mine = torch.empty((self.width,), dtype=torch.int32, device=device)
         self.all = torch.empty((world, self.width), dtype=torch.int32, device=device)
+        self.allc = torch.empty((world, n_dirs), dtype=torch.int32, device=device)
+        self.allm = torch.empty((world, n_dirs), dtype=torch.int32, device=device)
+        self.allp = torch.empty((world, 16), dtype=torch.int32, device=device)
         self.flags = torch.empty((n_files,), dtype=torch.uint8, device=device)
 
     def gather(self, ctx, dt):
         nd, m = self.nd, self.mine
-        # the library writes these tensors on its own stream: the previous pass's collectives (which a
-        # rank that does not finalise never waited for) must be done with them first
-        self.torch.cuda.current_stream().synchronize()
-        ctx.partials(dt, m[0:nd].data_ptr(), m[nd:2 * nd].data_ptr())
-        ctx.pieces(dt, m[2 * nd:].data_ptr())
-        ctx.file_flags_get(dt, self.flags.data_ptr())
+        cur = self.torch.cuda.current_stream()
+        # the previous pass's collectives and merges (which a rank that does not finalise never waited
+        # for) must be done with these buffers before the library writes them again
+        cur.synchronize()
+        ctx.export_async(dt, m[0:nd].data_ptr(), m[nd:2 * nd].data_ptr(), m[2 * nd:].data_ptr(), self.flags.data_ptr())
+        cur.wait_stream(self.lib_stream)
         self.dist.all_gather_into_tensor(self.all.view(-1), m)
         self.dist.all_reduce(self.flags)
 
     def merge_on_root(self, ctx, dt, tree, split, fill_seed=None):
         """Rank 0 only, after gather()."""
         nd, a = self.nd, self.all
-        allc = a[:, 0:nd].contiguous()
-        allm = a[:, nd:2 * nd].contiguous()
-        allp = a[:, 2 * nd:].contiguous()
-        self.torch.cuda.current_stream().synchronize()
-        ctx.merge_partials(dt, allc.data_ptr(), allm.data_ptr(), self.world)
-        ctx.file_flags_set(dt, self.flags.data_ptr())
-        ctx.merge_pieces(dt, allp.data_ptr(), self.world)
+        self.allc.copy_(a[:, 0:nd])
+        self.allm.copy_(a[:, nd:2 * nd])
+        self.allp.copy_(a[:, 2 * nd:])
+        self.lib_stream.wait_stream(self.torch.cuda.current_stream())
+        ctx.import_async(dt, self.allc.data_ptr(), self.allm.data_ptr(), self.allp.data_ptr(), self.flags.data_ptr(), self.world)
         return settle_undecided(ctx, tree, dt, split, fill_seed) if split else []

@@ -38,7 +38,7 @@ def main():
             cuts = [0] + inner + [total]
         split = multi.split_files(tree, cuts)
         dt = ctx.upload_chunks(tree, cuts[rank], cuts[rank + 1])
-        xch = multi.RankExchange(dist, torch, nd, nf, world)
+        xch = multi.RankExchange(dist, torch, nd, nf, world, ctx)
         for _ in range(2):                    # twice: the second pass reuses every buffer
             ctx.scan(dt)
             if rank == 0:
