@@ -12,6 +12,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <thread>
 
 #include "m2k_internal.h"
@@ -71,47 +74,58 @@ void tree_release(m2k_tree* t) {
 
 namespace {
 
-struct Ent { std::string name; uint8_t type; };
+// ---- phase 1: the walk, one task per directory, on a team of threads ---------------------------------
+// A directory task opens the directory, reads and sorts its names (byte order == sort.Strings), lstats
+// (and, for symlinks, stats) every entry relative to the open directory, and queues one task per real
+// sub-directory.  Nothing is numbered yet: pre-order ids need the whole shape of the tree.
+struct Ent { std::string name; uint8_t type; uint64_t size; uint32_t child_node; };
 
-struct Walker {
-  std::vector<uint32_t> dir_parent, dir_end, dir_entry, dir_first, dir_depth;
-  std::vector<uint8_t> dir_flags;
-  std::vector<std::string> dir_path;
-  std::vector<uint32_t> entry_dir, entry_name_off, entry_child;
-  std::vector<uint8_t> entry_type;
-  std::vector<uint8_t> names;
-  std::vector<uint32_t> file_entry;
-  std::vector<uint64_t> file_len;
-  uint32_t max_depth = 0;
-  bool newline_name = false;
+struct DirNode {
+  std::string path;  // the path filepath.Walk reports
+  uint32_t depth = 0;
+  uint8_t flags = 0;
+  std::vector<Ent> ents;
+};
 
-  static uint8_t mode_type(mode_t m) {
-    return S_ISREG(m) ? M2K_T_REG : S_ISDIR(m) ? M2K_T_DIR : S_ISLNK(m) ? M2K_T_LNK : M2K_T_OTHER;
+static uint8_t mode_type(mode_t m) {
+  return S_ISREG(m) ? M2K_T_REG : S_ISDIR(m) ? M2K_T_DIR : S_ISLNK(m) ? M2K_T_LNK : M2K_T_OTHER;
+}
+
+struct ParallelWalk {
+  std::mutex m;
+  std::condition_variable cv;
+  std::vector<std::unique_ptr<DirNode>> nodes;
+  std::vector<uint32_t> pending;
+  unsigned active = 0;
+  std::atomic<bool> newline_name{false};
+
+  uint32_t add_node(std::string path, uint32_t depth) {  // caller holds m
+    nodes.emplace_back(new DirNode());
+    nodes.back()->path = std::move(path);
+    nodes.back()->depth = depth;
+    return (uint32_t)nodes.size() - 1;
   }
 
-  void visit(int parent_fd, const char* name, const std::string& path, uint32_t parent, uint32_t my_entry, uint32_t depth) {
-    uint32_t id = (uint32_t)dir_parent.size();
-    dir_parent.push_back(parent); dir_end.push_back(0); dir_entry.push_back(my_entry); dir_depth.push_back(depth);
-    dir_flags.push_back(0); dir_path.push_back(path);
-    dir_first.push_back((uint32_t)entry_dir.size());
-    if (depth > max_depth) max_depth = depth;
-    int fd = openat(parent_fd, name, O_RDONLY | O_DIRECTORY | O_CLOEXEC);
+  void process(uint32_t id) {
+    DirNode* n;
+    { std::lock_guard<std::mutex> lk(m); n = nodes[id].get(); }
+    int fd = open(n->path.c_str(), O_RDONLY | O_DIRECTORY | O_CLOEXEC);
     DIR* dp = fd >= 0 ? fdopendir(fd) : nullptr;
     if (!dp) {
       if (fd >= 0) close(fd);
-      dir_flags[id] = 1;  // ReadDir failed: the walk reports the directory and moves on
-      dir_end[id] = (uint32_t)dir_parent.size();
+      n->flags = 1;  // ReadDir failed: the walk reports the directory and moves on
       return;
     }
-    std::vector<Ent> ents;
+    std::vector<Ent>& ents = n->ents;
     while (struct dirent* de = readdir(dp)) {
-      const char* n = de->d_name;
-      if (n[0] == '.' && (n[1] == 0 || (n[1] == '.' && n[2] == 0))) continue;
-      ents.push_back({n, 0});
+      const char* nm = de->d_name;
+      if (nm[0] == '.' && (nm[1] == 0 || (nm[1] == '.' && nm[2] == 0))) continue;
+      ents.push_back({nm, 0, 0, M2K_NONE});
     }
-    std::sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.name < b.name; });  // byte order == sort.Strings
-    uint32_t e0 = (uint32_t)entry_dir.size();
-    for (Ent& en : ents) {
+    std::sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.name < b.name; });
+    std::vector<uint32_t> subdirs;
+    for (size_t k = 0; k < ents.size(); k++) {
+      Ent& en = ents[k];
       struct stat st, st2;
       uint8_t lt = M2K_T_ERR, ft = M2K_T_ERR;
       if (fstatat(fd, en.name.c_str(), &st, AT_SYMLINK_NOFOLLOW) == 0) {
@@ -120,33 +134,116 @@ struct Walker {
         else ft = lt;
       }
       en.type = (uint8_t)(lt | (ft << 4));
+      if (lt != M2K_T_DIR && ft == M2K_T_REG) en.size = (uint64_t)st.st_size;
       if (en.name.find('\n') != std::string::npos) newline_name = true;
-      uint32_t e = (uint32_t)entry_dir.size();
-      entry_dir.push_back(id);
-      entry_name_off.push_back((uint32_t)names.size());
-      names.insert(names.end(), en.name.begin(), en.name.end());
-      entry_type.push_back(en.type);
-      uint32_t child = M2K_NONE;
-      if (lt != M2K_T_DIR && ft == M2K_T_REG) {
-        child = (uint32_t)file_entry.size();
-        file_entry.push_back(e);
-        file_len.push_back((uint64_t)st.st_size);
-      }
-      entry_child.push_back(child);
-    }
-    for (size_t k = 0; k < ents.size(); k++) {
-      if ((ents[k].type & 0xF) != M2K_T_DIR) continue;
-      uint32_t e = e0 + (uint32_t)k;
-      entry_child[e] = (uint32_t)dir_parent.size();
-      std::string child_path = path;
-      if (child_path.empty() || child_path.back() != '/') child_path += '/';
-      child_path += ents[k].name;
-      visit(fd, ents[k].name.c_str(), child_path, id, e, depth + 1);
+      if (lt == M2K_T_DIR) subdirs.push_back((uint32_t)k);
     }
     closedir(dp);
-    dir_end[id] = (uint32_t)dir_parent.size();
+    if (!subdirs.empty()) {
+      std::lock_guard<std::mutex> lk(m);
+      for (uint32_t k : subdirs) {
+        std::string cp = n->path;
+        if (cp.empty() || cp.back() != '/') cp += '/';
+        cp += ents[k].name;
+        ents[k].child_node = add_node(std::move(cp), n->depth + 1);
+        pending.push_back(ents[k].child_node);
+      }
+      cv.notify_all();
+    }
+  }
+
+  void worker() {
+    for (;;) {
+      uint32_t id;
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return !pending.empty() || active == 0; });
+        if (pending.empty()) return;  // nothing queued and nobody working: the walk is complete
+        id = pending.back();
+        pending.pop_back();
+        active++;
+      }
+      process(id);
+      {
+        std::lock_guard<std::mutex> lk(m);
+        active--;
+        if (active == 0 && pending.empty()) cv.notify_all();
+      }
+    }
+  }
+
+  void run(const char* root_path, unsigned nt) {
+    { std::lock_guard<std::mutex> lk(m); pending.push_back(add_node(root_path, 0)); }
+    std::vector<std::thread> th;
+    for (unsigned i = 1; i < nt; i++) th.emplace_back([this] { worker(); });
+    worker();
+    for (auto& x : th) x.join();
   }
 };
+
+// ---- phase 2: number the directories in DFS pre-order and flatten into the struct of arrays --------
+struct Flat {
+  std::vector<uint32_t> dir_parent, dir_end, dir_entry, dir_depth, dir_node;
+  std::vector<uint8_t> dir_flags;
+  std::vector<uint32_t> entry_dir, entry_name_off, entry_child;
+  std::vector<uint8_t> entry_type;
+  std::vector<uint8_t> names;
+  std::vector<uint32_t> file_entry;
+  std::vector<uint64_t> file_len;
+  uint32_t max_depth = 0;
+};
+
+static void flatten(ParallelWalk& w, Flat& o) {
+  size_t n_ents = 0, n_name = 0;
+  for (auto& n : w.nodes) { n_ents += n->ents.size(); for (const Ent& e : n->ents) n_name += e.name.size(); }
+  const size_t nd = w.nodes.size();
+  o.dir_parent.reserve(nd); o.dir_end.assign(nd, 0); o.dir_entry.reserve(nd); o.dir_depth.reserve(nd); o.dir_node.reserve(nd); o.dir_flags.reserve(nd);
+  o.entry_dir.reserve(n_ents); o.entry_name_off.reserve(n_ents + 1); o.entry_child.reserve(n_ents); o.entry_type.reserve(n_ents);
+  o.names.reserve(n_name);
+  struct Frame { uint32_t node, id, e0, next; };  // next: index of the next entry of this directory to look at for a sub-directory
+  std::vector<Frame> st;
+  auto enter = [&](uint32_t node, uint32_t parent, uint32_t my_entry) {
+    const DirNode& n = *w.nodes[node];
+    const uint32_t id = (uint32_t)o.dir_parent.size();
+    o.dir_parent.push_back(parent); o.dir_entry.push_back(my_entry); o.dir_depth.push_back(n.depth); o.dir_flags.push_back(n.flags);
+    o.dir_node.push_back(node);
+    if (n.depth > o.max_depth) o.max_depth = n.depth;
+    const uint32_t e0 = (uint32_t)o.entry_dir.size();
+    for (const Ent& en : n.ents) {
+      const uint32_t e = (uint32_t)o.entry_dir.size();
+      o.entry_dir.push_back(id);
+      o.entry_name_off.push_back((uint32_t)o.names.size());
+      o.names.insert(o.names.end(), en.name.begin(), en.name.end());
+      o.entry_type.push_back(en.type);
+      uint32_t child = M2K_NONE;
+      const uint32_t lt = en.type & 0xF, ft = en.type >> 4;
+      if (lt != M2K_T_DIR && ft == M2K_T_REG) {
+        child = (uint32_t)o.file_entry.size();
+        o.file_entry.push_back(e);
+        o.file_len.push_back(en.size);
+      }
+      o.entry_child.push_back(child);
+    }
+    st.push_back({node, id, e0, 0});
+  };
+  enter(0, M2K_NONE, M2K_NONE);
+  while (!st.empty()) {
+    Frame& f = st.back();
+    const DirNode& n = *w.nodes[f.node];
+    bool descended = false;
+    while (f.next < n.ents.size()) {
+      const uint32_t k = f.next++;
+      if ((n.ents[k].type & 0xF) != M2K_T_DIR) continue;
+      const uint32_t e = f.e0 + k;
+      o.entry_child[e] = (uint32_t)o.dir_parent.size();
+      const uint32_t my_id = f.id;  // `f` dangles once enter() grows the stack
+      enter(n.ents[k].child_node, my_id, e);
+      descended = true;
+      break;
+    }
+    if (!descended) { o.dir_end[f.id] = (uint32_t)o.dir_parent.size(); st.pop_back(); }
+  }
+}
 
 }  // namespace
 
@@ -157,12 +254,17 @@ int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tre
     *err = std::string("cannot stat root ") + root_path + ": " + strerror(errno);
     return M2K_ERR_IO;
   }
-  Walker w;
-  w.visit(AT_FDCWD, root_path, root_path, M2K_NONE, M2K_NONE, 0);
-  if (w.newline_name) {
+  unsigned nt = std::thread::hardware_concurrency();
+  if (nt == 0) nt = 4;
+  if (nt > 32) nt = 32;
+  ParallelWalk pw;
+  pw.run(root_path, nt);
+  if (pw.newline_name) {
     *err = "a file name contains a newline: the reference's `find | wc -l` predicates are order dependent for such trees";
     return M2K_ERR_UNSUPPORTED;
   }
+  Flat w;
+  flatten(pw, w);
   uint32_t nd = (uint32_t)w.dir_parent.size(), ne = (uint32_t)w.entry_dir.size(), nf = (uint32_t)w.file_entry.size();
   // sizes can change between lstat and read: the read pass below is authoritative, so lay files
   // out with the stat sizes and clamp what is read
@@ -184,12 +286,8 @@ int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tre
   memcpy(t->dir_parent, w.dir_parent.data(), 4ull * nd); memcpy(t->dir_end, w.dir_end.data(), 4ull * nd);
   memcpy(t->dir_entry, w.dir_entry.data(), 4ull * nd); memcpy(t->dir_depth, w.dir_depth.data(), 4ull * nd);
   memcpy(t->dir_flags, w.dir_flags.data(), nd);
-  for (uint32_t d = 0; d < nd; d++) t->dir_first_entry[d] = w.dir_first[d];
-  t->dir_first_entry[nd] = ne;
-  // a directory's entries are contiguous only if nothing was appended between them: true because
-  // visit() appends all entries of a directory before recursing; but dir_first of the NEXT directory
-  // id is not dir_first[d+1] of the array for non-leaf d.  Recompute the CSR end from entry_dir.
   {
+    // entries were appended directory by directory in id order: the CSR is a count per directory
     std::vector<uint32_t> cnt(nd + 1, 0);
     for (uint32_t e = 0; e < ne; e++) cnt[w.entry_dir[e] + 1]++;
     for (uint32_t d = 0; d < nd; d++) cnt[d + 1] += cnt[d];
@@ -203,40 +301,84 @@ int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tre
   memcpy(t->file_entry, w.file_entry.data(), 4ull * nf);
   for (uint32_t f = 0; f < nf; f++) { t->file_off[f] = off[f]; t->file_len[f] = w.file_len[f]; }
   {
-    unsigned nt = std::thread::hardware_concurrency();
-    if (nt == 0) nt = 4;
-    if (nt > 32) nt = 32;
-    if (nt > nf) nt = nf ? nf : 1;
-    std::atomic<uint32_t> next{0};
-    auto worker = [&]() {
-      for (;;) {
-        uint32_t f = next.fetch_add(1);
-        if (f >= nf) break;
-        uint32_t e = w.file_entry[f];
-        std::string p = w.dir_path[w.entry_dir[e]];
-        if (p.empty() || p.back() != '/') p += '/';
-        p.append(reinterpret_cast<const char*>(w.names.data()) + w.entry_name_off[e],
-                 (e + 1 < ne ? w.entry_name_off[e + 1] : (uint32_t)w.names.size()) - w.entry_name_off[e]);
-        uint64_t cap = w.file_len[f], got = 0;
-        uint8_t* dst = t->bytes + off[f];
-        if (cap == 0) continue;
-        int fd = open(p.c_str(), O_RDONLY | O_CLOEXEC);
-        if (fd >= 0) {
-          while (got < cap) {
-            ssize_t r = read(fd, dst + got, cap - got);
-            if (r <= 0) break;
-            got += (uint64_t)r;
-          }
-          close(fd);
-        }
-        t->file_len[f] = got;  // unreadable or shrunk: what could be read (0 = no content signatures)
-        uint64_t padded = (cap + 15) & ~15ull;
-        memset(dst + got, 0, padded - got);
+    // ---- phase 3: the bytes.  Work units are runs of consecutive file ids (files of one directory are
+    // consecutive, so a worker opens the directory once and the files relative to it) and, for large
+    // files, segments read with pread, so that one multi-GB file does not pin the pass to one thread.
+    constexpr uint64_t kSegBytes = 32ull << 20;
+    constexpr uint32_t kRunFiles = 128;
+    struct Unit { uint32_t f0, f1; uint64_t seg_off, seg_len; uint64_t got; };
+    std::vector<Unit> units;
+    for (uint32_t f = 0; f < nf;) {
+      if (w.file_len[f] > kSegBytes) {
+        for (uint64_t o = 0; o < w.file_len[f]; o += kSegBytes) units.push_back({f, f + 1, o, std::min(kSegBytes, w.file_len[f] - o), 0});
+        f++;
+        continue;
       }
+      uint32_t g = f;
+      uint64_t bytes = 0;
+      while (g < nf && g - f < kRunFiles && w.file_len[g] <= kSegBytes && bytes <= kSegBytes) { bytes += w.file_len[g]; g++; }
+      units.push_back({f, g, 0, 0, 0});
+      f = g;
+    }
+    if (nt > units.size()) nt = units.empty() ? 1 : (unsigned)units.size();
+    std::atomic<size_t> next{0};
+    auto name_of = [&](uint32_t e) {
+      return std::string(reinterpret_cast<const char*>(w.names.data()) + w.entry_name_off[e],
+                         (e + 1 < ne ? w.entry_name_off[e + 1] : (uint32_t)w.names.size()) - w.entry_name_off[e]);
+    };
+    auto worker = [&]() {
+      int dfd = -1;
+      uint32_t dfd_dir = M2K_NONE;
+      for (;;) {
+        size_t u = next.fetch_add(1);
+        if (u >= units.size()) break;
+        Unit& un = units[u];
+        for (uint32_t f = un.f0; f < un.f1; f++) {
+          const uint64_t cap = w.file_len[f];
+          if (cap == 0) continue;
+          const uint32_t e = w.file_entry[f], d = w.entry_dir[e];
+          if (d != dfd_dir) {
+            if (dfd >= 0) close(dfd);
+            dfd = open(pw.nodes[w.dir_node[d]]->path.c_str(), O_RDONLY | O_DIRECTORY | O_CLOEXEC);
+            dfd_dir = d;
+          }
+          uint8_t* dst = t->bytes + off[f];
+          const uint64_t lo = un.seg_len ? un.seg_off : 0, want = un.seg_len ? un.seg_len : cap;
+          uint64_t got = 0;
+          int fd = dfd >= 0 ? openat(dfd, name_of(e).c_str(), O_RDONLY | O_CLOEXEC) : -1;
+          if (fd >= 0) {
+            while (got < want) {
+              ssize_t r = pread(fd, dst + lo + got, want - got, (off_t)(lo + got));
+              if (r <= 0) break;
+              got += (uint64_t)r;
+            }
+            close(fd);
+          }
+          if (un.seg_len) { un.got = got; continue; }  // stitched below
+          t->file_len[f] = got;  // unreadable or shrunk: what could be read (0 = no content signatures)
+          memset(dst + got, 0, ((cap + 15) & ~15ull) - got);
+        }
+      }
+      if (dfd >= 0) close(dfd);
     };
     std::vector<std::thread> th;
-    for (unsigned i = 0; i < nt; i++) th.emplace_back(worker);
+    for (unsigned i = 1; i < nt; i++) th.emplace_back(worker);
+    worker();
     for (auto& x : th) x.join();
+    // segmented files: the content is the run of complete segments plus the first short one
+    for (size_t u = 0; u < units.size();) {
+      if (!units[u].seg_len) { u++; continue; }
+      const uint32_t f = units[u].f0;
+      uint64_t len = 0;
+      bool open_run = true;
+      for (; u < units.size() && units[u].seg_len && units[u].f0 == f; u++) {
+        if (!open_run) continue;
+        len += units[u].got;
+        if (units[u].got < units[u].seg_len) open_run = false;
+      }
+      t->file_len[f] = len;
+      memset(t->bytes + off[f] + len, 0, ((w.file_len[f] + 15) & ~15ull) - len);
+    }
     memset(t->bytes + total - 16, 0, 16);
   }
   uint64_t cb = 0;
