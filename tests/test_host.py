@@ -272,3 +272,25 @@ def test_plan_shards_cuts_only_large_files():
                     assert max(sizes) - min(sizes) <= 2 * ((1 << 20) + 4096 * 17)
     finally:
         lib.tree_free_host(tp)
+
+
+def test_packer_reproduces_a_materialised_generator_tree(tmp_path):
+    """A generator tree written to disk and packed again (threaded walk, per-directory reads, one file
+    large enough to be read in pread segments) is the generator's tree, array for array and byte for byte."""
+    from move2kube_b200 import synthfs
+    p = small_synth(seed=17, n_files=4000, n_dirs=300, total=70 << 20, n_huge=1, huge_bytes=40 << 20)
+    src = lib.synth_tree_host(p, host_bytes=True)
+    root = os.fsencode(str(tmp_path / "tree"))
+    try:
+        n = synthfs.materialize(src, root)
+        assert n == src.contents.content_bytes
+        got = lib.pack_tree_host(root)
+        try:
+            a, b = _tree_arrays(src), _tree_arrays(got)
+            assert max(src.contents.file_len[0:src.contents.n_files]) > 32 << 20
+            for k in a:
+                assert a[k] == b[k], k
+        finally:
+            lib.tree_free_host(got)
+    finally:
+        lib.tree_free_host(src)
