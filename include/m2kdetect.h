@@ -217,6 +217,12 @@ int m2k_synth_fill_host(const m2k_tree* tree, uint64_t seed, uint32_t file_begin
 /* -- whole path, host buffers in, host results out (H2D + kernels + D2H): the call a plugin makes -- */
 int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_params* params, m2k_result** out);
 void m2k_result_free(m2k_result* r);
+/* -- the same for a tree that is looked at once, straight from the file system: the walk and numbering
+ * of m2k_pack_tree, but the file bytes are never gathered on the host -- host threads read them into
+ * the context's two pinned blocks while the DMA engine drains the other one.  *tree_out is the packed
+ * tree without a bytes blob (names, types, sizes, and the contents of the .m2kignore files); release
+ * it with m2k_tree_free(ctx, tree) after m2k_result_free. -- */
+int m2k_pack_detect(m2k_ctx* ctx, const char* root_path, const m2k_detect_params* params, m2k_tree** tree_out, m2k_result** out);
 
 /* -- staged form (bench, multi-GPU): a shard = file ids [file_begin, file_end) -- */
 int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out);

@@ -336,6 +336,13 @@ static void parallel_memcpy(void* dst, const void* src, size_t n);  // below, on
 // while the DMA engine drains the other -- which needs no page-locking of the caller's buffer (that
 // costs more than reading the files did: 0.6 s for 2 GB).
 static constexpr size_t kStageBytes = 32u << 20;
+static int ensure_stage(Ctx* C) {
+  for (int k = 0; k < 2; k++) {
+    if (!C->stage[k]) { CU(cudaHostAlloc(&C->stage[k], kStageBytes, cudaHostAllocDefault)); CU(cudaEventCreateWithFlags(&C->stage_ev[k], cudaEventDisableTiming)); }
+    else CU(cudaEventSynchronize(C->stage_ev[k]));
+  }
+  return M2K_OK;
+}
 static int copy_to_device(Ctx* C, cudaStream_t s, void* dst, const void* src, size_t n) {
   if (!n) return M2K_OK;
   cudaPointerAttributes attr;
@@ -343,10 +350,7 @@ static int copy_to_device(Ctx* C, cudaStream_t s, void* dst, const void* src, si
   if (cudaPointerGetAttributes(&attr, src) == cudaSuccess) pageable = attr.type == cudaMemoryTypeUnregistered;
   else cudaGetLastError();
   if (!pageable || n < (4u << 20)) { CU(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s)); return M2K_OK; }
-  for (int k = 0; k < 2; k++) {
-    if (!C->stage[k]) { CU(cudaHostAlloc(&C->stage[k], kStageBytes, cudaHostAllocDefault)); CU(cudaEventCreateWithFlags(&C->stage_ev[k], cudaEventDisableTiming)); }
-    else CU(cudaEventSynchronize(C->stage_ev[k]));
-  }
+  if (int rc = ensure_stage(C)) return rc;
   size_t off = 0;
   for (int k = 0; off < n; k ^= 1) {
     const size_t len = std::min(kStageBytes, n - off);
@@ -1241,6 +1245,82 @@ extern "C" int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_p
     (*out)->n_kernel_launches = (uint32_t)(ctx->c.launches - l0);
   }
   return rc;
+}
+
+// Pack and detect in one call, for a tree that is looked at once: the walk and the numbering as in
+// m2k_pack_tree, but the file bytes are never gathered on the host -- a team of threads reads them
+// straight into the context's two pinned blocks while the DMA engine drains the other one into the
+// device buffer.  *tree_out is the packed tree WITHOUT a bytes blob (names, types, sizes; the
+// .m2kignore contents are kept for the ignore rules); release it with m2k_tree_free.
+extern "C" int m2k_pack_detect(m2k_ctx* ctx, const char* root_path, const m2k_detect_params* params, m2k_tree** tree_out, m2k_result** out) {
+  if (!ctx || !root_path || !tree_out || !out) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_pack_detect: NULL argument");
+  Ctx* C = &ctx->c;
+  *tree_out = nullptr;
+  *out = nullptr;
+  CU(cudaSetDevice(C->device));
+  const bool content = !(params && params->skip_content);
+  double t0 = now_ms();
+  uint64_t l0 = C->launches;
+  PackPlan plan;
+  m2k_tree* tree = nullptr;
+  std::string err;
+  if (int rc = pack_plan(root_path, content ? 1 : 0, false, false, &plan, &tree, &err)) return fail(C, rc, "%s", err.c_str());
+  pack_keep_rule_files(&plan, tree);
+  m2k_devtree* dt = nullptr;
+  int rc = upload_impl(ctx, tree, 0, tree->n_files, 0, M2K_NONE, &dt);
+  if (rc != M2K_OK) { tree_release(tree); return rc; }
+  auto drop = [&]() { m2k_devtree_free(ctx, dt); tree_release(tree); };
+  // stream the bytes: block k is filled by the team (each thread a byte sub-range: files are opened
+  // relative to their directory, large files are shared between threads through pread) while block
+  // k-1 is on its way to the device
+  std::atomic<bool> stale{false};
+  {
+    if ((rc = ensure_stage(C)) != M2K_OK) { drop(); return rc; }
+    const uint64_t total = pack_plan_bytes(&plan);
+    cudaStream_t s = C->stream;
+    cudaError_t ce = cudaEventRecord(C->ev[0], s);
+    int k = 0;
+    for (uint64_t lo = 0; lo < total && ce == cudaSuccess; lo += kStageBytes, k ^= 1) {
+      const uint64_t len = std::min<uint64_t>(kStageBytes, total - lo);
+      ce = cudaEventSynchronize(C->stage_ev[k]);
+      if (ce != cudaSuccess) break;
+      uint8_t* blk = static_cast<uint8_t*>(C->stage[k]);
+      const unsigned nt = std::max(1u, std::min<unsigned>(host_threads(len, 256u << 10), 32));
+      run_threads(nt, [&](unsigned tid) {
+        uint64_t a = (len * tid / nt) & ~15ull, b = tid + 1 == nt ? len : (len * (tid + 1) / nt) & ~15ull;
+        if (b > a && !pack_read_range(&plan, lo + a, lo + b, blk + a)) stale = true;
+      });
+      ce = cudaMemcpyAsync(dt->t.bytes + lo, blk, len, cudaMemcpyHostToDevice, s);
+      if (ce == cudaSuccess) ce = cudaEventRecord(C->stage_ev[k], s);
+    }
+    if (ce == cudaSuccess) ce = cudaEventRecord(C->ev[1], s);
+    if (ce != cudaSuccess) { drop(); return fail(C, M2K_ERR_CUDA, "streaming the tree to the device failed: %s", cudaGetErrorString(ce)); }
+  }
+  if (stale) {
+    // a file shrank between the walk and the read: the layout is stale.  Take the two-step road, whose
+    // read pass settles the sizes before anything is uploaded.
+    drop();
+    m2k_tree* full = nullptr;
+    if ((rc = pack_tree_impl(false, root_path, content ? 1 : 0, &full, &err)) != M2K_OK) return fail(C, rc, "%s", err.c_str());
+    rc = m2k_detect(ctx, full, params, out);
+    if (rc != M2K_OK) { tree_release(full); return rc; }
+    *tree_out = full;
+    return M2K_OK;
+  }
+  rc = m2k_scan(ctx, dt, params);
+  if (rc == M2K_OK) rc = m2k_finalize(ctx, dt, params, out);
+  if (rc != M2K_OK) { drop(); return rc; }
+  cudaStreamSynchronize(C->stream);
+  float ms_h2d = 0.f;
+  if (cudaEventElapsedTime(&ms_h2d, C->ev[0], C->ev[1]) != cudaSuccess) cudaGetLastError();
+  devtree_release(&dt->t);
+  dt->t = DevTree();
+  (*out)->owner = dt;
+  (*out)->ms_h2d = ms_h2d;  // here: reading the files and copying them, overlapped
+  (*out)->ms_total = (float)(now_ms() - t0);
+  (*out)->n_kernel_launches = (uint32_t)(C->launches - l0);
+  *tree_out = tree;
+  return M2K_OK;
 }
 
 // ---- host helpers exported for the mirror ----------------------------------------------------

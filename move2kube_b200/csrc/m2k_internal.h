@@ -201,6 +201,13 @@ m2k_tree* tree_alloc(uint32_t n_dirs, uint32_t n_entries, uint32_t n_files, uint
                      bool with_bytes, bool pinned, const char* root);
 void tree_release(m2k_tree* t);
 int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tree** out, std::string* err);
+// the packer in steps, for callers that stream the bytes instead of holding them (m2k_pack_detect):
+// the walk + numbering + byte layout (a tree with or without a bytes blob), then any byte range on demand
+struct PackPlan { struct Impl; Impl* p; PackPlan(); ~PackPlan(); PackPlan(const PackPlan&) = delete; PackPlan& operator=(const PackPlan&) = delete; };
+int pack_plan(const char* root_path, int read_content, bool pinned, bool with_bytes, PackPlan* plan, m2k_tree** out, std::string* err);
+uint64_t pack_plan_bytes(const PackPlan* plan);
+bool pack_read_range(const PackPlan* plan, uint64_t lo, uint64_t hi, uint8_t* dst);
+void pack_keep_rule_files(const PackPlan* plan, m2k_tree* t);
 int synth_tree_impl(bool pinned, const m2k_synth_params* p, int host_bytes, m2k_tree** out, std::string* err);
 void synth_fill_host(const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, uint8_t* dst, int n_threads);
 

@@ -247,26 +247,39 @@ static void flatten(ParallelWalk& w, Flat& o) {
 
 }  // namespace
 
-int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tree** out, std::string* err) {
+// Everything of a packed tree except the bytes: the walk, the numbering, the layout of the byte blob.
+struct PackPlan::Impl {
+  ParallelWalk pw;
+  Flat w;
+  std::vector<uint64_t> off;
+  uint64_t total = 0;
+  unsigned nt = 4;
+};
+PackPlan::PackPlan() : p(new Impl()) {}
+PackPlan::~PackPlan() { delete p; }
+
+int pack_plan(const char* root_path, int read_content, bool pinned, bool with_bytes, PackPlan* plan, m2k_tree** out, std::string* err) {
   *out = nullptr;
   struct stat st;
   if (stat(root_path, &st) != 0) {
     *err = std::string("cannot stat root ") + root_path + ": " + strerror(errno);
     return M2K_ERR_IO;
   }
+  PackPlan::Impl& P = *plan->p;
   unsigned nt = std::thread::hardware_concurrency();
   if (nt == 0) nt = 4;
   if (nt > 32) nt = 32;
-  ParallelWalk pw;
+  P.nt = nt;
+  ParallelWalk& pw = P.pw;
   pw.run(root_path, nt);
   if (pw.newline_name) {
     *err = "a file name contains a newline: the reference's `find | wc -l` predicates are order dependent for such trees";
     return M2K_ERR_UNSUPPORTED;
   }
-  Flat w;
+  Flat& w = P.w;
   flatten(pw, w);
   uint32_t nd = (uint32_t)w.dir_parent.size(), ne = (uint32_t)w.entry_dir.size(), nf = (uint32_t)w.file_entry.size();
-  // sizes can change between lstat and read: the read pass below is authoritative, so lay files
+  // sizes can change between lstat and read: the read pass is authoritative, so lay files
   // out with the stat sizes and clamp what is read
   // read_content == 0: names only -- but the .m2kignore files are always read, the walk needs their rules
   if (!read_content) {
@@ -276,11 +289,13 @@ int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tre
       if (!(n1 - n0 == 10 && memcmp(w.names.data() + n0, ".m2kignore", 10) == 0)) w.file_len[f] = 0;
     }
   }
-  std::vector<uint64_t> off(nf);
+  std::vector<uint64_t>& off = P.off;
+  off.resize(nf);
   uint64_t total = 0;
   for (uint32_t f = 0; f < nf; f++) { off[f] = total; total += (w.file_len[f] + 15) & ~15ull; }
   total += 16;
-  m2k_tree* t = tree_alloc(nd, ne, nf, w.names.size(), total, true, pinned, root_path);
+  P.total = total;
+  m2k_tree* t = tree_alloc(nd, ne, nf, w.names.size(), total, with_bytes, pinned, root_path);
   if (!t) { *err = "out of host memory while packing"; return M2K_ERR_NOMEM; }
   t->max_depth = w.max_depth;
   memcpy(t->dir_parent, w.dir_parent.data(), 4ull * nd); memcpy(t->dir_end, w.dir_end.data(), 4ull * nd);
@@ -299,7 +314,92 @@ int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tre
   memcpy(t->entry_type, w.entry_type.data(), ne); memcpy(t->entry_child, w.entry_child.data(), 4ull * ne);
   if (!w.names.empty()) memcpy(t->names, w.names.data(), w.names.size());
   memcpy(t->file_entry, w.file_entry.data(), 4ull * nf);
-  for (uint32_t f = 0; f < nf; f++) { t->file_off[f] = off[f]; t->file_len[f] = w.file_len[f]; }
+  uint64_t cb = 0;
+  for (uint32_t f = 0; f < nf; f++) { t->file_off[f] = off[f]; t->file_len[f] = w.file_len[f]; cb += w.file_len[f]; }
+  t->content_bytes = cb;
+  *out = t;
+  return M2K_OK;
+}
+
+uint64_t pack_plan_bytes(const PackPlan* plan) { return plan->p->total; }
+
+// Bytes [lo, hi) of the blob the plan laid out, read from the files into dst (dst[0] is byte lo): this
+// thread's share of a block that a team fills together.  Files are opened relative to their directory
+// and read with pread, so a file that straddles the range contributes just its part; padding is zeroed.
+// Returns false when a file turned out shorter than its lstat size (the plan is then stale).
+bool pack_read_range(const PackPlan* plan, uint64_t lo, uint64_t hi, uint8_t* dst) {
+  const PackPlan::Impl& P = *plan->p;
+  const Flat& w = P.w;
+  const uint32_t nf = (uint32_t)w.file_entry.size(), ne = (uint32_t)w.entry_dir.size();
+  if (hi > P.total) hi = P.total;
+  if (lo >= hi) return true;
+  // first file whose padded extent ends after lo
+  uint32_t f = (uint32_t)(std::upper_bound(P.off.begin(), P.off.end(), lo) - P.off.begin());
+  if (f > 0) f--;
+  bool ok = true;
+  int dfd = -1;
+  uint32_t dfd_dir = M2K_NONE;
+  uint64_t at = lo;  // everything in [lo, at) has been written
+  for (; f < nf && P.off[f] < hi; f++) {
+    const uint64_t fb = P.off[f], len = w.file_len[f], fe = fb + len;
+    const uint64_t a = std::max(fb, lo), b = std::min(fe, hi);
+    if (a > at) { memset(dst + (at - lo), 0, a - at); at = a; }  // padding before this file's part
+    if (b <= a) continue;
+    const uint32_t e = w.file_entry[f], d = w.entry_dir[e];
+    if (d != dfd_dir) {
+      if (dfd >= 0) close(dfd);
+      dfd = open(P.pw.nodes[w.dir_node[d]]->path.c_str(), O_RDONLY | O_DIRECTORY | O_CLOEXEC);
+      dfd_dir = d;
+    }
+    const std::string name(reinterpret_cast<const char*>(w.names.data()) + w.entry_name_off[e],
+                           (e + 1 < ne ? w.entry_name_off[e + 1] : (uint32_t)w.names.size()) - w.entry_name_off[e]);
+    uint64_t got = 0;
+    const int fd = dfd >= 0 ? openat(dfd, name.c_str(), O_RDONLY | O_CLOEXEC) : -1;
+    if (fd >= 0) {
+      while (got < b - a) {
+        ssize_t r = pread(fd, dst + (a - lo) + got, b - a - got, (off_t)(a - fb + got));
+        if (r <= 0) break;
+        got += (uint64_t)r;
+      }
+      close(fd);
+    }
+    if (got < b - a) { ok = false; memset(dst + (a - lo) + got, 0, b - a - got); }
+    at = b;
+  }
+  if (at < hi) memset(dst + (at - lo), 0, hi - at);
+  if (dfd >= 0) close(dfd);
+  return ok;
+}
+
+// The rule files' contents, for a tree packed without a host copy of the bytes (m2k_prepare reads them).
+void pack_keep_rule_files(const PackPlan* plan, m2k_tree* t) {
+  const PackPlan::Impl& P = *plan->p;
+  const Flat& w = P.w;
+  TreeOwner* o = static_cast<TreeOwner*>(t->owner);
+  const uint32_t nf = (uint32_t)w.file_entry.size(), ne = (uint32_t)w.entry_dir.size();
+  for (uint32_t f = 0; f < nf; f++) {
+    const uint32_t e = w.file_entry[f];
+    const uint32_t n0 = w.entry_name_off[e], n1 = e + 1 < ne ? w.entry_name_off[e + 1] : (uint32_t)w.names.size();
+    if (!(n1 - n0 == 10 && memcmp(w.names.data() + n0, ".m2kignore", 10) == 0)) continue;
+    std::string data((size_t)((w.file_len[f] + 15) & ~15ull), '\0');
+    if (!data.empty()) pack_read_range(plan, P.off[f], P.off[f] + data.size(), reinterpret_cast<uint8_t*>(&data[0]));
+    data.resize((size_t)w.file_len[f]);
+    o->literal_file.push_back(f);  // ascending: host_file_bytes searches this list
+    o->literal_data.push_back(std::move(data));
+  }
+}
+
+int pack_tree_impl(bool pinned, const char* root_path, int read_content, m2k_tree** out, std::string* err) {
+  PackPlan plan;
+  m2k_tree* t = nullptr;
+  if (int rc = pack_plan(root_path, read_content, pinned, true, &plan, &t, err)) return rc;
+  PackPlan::Impl& P = *plan.p;
+  ParallelWalk& pw = P.pw;
+  Flat& w = P.w;
+  std::vector<uint64_t>& off = P.off;
+  const uint64_t total = P.total;
+  unsigned nt = P.nt;
+  const uint32_t ne = (uint32_t)w.entry_dir.size(), nf = (uint32_t)w.file_entry.size();
   {
     // ---- phase 3: the bytes.  Work units are runs of consecutive file ids (files of one directory are
     // consecutive, so a worker opens the directory once and the files relative to it) and, for large

@@ -30,7 +30,7 @@ EXPORTS = [
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
-    "m2k_export_async", "m2k_import_async",
+    "m2k_export_async", "m2k_import_async", "m2k_pack_detect",
 ]
 
 
@@ -100,6 +100,7 @@ def load():
     L.m2k_devtree_content_bytes.restype = C.c_uint64
     L.m2k_export_async.argtypes = [vp, vp, vp, vp, vp, vp]
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
+    L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -178,6 +179,14 @@ class Context:
         rp = C.POINTER(_abi.Result)()
         _check(self.L.m2k_detect(self.h, tree, C.byref(p), C.byref(rp)), self.h)
         return rp
+
+    def pack_detect(self, root: bytes, flavor=_abi.SH_BASH, pre=(), skip_content=False):
+        """(tree without bytes, result): pack and detect in one call, bytes streamed from the files."""
+        p, keep = make_params(flavor, pre, skip_content)
+        tp = C.POINTER(_abi.Tree)()
+        rp = C.POINTER(_abi.Result)()
+        _check(self.L.m2k_pack_detect(self.h, root, C.byref(p), C.byref(tp), C.byref(rp)), self.h)
+        return tp, rp
 
     def result_free(self, res):
         self.L.m2k_result_free(res)

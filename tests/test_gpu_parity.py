@@ -460,3 +460,57 @@ def test_pageable_tree_goes_through_the_staging_blocks(ctx, oracle):
             ctx.result_free(res)
     finally:
         lib.tree_free_host(tree)
+
+
+@pytest.mark.parametrize("name", ["samples", "nasty", "multiignores", "ignorecontents", "emptydir", "random007", "random019"])
+def test_pack_detect_streams_the_same_answer(ctx, tmp_path, name):
+    """m2k_pack_detect (bytes streamed from the files through the pinned blocks, never gathered on the
+    host) against m2k_pack_tree + m2k_detect on the same directory: every array."""
+    spec = next(g for g in GOLDENS if g["name"] == name)
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / name)))
+    tree = ctx.pack_tree(root)
+    want = ctx.detect(tree)
+    for skip in (False, True):
+        if skip:
+            ctx.result_free(want)
+            want = ctx.detect(tree, skip_content=True)
+        t2, got = ctx.pack_detect(root, skip_content=skip)
+        assert not t2.contents.bytes
+        assert _meta(t2) == _meta(tree)
+        assert_same_result(tree, got, want)
+        g, w = got.contents, want.contents
+        assert [g.ignore_dirs[i] for i in range(g.n_ignore_dirs)] == [w.ignore_dirs[i] for i in range(w.n_ignore_dirs)]
+        assert [g.ignore_contents[i] for i in range(g.n_ignore_contents)] == [w.ignore_contents[i] for i in range(w.n_ignore_contents)]
+        ctx.result_free(got)
+        ctx.tree_free(t2)
+    ctx.result_free(want)
+    ctx.tree_free(tree)
+
+
+def _meta(tp):
+    t = tp.contents
+    return (t.n_dirs, t.n_entries, t.n_files, t.dir_parent[0:t.n_dirs], t.entry_dir[0:t.n_entries], t.entry_type[0:t.n_entries],
+            bytes(bytearray(t.names[0:t.n_name_bytes])), t.file_len[0:t.n_files] if t.n_files else [])
+
+
+def test_pack_detect_on_a_large_materialised_tree(ctx, oracle, tmp_path):
+    """Enough bytes for the two pinned blocks to wrap around several times (150 MB), one file larger
+    than a block: the streamed pass equals the oracle's answer on the generator's tree."""
+    from move2kube_b200 import synthfs
+    p = synth_params(29, 3000, 200, 150 << 20, n_huge=1, huge_bytes=70 << 20)
+    src = lib.synth_tree_host(p, host_bytes=True)
+    root = os.fsencode(str(tmp_path / "tree"))
+    try:
+        synthfs.materialize(src, root)
+        ores = oracle.detect(src)
+        t2, got = ctx.pack_detect(root)
+        o, g = ores.contents, got.contents
+        nd, nf = src.contents.n_dirs, src.contents.n_files
+        assert g.file_flags[0:nf] == o.file_flags[0:nf]
+        assert g.dir_opts[0:nd] == o.dir_opts[0:nd] and g.dir_state[0:nd] == o.dir_state[0:nd]
+        assert g.dir_main_file[0:nd] == o.dir_main_file[0:nd]
+        oracle.lib().m2ko_result_free(ores)
+        ctx.result_free(got)
+        ctx.tree_free(t2)
+    finally:
+        lib.tree_free_host(src)
