@@ -476,7 +476,8 @@ def test_pack_detect_streams_the_same_answer(ctx, tmp_path, name):
             want = ctx.detect(tree, skip_content=True)
         t2, got = ctx.pack_detect(root, skip_content=skip)
         assert not t2.contents.bytes
-        assert _meta(t2) == _meta(tree)
+        # (names only: the streamed tree then carries no sizes except for the rule files)
+        assert _meta(t2)[:7] == _meta(tree)[:7] and (skip or _meta(t2) == _meta(tree))
         assert_same_result(tree, got, want)
         g, w = got.contents, want.contents
         assert [g.ignore_dirs[i] for i in range(g.n_ignore_dirs)] == [w.ignore_dirs[i] for i in range(w.n_ignore_dirs)]
