@@ -48,16 +48,11 @@ class Detection:
         self.broot = os.fsencode(root)
         self.ctx = context()
         self.flavor = sh_flavor() if flavor is None else flavor
-        # one-shot use: pack into ordinary memory (page-locking the whole tree would cost more than
-        # reading it); m2k_upload streams it to the device through the context's pinned staging blocks
-        self.tree = lib.pack_tree_host(self.broot, read_content=not skip_content)
+        # one-shot use: m2k_pack_detect walks the tree once and streams the file bytes from the files to the
+        # device through the context's pinned blocks -- they are never gathered on the host
+        self.tree = None
         self.res = None
-        try:
-            self.res = self.ctx.detect(self.tree, self.flavor, [os.fsencode(p) for p in pre], skip_content)
-        except Exception:
-            lib.tree_free_host(self.tree)
-            self.tree = None
-            raise
+        self.tree, self.res = self.ctx.pack_detect(self.broot, self.flavor, [os.fsencode(p) for p in pre], skip_content)
         t, r = self.tree.contents, self.res.contents
         self.n_dirs, self.n_entries, self.n_files = t.n_dirs, t.n_entries, t.n_files
         names = bytes(bytearray(t.names[0:t.n_name_bytes])) if t.n_name_bytes else b""
@@ -102,7 +97,7 @@ class Detection:
             self.ctx.result_free(self.res)
             self.res = None
         if self.tree is not None:
-            lib.tree_free_host(self.tree)
+            self.ctx.tree_free(self.tree)
             self.tree = None
 
     # -- look-ups
