@@ -813,6 +813,8 @@ class HostTeam {
   void run(unsigned nt, const std::function<void(unsigned)>& fn) {
     if (nt <= 1) { fn(0); return; }
     if (nt > workers_ + 1) nt = workers_ + 1;
+    // one job at a time: contexts driven from different host threads share this team
+    std::lock_guard<std::mutex> one(run_m_);
     {
       std::lock_guard<std::mutex> lk(m_);
       job_ = &fn; active_ = nt - 1; remaining_ = nt - 1; gen_++;
@@ -848,7 +850,7 @@ class HostTeam {
       if (--remaining_ == 0) done_.notify_one();
     }
   }
-  std::mutex m_;
+  std::mutex m_, run_m_;
   std::condition_variable cv_, done_;
   const std::function<void(unsigned)>* job_ = nullptr;
   unsigned workers_ = 0, active_ = 0, remaining_ = 0;

@@ -294,3 +294,28 @@ def test_packer_reproduces_a_materialised_generator_tree(tmp_path):
             lib.tree_free_host(got)
     finally:
         lib.tree_free_host(src)
+
+
+def test_host_thread_team_is_shared_safely_between_caller_threads():
+    """Contexts driven from different host threads share one team of worker threads: two callers at
+    once (ctypes drops the GIL during the call) must both get complete, identical answers."""
+    import threading
+    tp = lib.synth_tree_host(small_synth(seed=23, n_files=30000, n_dirs=3000, total=1 << 20), host_bytes=False)
+    try:
+        L = lib.load()
+        out = {}
+
+        def work(k):
+            ms = (C.c_double * 6)()
+            nf, nr = C.c_uint32(), C.c_uint32()
+            rc = L.m2k_host_prepare_probe(tp, None, 20, ms, C.byref(nf), C.byref(nr))
+            out[k] = (rc, nf.value, nr.value)
+
+        th = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        assert len(out) == 4 and len(set(out.values())) == 1 and out[0][0] == 0 and out[0][2] > 0
+    finally:
+        lib.tree_free_host(tp)
