@@ -300,7 +300,8 @@ def test_host_thread_team_is_shared_safely_between_caller_threads():
     """Contexts driven from different host threads share one team of worker threads: two callers at
     once (ctypes drops the GIL during the call) must both get complete, identical answers."""
     import threading
-    tp = lib.synth_tree_host(small_synth(seed=23, n_files=30000, n_dirs=3000, total=1 << 20), host_bytes=False)
+    p = _abi.SynthParams(seed=23, n_files=30000, n_dirs=3000, max_depth=6, n_ignore_files=800, total_bytes=1 << 20)
+    tp = lib.synth_tree_host(p, host_bytes=False)
     try:
         L = lib.load()
         out = {}
@@ -316,6 +317,6 @@ def test_host_thread_team_is_shared_safely_between_caller_threads():
             x.start()
         for x in th:
             x.join()
-        assert len(out) == 4 and len(set(out.values())) == 1 and out[0][0] == 0 and out[0][2] > 0
+        assert len(out) == 4 and len(set(out.values())) == 1 and out[0][0] == 0 and out[0][2] > 4000
     finally:
         lib.tree_free_host(tp)
