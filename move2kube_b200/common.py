@@ -1,6 +1,7 @@
 """Mirror of the three internal/common helpers on the path (reference: internal/common/utils.go:47-82,
 85-120, 308-315), answered from the packed tree instead of one more filesystem walk each."""
 import os
+import stat
 
 from . import _abi, detection, lib
 
@@ -15,11 +16,19 @@ def IsStringPresent(lst, value: str) -> bool:
     return any(lib.equal_fold(os.fsencode(x), v) for x in lst)
 
 
+def _root_is_not_a_directory(inputPath: str) -> bool:
+    """filepath.Walk Lstats the root: anything but a real directory (a file, a symlink -- even one to
+    a directory) is reported once, as itself, and nothing below it is looked at (utils_test.go:41-50, 98-107)."""
+    return not stat.S_ISDIR(os.lstat(inputPath).st_mode)
+
+
 def GetFilesByName(inputPath: str, names):
     """utils.go:85-120.  Returns (files, err): non-directories whose basename equals one of `names`,
     in filepath.Walk order; a missing root is an error."""
     if not os.path.lexists(inputPath):
         return [], FileNotFoundError(inputPath)
+    if _root_is_not_a_directory(inputPath):
+        return ([inputPath] if os.path.basename(inputPath) in names else []), None
     det = detection.detect(inputPath, skip_content=True)
     out = []
     known = [n for n in names if n in _NAME_BITS]
@@ -42,6 +51,10 @@ def GetFilesByExt(inputPath: str, exts):
     """utils.go:47-82.  filepath.Ext of the basename must equal one of `exts`."""
     if not os.path.lexists(inputPath):
         return None, FileNotFoundError(inputPath)
+    if _root_is_not_a_directory(inputPath):
+        base = os.path.basename(inputPath)
+        i = base.rfind(".")  # filepath.Ext: from the last dot of the base name, a leading dot included
+        return ([inputPath] if i >= 0 and base[i:] in exts else []), None
     det = detection.detect(inputPath, skip_content=True)
     if sorted(exts) == [".yaml", ".yml"]:
         return [os.fsdecode(det.entry_path(e)) for e in det.entries_with(_abi.N_YAML)], None
