@@ -34,9 +34,13 @@ func (t *Any2KubeGPUTranslator) GetServiceOptions(inputPath string, plan plantyp
 			}
 		}
 	}
-	if _, err := os.Lstat(inputPath); err != nil {
+	if info, err := os.Lstat(inputPath); err != nil {
 		// filepath.Walk would hand this error to the callback, which warns and returns nil (any2kube_test.go:38-53)
 		log.Warnf("Skipping path %q due to error. Error: %q", inputPath, err)
+		return services, nil
+	} else if !info.IsDir() {
+		// filepath.Walk Lstats its root: a file, or a symlink even to a directory, is visited alone and
+		// `!info.IsDir()` returns nil (any2kube.go:63-65)
 		return services, nil
 	}
 	res, err := m2kdetect.Detect(inputPath, preContainerizedSourcePaths, os.Getenv("M2K_SH") == "dash")

@@ -88,8 +88,11 @@ type Result struct {
 	KernelMillis float32
 }
 
-// Detect packs rootPath (one walk, pinned host buffers owned by C) and runs the whole path on the GPU.
-// A GPU failure is returned as an error: there is no CPU fallback.
+// Detect walks rootPath once and runs the whole path on the GPU.  It uses m2k_pack_detect: the file bytes
+// are streamed from the files through the context's pinned blocks and never gathered on the host (the
+// measured fastest road for a tree that is looked at once; page-locking a whole-tree buffer costs more
+// than reading the files).  A GPU failure is returned as an error: there is no CPU fallback.
+// A root that Lstat says is not a directory returns ErrNotDir (filepath.Walk visits it alone).
 func Detect(rootPath string, preContainerized []string, dashSh bool) (*Result, error) {
 	mu.Lock()
 	defer mu.Unlock()
@@ -101,44 +104,91 @@ func Detect(rootPath string, preContainerized []string, dashSh bool) (*Result, e
 	}
 	croot := C.CString(rootPath)
 	defer C.free(unsafe.Pointer(croot))
-	var tree *C.m2k_tree
-	if rc := C.m2k_pack_tree(c, croot, 1, &tree); rc != C.M2K_OK {
-		return nil, fmt.Errorf("m2kdetect: pack %q: %s", rootPath, C.GoString(C.m2k_last_error(c)))
-	}
-	defer C.m2k_tree_free(c, tree)
 
 	var params C.m2k_detect_params
 	if dashSh {
 		params.sh_flavor = C.M2K_SH_DASH
 	}
-	// pre paths live in C memory for the duration of the call: never hand Go-GC memory to async copies
-	cpre := make([]*C.char, len(preContainerized)+1)
-	for i, p := range preContainerized {
-		cpre[i] = C.CString(p)
-		defer C.free(unsafe.Pointer(cpre[i]))
-	}
-	carr := (**C.char)(C.malloc(C.size_t(len(cpre)) * C.size_t(unsafe.Sizeof(uintptr(0)))))
+	// pre paths live in C memory for the duration of the call: never hand Go-GC memory to C code that keeps it
+	n := len(preContainerized)
+	carr := (**C.char)(C.malloc(C.size_t(n+1) * C.size_t(unsafe.Sizeof(uintptr(0)))))
 	defer C.free(unsafe.Pointer(carr))
-	copy(unsafe.Slice(carr, len(cpre)), cpre)
-	params.n_pre = C.uint32_t(len(preContainerized))
+	cslots := (*[1 << 28]*C.char)(unsafe.Pointer(carr))[: n+1 : n+1] // Go 1.15: no unsafe.Slice
+	for i, p := range preContainerized {
+		cslots[i] = C.CString(p)
+		defer C.free(unsafe.Pointer(cslots[i]))
+	}
+	cslots[n] = nil
+	params.n_pre = C.uint32_t(n)
 	params.pre_paths = carr
 
+	var tree *C.m2k_tree
 	var res *C.m2k_result
-	if rc := C.m2k_detect(c, tree, &params, &res); rc != C.M2K_OK {
+	if rc := C.m2k_pack_detect(c, croot, &params, &tree, &res); rc != C.M2K_OK {
+		if rc == C.M2K_ERR_NOTDIR {
+			return nil, ErrNotDir
+		}
 		return nil, fmt.Errorf("m2kdetect: detect %q: %s", rootPath, C.GoString(C.m2k_last_error(c)))
 	}
+	defer C.m2k_tree_free(c, tree)
 	defer C.m2k_result_free(res)
 	return copyOut(tree, res), nil
+}
+
+// ErrNotDir: the root exists but is not a directory for Lstat (a file, or a symlink even to a directory).
+var ErrNotDir = fmt.Errorf("m2kdetect: root is not a directory")
+
+// IsDockerFile is isDockerFile (dockerfile2kube.go:117-144) for one file's bytes, through the same kernels:
+// what getDockerfileServices needs when its root is not a directory.
+func IsDockerFile(data []byte) (bool, error) {
+	mu.Lock()
+	defer mu.Unlock()
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	c, err := context()
+	if err != nil {
+		return false, err
+	}
+	var cdata unsafe.Pointer
+	if len(data) > 0 {
+		cdata = C.CBytes(data)
+		defer C.free(cdata)
+	}
+	var flags C.uint32_t
+	if rc := C.m2k_is_dockerfile(c, (*C.uint8_t)(cdata), C.uint64_t(len(data)), &flags); rc != C.M2K_OK {
+		return false, fmt.Errorf("m2kdetect: %s", C.GoString(C.m2k_last_error(c)))
+	}
+	return flags&C.M2K_FILE_DOCKERFILE != 0, nil
+}
+
+// Go 1.15-compatible views of C arrays (the reference's go.mod says go 1.15; unsafe.Slice is 1.17)
+func u32s(p *C.uint32_t, n int) []uint32 {
+	if n == 0 || p == nil {
+		return nil
+	}
+	return (*[1 << 28]uint32)(unsafe.Pointer(p))[:n:n]
+}
+func u8s(p *C.uint8_t, n int) []uint8 {
+	if n == 0 || p == nil {
+		return nil
+	}
+	return (*[1 << 30]uint8)(unsafe.Pointer(p))[:n:n]
+}
+func strs(p **C.char, n int) []*C.char {
+	if n == 0 || p == nil {
+		return nil
+	}
+	return (*[1 << 28]*C.char)(unsafe.Pointer(p))[:n:n]
 }
 
 func copyOut(t *C.m2k_tree, r *C.m2k_result) *Result {
 	nd, ne, nf := int(t.n_dirs), int(t.n_entries), int(t.n_files)
 	out := &Result{}
-	names := unsafe.Slice((*byte)(unsafe.Pointer(t.names)), int(t.n_name_bytes))
-	nameOff := unsafe.Slice((*uint32)(unsafe.Pointer(t.entry_name_off)), ne+1)
-	entryDir := unsafe.Slice((*uint32)(unsafe.Pointer(t.entry_dir)), ne)
-	dirEntry := unsafe.Slice((*uint32)(unsafe.Pointer(t.dir_entry)), nd)
-	dirParent := unsafe.Slice((*uint32)(unsafe.Pointer(t.dir_parent)), nd)
+	names := u8s(t.names, int(t.n_name_bytes))
+	nameOff := u32s(t.entry_name_off, ne+1)
+	entryDir := u32s(t.entry_dir, ne)
+	dirEntry := u32s(t.dir_entry, nd)
+	dirParent := u32s(t.dir_parent, nd)
 	root := C.GoString(t.root_path)
 	out.DirPath = make([]string, nd)
 	for d := 0; d < nd; d++ {
@@ -153,23 +203,23 @@ func copyOut(t *C.m2k_tree, r *C.m2k_result) *Result {
 	for e := 0; e < ne; e++ {
 		out.EntryPath[e] = joinPath(out.DirPath[entryDir[e]], string(names[nameOff[e]:nameOff[e+1]]))
 	}
-	out.DirOpts = append([]uint32(nil), unsafe.Slice((*uint32)(unsafe.Pointer(r.dir_opts)), nd)...)
-	out.DirState = append([]uint8(nil), unsafe.Slice((*uint8)(unsafe.Pointer(r.dir_state)), nd)...)
-	out.DirIgnore = append([]uint8(nil), unsafe.Slice((*uint8)(unsafe.Pointer(r.dir_ignore)), nd)...)
-	out.DirEnd = append([]uint32(nil), unsafe.Slice((*uint32)(unsafe.Pointer(t.dir_end)), nd)...)
-	out.DirMainFile = append([]uint32(nil), unsafe.Slice((*uint32)(unsafe.Pointer(r.dir_main_file)), nd)...)
-	out.ServiceDirs = append([]uint32(nil), unsafe.Slice((*uint32)(unsafe.Pointer(r.service_dirs)), int(r.n_services))...)
-	out.FileFlags = append([]uint8(nil), unsafe.Slice((*uint8)(unsafe.Pointer(r.file_flags)), nf)...)
-	out.EntryFeat = append([]uint32(nil), unsafe.Slice((*uint32)(unsafe.Pointer(r.entry_feat)), ne)...)
-	fileEntry := unsafe.Slice((*uint32)(unsafe.Pointer(t.file_entry)), nf)
+	out.DirOpts = append([]uint32(nil), u32s(r.dir_opts, nd)...)
+	out.DirState = append([]uint8(nil), u8s(r.dir_state, nd)...)
+	out.DirIgnore = append([]uint8(nil), u8s(r.dir_ignore, nd)...)
+	out.DirEnd = append([]uint32(nil), u32s(t.dir_end, nd)...)
+	out.DirMainFile = append([]uint32(nil), u32s(r.dir_main_file, nd)...)
+	out.ServiceDirs = append([]uint32(nil), u32s(r.service_dirs, int(r.n_services))...)
+	out.FileFlags = append([]uint8(nil), u8s(r.file_flags, nf)...)
+	out.EntryFeat = append([]uint32(nil), u32s(r.entry_feat, ne)...)
+	fileEntry := u32s(t.file_entry, nf)
 	out.FilePath = make([]string, nf)
 	for f := 0; f < nf; f++ {
 		out.FilePath[f] = out.EntryPath[fileEntry[f]]
 	}
-	for _, p := range unsafe.Slice(r.ignore_dirs, int(r.n_ignore_dirs)) {
+	for _, p := range strs(r.ignore_dirs, int(r.n_ignore_dirs)) {
 		out.IgnoreDirs = append(out.IgnoreDirs, C.GoString(p))
 	}
-	for _, p := range unsafe.Slice(r.ignore_contents, int(r.n_ignore_contents)) {
+	for _, p := range strs(r.ignore_contents, int(r.n_ignore_contents)) {
 		out.IgnoreConts = append(out.IgnoreConts, C.GoString(p))
 	}
 	out.KernelMillis = float32(r.ms_kernels)

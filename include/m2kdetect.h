@@ -46,7 +46,11 @@ typedef enum m2k_status {
   M2K_ERR_NOMEM = -4,
   M2K_ERR_UNSUPPORTED = -5, /* input the packed representation cannot express exactly
                                (e.g. a file name containing a newline) */
-  M2K_ERR_LIMIT = -6        /* a stated size limit was exceeded */
+  M2K_ERR_LIMIT = -6,       /* a stated size limit was exceeded */
+  M2K_ERR_NOTDIR = -7       /* the root exists but Lstat says it is not a directory (a file, or a symlink even
+                               to a directory): filepath.Walk visits it alone -- no services (any2kube.go:63-65),
+                               and getDockerfileServices asks isDockerFile about the root itself
+                               (dockerfile2kube.go:154-167; see m2k_is_dockerfile) */
 } m2k_status;
 
 /* ---- entry types: low nibble = lstat type, high nibble = type after following symlinks ---- */
@@ -224,6 +228,11 @@ void m2k_result_free(m2k_result* r);
  * it with m2k_tree_free(ctx, tree) after m2k_result_free. -- */
 int m2k_pack_detect(m2k_ctx* ctx, const char* root_path, const m2k_detect_params* params, m2k_tree** tree_out, m2k_result** out);
 
+/* -- isDockerFile (dockerfile2kube.go:117-144) for one file the caller has read, through the same kernels:
+ * what getDockerfileServices needs when its root is not a directory (M2K_ERR_NOTDIR).  *file_flags gets the
+ * M2K_FILE_* bits; M2K_FILE_DOCKERFILE is isDockerFile's answer. -- */
+int m2k_is_dockerfile(m2k_ctx* ctx, const uint8_t* data, uint64_t len, uint32_t* file_flags);
+
 /* -- staged form (bench, multi-GPU): a shard = file ids [file_begin, file_end) -- */
 int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out);
 /* -- a shard as a range of 64 KiB chunks, so that one multi-GB file can be spread over several GPUs
@@ -304,9 +313,11 @@ void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
  *   d_bytes        file contents; each file starts at a multiple of 16, is zero padded to 16 bytes,
  *                  and at least 16 zero bytes follow the last file
  *   d_file_off/len [n_files] offset into d_bytes / length in bytes
- *   d_chunk_first  [n_files+1] exclusive prefix sum of ceil(len / 65536); n_chunks = d_chunk_first[n_files]
+ *   d_chunk_first  [n_files+1] exclusive prefix sum of ceil(len / 65536); n_chunks MUST equal
+ *                  d_chunk_first[n_files] (the host cannot read it; a prefix that runs past n_chunks is cut off there)
  *   d_file_flags   [n_files] out: M2K_FILE_HAS_MAIN | M2K_FILE_LONG_LINE
- * Work is queued on `stream` (a cudaStream_t, NULL = default stream) and not waited for.  The first
+ * Work is queued on `stream` (a cudaStream_t, NULL = default stream) and not waited for; the caller's
+ * current device is the same after the call as before it.  The first
  * call on a device looks up the table's device address: make it before any stream capture.  Calls
  * share the table; run them one after the other (overlapping calls race on it).  Nothing in the
  * table needs clearing between calls: each call writes every record it later reads.

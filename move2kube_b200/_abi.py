@@ -3,7 +3,7 @@ import ctypes as C
 
 NONE = 0xFFFFFFFF
 
-OK, ERR_ARG, ERR_CUDA, ERR_IO, ERR_NOMEM, ERR_UNSUPPORTED, ERR_LIMIT = 0, -1, -2, -3, -4, -5, -6
+OK, ERR_ARG, ERR_CUDA, ERR_IO, ERR_NOMEM, ERR_UNSUPPORTED, ERR_LIMIT, ERR_NOTDIR = 0, -1, -2, -3, -4, -5, -6, -7
 
 T_ERR, T_REG, T_DIR, T_LNK, T_OTHER = 0, 1, 2, 3, 4
 SH_BASH, SH_DASH = 0, 1

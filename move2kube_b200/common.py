@@ -30,11 +30,18 @@ def GetFilesByName(inputPath: str, names):
     if _root_is_not_a_directory(inputPath):
         return ([inputPath] if os.path.basename(inputPath) in names else []), None
     det = detection.detect(inputPath, skip_content=True)
+    try:
+        return _files_by_name(det, names), None
+    finally:
+        det.close()
+
+
+def _files_by_name(det, names):
     out = []
     known = [n for n in names if n in _NAME_BITS]
     other = [os.fsencode(n) for n in names if n not in _NAME_BITS]
     if known and not other and len(known) == 1:
-        return [os.fsdecode(det.entry_path(e)) for e in det.entries_with(_NAME_BITS[known[0]])], None
+        return [os.fsdecode(det.entry_path(e)) for e in det.entries_with(_NAME_BITS[known[0]])]
     # general case: any basename -- filter the packed name table (still no filesystem walk)
     t = det.tree.contents
     want = set(os.fsencode(n) for n in names)
@@ -44,7 +51,7 @@ def GetFilesByName(inputPath: str, names):
             feat[e] = 1
     for e in lib.list_entries(det.tree, 0, feat):
         out.append(os.fsdecode(det.entry_path(e)))
-    return out, None
+    return out
 
 
 def GetFilesByExt(inputPath: str, exts):
@@ -56,8 +63,15 @@ def GetFilesByExt(inputPath: str, exts):
         i = base.rfind(".")  # filepath.Ext: from the last dot of the base name, a leading dot included
         return ([inputPath] if i >= 0 and base[i:] in exts else []), None
     det = detection.detect(inputPath, skip_content=True)
+    try:
+        return _files_by_ext(det, exts), None
+    finally:
+        det.close()
+
+
+def _files_by_ext(det, exts):
     if sorted(exts) == [".yaml", ".yml"]:
-        return [os.fsdecode(det.entry_path(e)) for e in det.entries_with(_abi.N_YAML)], None
+        return [os.fsdecode(det.entry_path(e)) for e in det.entries_with(_abi.N_YAML)]
     t = det.tree.contents
     feat = (lib.C.c_uint32 * max(1, det.n_entries))()
     bexts = [os.fsencode(x) for x in exts]
@@ -69,4 +83,4 @@ def GetFilesByExt(inputPath: str, exts):
         ext = nm[i:] if i >= 0 else b""
         if ext in bexts:
             feat[e] = 1
-    return [os.fsdecode(det.entry_path(e)) for e in lib.list_entries(det.tree, 0, feat)], None
+    return [os.fsdecode(det.entry_path(e)) for e in lib.list_entries(det.tree, 0, feat)]

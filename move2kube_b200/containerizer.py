@@ -169,11 +169,25 @@ class Containerizers:
     def __init__(self):
         self.containerizers = []
         self.det = None
+        self._own_det = False
+
+    def close(self):
+        if self._own_det and self.det is not None:
+            self.det.close()
+        self.det = None
+        self._own_det = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def InitContainerizers(self, path: str, det: "detection.Detection" = None):
         """containerizer.go:56-62: Init(path) then Init(AssetsPath) for each of the four containerizers."""
-        if det is None and os.path.isdir(path):
-            det = detection.detect(path)
+        if det is None and os.path.isdir(path) and not os.path.islink(path):
+            det = detection.detect(path)  # owned by this object: released by close() / when it is collected
+            self._own_det = True
         self.det = det
         self.containerizers = [DockerfileContainerizer(), S2IContainerizer(), CNBContainerizer(), ReuseContainerizer()]
         for c in self.containerizers:

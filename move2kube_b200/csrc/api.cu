@@ -1325,6 +1325,30 @@ extern "C" int m2k_pack_detect(m2k_ctx* ctx, const char* root_path, const m2k_de
   return M2K_OK;
 }
 
+// isDockerFile (dockerfile2kube.go:117-144) for ONE file the caller has read: what
+// getDockerfileServices does when filepath.Walk hands it a root that is not a directory.  The bytes
+// become a one-file tree and take the same kernels as every other file.
+extern "C" int m2k_is_dockerfile(m2k_ctx* ctx, const uint8_t* data, uint64_t len, uint32_t* file_flags) {
+  if (!ctx || (!data && len) || !file_flags) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_is_dockerfile: NULL argument");
+  *file_flags = 0;
+  const uint64_t padded = (len + 15) & ~15ull;
+  m2k_tree* t = tree_alloc(1, 1, 1, 1, padded + 16, true, false, ".");
+  if (!t) return fail(&ctx->c, M2K_ERR_NOMEM, "out of host memory");
+  t->dir_parent[0] = M2K_NONE; t->dir_end[0] = 1; t->dir_entry[0] = M2K_NONE;
+  t->dir_first_entry[0] = 0; t->dir_first_entry[1] = 1;
+  t->entry_dir[0] = 0; t->entry_name_off[0] = 0; t->entry_name_off[1] = 1;
+  t->entry_type[0] = M2K_T_REG | (M2K_T_REG << 4); t->entry_child[0] = 0; t->names[0] = 'f';
+  t->file_entry[0] = 0; t->file_off[0] = 0; t->file_len[0] = len;
+  t->content_bytes = len;
+  memset(t->bytes, 0, padded + 16);
+  if (len) memcpy(t->bytes, data, len);
+  m2k_result* r = nullptr;
+  int rc = m2k_detect(ctx, t, nullptr, &r);
+  if (rc == M2K_OK) { *file_flags = r->file_flags[0]; m2k_result_free(r); }
+  tree_release(t);
+  return rc;
+}
+
 // ---- host helpers exported for the mirror ----------------------------------------------------
 extern "C" int m2k_path_clean(const char* path, char* outbuf, size_t cap) {
   if (!path || !outbuf || !cap) return M2K_ERR_ARG;

@@ -41,14 +41,18 @@ static int g_sm_count[kMaxDevices];
 // Per-file flags from the chunk records: one thread per file walks its records in order and keeps
 // the bytes since the last newline; the records are exact to the byte, so the file itself is not
 // looked at again.  Device code may name the array directly.
-__global__ void __launch_bounds__(128) k_noalloc_file_flags(uint32_t n_files, const uint32_t* __restrict__ chunk_first,
+// `n_chunks` is what the host checked against the table and what the scan wrote: a prefix array that
+// runs past it (it must not: n_chunks == chunk_first[n_files]) is cut off there, so this kernel never
+// reads a record this call did not write, nor past the table.
+__global__ void __launch_bounds__(128) k_noalloc_file_flags(uint32_t n_files, uint32_t n_chunks, const uint32_t* __restrict__ chunk_first,
                                                              const uint64_t* __restrict__ file_len, uint8_t* __restrict__ file_flags) {
   uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= n_files) return;
   const uint64_t len = file_len[f];
   uint32_t has_main = 0, is_long = 0;
   uint64_t run = 0;  // bytes since the last newline (or since the start of the file)
-  for (uint32_t c = chunk_first[f], k = 0; c < chunk_first[f + 1]; c++, k++) {
+  const uint32_t c_end = chunk_first[f + 1] < n_chunks ? chunk_first[f + 1] : n_chunks;
+  for (uint32_t c = chunk_first[f], k = 0; c < c_end; c++, k++) {
     const ChunkRec rec = g_noalloc_records[c];
     const uint64_t b0 = (uint64_t)k * kChunkBytes;
     const uint64_t nb = len - b0 < kChunkBytes ? len - b0 : kChunkBytes;
@@ -85,8 +89,19 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
     return noalloc_fail(M2K_ERR_LIMIT,
                         "m2k_scan_flags_noalloc: %u chunks of 64 KiB exceed the built-in record table (%u chunks, 16 GiB of "
                         "content): split the input or use m2k_scan", n_chunks, kNoAllocMaxChunks);
-  cudaError_t e = cudaSetDevice(device);
-  if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  // the caller is in the middle of its own CUDA work: its current device is put back on every way out
+  struct DeviceGuard {
+    int prev = -1;
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  } guard;
+  int cur = -1;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (cur != device) {
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    guard.prev = cur;
+  }
   {
     // set-up, once per device, with that device current
     std::lock_guard<std::mutex> lock(g_setup_mutex);
@@ -120,7 +135,7 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
   t.bytes = const_cast<uint8_t*>(d_bytes);
   t.shard_byte0 = 0;
   launch_scan_bytes(&c, &t, g_records_ptr[device]);
-  k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, d_chunk_first, d_file_len, d_file_flags);
+  k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, n_chunks, d_chunk_first, d_file_len, d_file_flags);
   e = cudaGetLastError();
   if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: kernel launch: %s", cudaGetErrorString(e));
   return M2K_OK;

@@ -260,10 +260,17 @@ PackPlan::~PackPlan() { delete p; }
 
 int pack_plan(const char* root_path, int read_content, bool pinned, bool with_bytes, PackPlan* plan, m2k_tree** out, std::string* err) {
   *out = nullptr;
+  // filepath.Walk Lstats its root: a root that is not a real directory (a file, a symlink -- even one
+  // to a directory) is handed to the callback once, as itself, and nothing below it is looked at
+  // (any2kube.go:58-65, utils.go:93-101).  Such a root has no packed form; the caller answers for it.
   struct stat st;
-  if (stat(root_path, &st) != 0) {
+  if (lstat(root_path, &st) != 0) {
     *err = std::string("cannot stat root ") + root_path + ": " + strerror(errno);
     return M2K_ERR_IO;
+  }
+  if (!S_ISDIR(st.st_mode)) {
+    *err = std::string("root ") + root_path + " is not a directory (filepath.Walk visits it alone, as a non-directory)";
+    return M2K_ERR_NOTDIR;
   }
   PackPlan::Impl& P = *plan->p;
   unsigned nt = std::thread::hardware_concurrency();

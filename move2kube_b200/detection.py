@@ -124,8 +124,19 @@ class Detection:
         return lib.list_entries(self.tree, feature_bit, self.res.contents.entry_feat)
 
     def dockerfiles(self):
-        """Paths isDockerFile() accepts, in Walk order of file ids (dockerfile2kube.go:154-167)."""
-        return [self.file_path(f) for f in range(self.n_files) if self.file_flags[f] & _abi.FILE_DOCKERFILE]
+        """Paths isDockerFile() accepts, in filepath.Walk order (dockerfile2kube.go:154-167).  File ids
+        are numbered by (directory id, name), which is not Walk order when a file's name sorts after a
+        sub-directory of the same directory: the entries go through the same ordering as
+        GetFilesByName / GetFilesByExt."""
+        feat = (lib.C.c_uint32 * max(1, self.n_entries))()
+        any_set = False
+        for f in range(self.n_files):
+            if self.file_flags[f] & _abi.FILE_DOCKERFILE:
+                feat[self.file_entry[f]] = 1
+                any_set = True
+        if not any_set:
+            return []
+        return [self.entry_path(e) for e in lib.list_entries(self.tree, 0, feat)]
 
     def main_script_rel_path(self, d: int) -> str:
         """What the python detect scripts print as main_script_rel_path / app_file (a11)."""
@@ -135,7 +146,10 @@ class Detection:
         return os.fsdecode(os.path.relpath(self.file_path(f), self.dir_path[d]))
 
 
-def detect(root: str, pre=(), flavor=None, skip_content=False, cache=True) -> Detection:
+def detect(root: str, pre=(), flavor=None, skip_content=False, cache=False) -> Detection:
+    """One detection pass.  The reference re-walks the tree on every call, so nothing is cached unless
+    the caller asks for it (cache=True keeps the Detection, and the host memory it holds, until reset();
+    a cached answer goes stale when the tree changes).  Without the cache the caller closes it."""
     key = (root, tuple(pre), sh_flavor() if flavor is None else flavor, skip_content)
     if cache and key in _cache:
         return _cache[key]

@@ -30,7 +30,7 @@ EXPORTS = [
     "m2k_list_entries", "m2k_scan_flags_noalloc", "m2k_host_prepare_probe",
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
-    "m2k_export_async", "m2k_import_async", "m2k_pack_detect",
+    "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
 ]
 
 
@@ -101,6 +101,7 @@ def load():
     L.m2k_export_async.argtypes = [vp, vp, vp, vp, vp, vp]
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
+    L.m2k_is_dockerfile.argtypes = [vp, C.c_char_p, C.c_uint64, _abi.u32p]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -190,6 +191,12 @@ class Context:
 
     def result_free(self, res):
         self.L.m2k_result_free(res)
+
+    def is_dockerfile(self, data: bytes) -> bool:
+        """isDockerFile (dockerfile2kube.go:117-144) for one file's bytes, through the same kernels."""
+        flags = C.c_uint32()
+        _check(self.L.m2k_is_dockerfile(self.h, data, len(data), C.byref(flags)), self.h)
+        return bool(flags.value & _abi.FILE_DOCKERFILE)
 
     # -- staged
     def upload(self, tree, file_begin=0, file_end=None):

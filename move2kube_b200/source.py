@@ -8,6 +8,7 @@ surface: SURVEY.md section 8b).
 """
 import logging
 import os
+import stat
 
 from . import _abi, containerizer, detection, lib, plan as plantypes
 
@@ -31,8 +32,13 @@ class Any2KubeTranslator:
     def getIgnorePaths(self, inputPath: str, det: "detection.Detection" = None):
         """any2kube.go:151-181 -- answered from the detection pass (the .m2kignore files were found by
         the name-feature kernel and parsed once)."""
-        det = det or detection.detect(inputPath)
-        return ([os.fsdecode(p) for p in det.ignore_dirs], [os.fsdecode(p) for p in det.ignore_contents])
+        own = det is None
+        det = det or detection.detect(inputPath, skip_content=True)
+        try:
+            return ([os.fsdecode(p) for p in det.ignore_dirs], [os.fsdecode(p) for p in det.ignore_contents])
+        finally:
+            if own:
+                det.close()
 
     def GetServiceOptions(self, inputPath: str, plan: plantypes.Plan):
         """any2kube.go:43-105.  Returns (services, err)."""
@@ -46,6 +52,10 @@ class Any2KubeTranslator:
         if not os.path.lexists(inputPath):
             # filepath.Walk hands the Lstat error to the callback, which warns and returns nil
             log.warning("Skipping path %r due to error. Error: no such file or directory", inputPath)
+            return services, None
+        if not stat.S_ISDIR(os.lstat(inputPath).st_mode):
+            # filepath.Walk Lstats the root: a file, or a symlink (even to a directory), is handed to the
+            # callback once and `!info.IsDir()` returns nil (any2kube.go:63-65) -- no services
             return services, None
         try:
             det = detection.detect(inputPath, pre=preContainerizedSourcePaths, cache=False)
@@ -120,6 +130,25 @@ class DockerfileTranslator:
     Dockerfiles.  Bucketing them into services (:171-263) is host string logic downstream of the path."""
 
     def GetDockerfiles(self, inputPath: str):
+        """getDockerfileServices' walk (dockerfile2kube.go:146-170).  Returns (paths, err)."""
+        try:
+            st = os.stat(inputPath)
+        except FileNotFoundError as e:  # os.Stat + IsNotExist (:147-149)
+            return [], e
+        except OSError:
+            st = None
+        if st is None or not stat.S_ISDIR(os.lstat(inputPath).st_mode):
+            # the Walk visits the root alone, as a non-directory: isDockerFile(root).  os.Open follows a
+            # symlink; reading a directory (a symlink to one) fails, and so does Parse
+            try:
+                with open(inputPath, "rb") as f:
+                    data = f.read()
+            except OSError:
+                return [], None
+            try:
+                return ([inputPath] if detection.context().is_dockerfile(data) else []), None
+            except lib.M2KError as e:
+                return [], e
         det = detection.detect(inputPath, cache=False)
         try:
             return [os.fsdecode(p) for p in det.dockerfiles()], None

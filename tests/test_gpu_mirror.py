@@ -136,9 +136,39 @@ def test_dockerfile_translator_finds_dockerfiles(tmp_path, assets):
     (d / "svc" / "notes.txt").write_text("FROM is just the first word here, twice\n")
     (d / "build.Dockerfile").write_text("ARG V=1\nFROM alpine:$V AS b\n")
     (d / "broken").write_text("FROM alpine\nENV X\n")
+    # filepath.Walk interleaves files and sub-directories by name: a file sorted after "svc" comes after svc's files
+    (d / "zz.Dockerfile").write_text("FROM scratch\n")
     files, err = source.DockerfileTranslator().GetDockerfiles(str(d))
     assert err is None
-    assert [os.path.relpath(f, str(d)) for f in files] == ["build.Dockerfile", "svc/Dockerfile"]
+    assert [os.path.relpath(f, str(d)) for f in files] == ["build.Dockerfile", "svc/Dockerfile", "zz.Dockerfile"]
+
+
+def test_a_root_that_is_not_a_directory(tmp_path, assets):
+    """filepath.Walk Lstats its root: a symlink to a directory, or a file, is visited alone.  Any2Kube
+    returns no services (any2kube.go:63-65); getDockerfileServices asks isDockerFile about the root
+    itself (dockerfile2kube.go:154-167)."""
+    real = tmp_path / "real"
+    real.mkdir()
+    (real / "package.json").write_text("{}")
+    (real / "Dockerfile").write_text("FROM node:14\nCMD [\"node\"]\n")
+    link = tmp_path / "link"
+    os.symlink(str(real), str(link))
+    services, err = source.Any2KubeTranslator().GetServiceOptions(str(real), plantypes.NewPlan())
+    assert err is None and len(services) >= 1
+    services, err = source.Any2KubeTranslator().GetServiceOptions(str(link), plantypes.NewPlan())
+    assert err is None and services == []
+    services, err = source.Any2KubeTranslator().GetServiceOptions(str(real / "package.json"), plantypes.NewPlan())
+    assert err is None and services == []
+    tr = source.DockerfileTranslator()
+    assert tr.GetDockerfiles(str(real)) == ([str(real / "Dockerfile")], None)
+    assert tr.GetDockerfiles(str(link)) == ([], None)                      # reading a directory fails, so does Parse
+    assert tr.GetDockerfiles(str(real / "Dockerfile")) == ([str(real / "Dockerfile")], None)
+    assert tr.GetDockerfiles(str(real / "package.json")) == ([], None)
+    flink = tmp_path / "df-link"
+    os.symlink(str(real / "Dockerfile"), str(flink))
+    assert tr.GetDockerfiles(str(flink)) == ([str(flink)], None)            # os.Open follows the link
+    files, err = tr.GetDockerfiles(str(tmp_path / "nope"))
+    assert files == [] and err is not None
 
 
 @pytest.mark.parametrize("key", ["planfornodejsapp", "servicesfornodejsapp", "servicesfornodejsappwithm2kignorecase1",

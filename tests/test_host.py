@@ -27,6 +27,15 @@ def test_library_exports_every_declared_symbol():
     assert L.m2k_abi_version() == 1
 
 
+def test_header_compiles_as_c(tmp_path):
+    """cgo compiles include/m2kdetect.h as C, not C++: it must be valid C11 on its own."""
+    import subprocess
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "m2kdetect.h"\nint main(void) { m2k_tree t; (void)t; return M2K_ABI_VERSION - 1; }\n')
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-fsyntax-only",
+                           "-I", os.path.join(REPO, "include"), str(src)])
+
+
 def test_no_gpu_means_a_loud_error_not_a_fallback():
     import torch
     if torch.cuda.is_available():
@@ -73,6 +82,14 @@ def test_packer_errors(tmp_path):
     with pytest.raises(lib.M2KError) as ei:
         lib.pack_tree_host(os.fsencode(str(tmp_path / "nope")))
     assert ei.value.code == _abi.ERR_IO
+    # filepath.Walk Lstats its root: a file or a symlink (even to a directory) has no packed form
+    (tmp_path / "real").mkdir()
+    os.symlink(str(tmp_path / "real"), str(tmp_path / "link"))
+    (tmp_path / "file").write_text("x")
+    for name in ("link", "file"):
+        with pytest.raises(lib.M2KError) as ei:
+            lib.pack_tree_host(os.fsencode(str(tmp_path / name)))
+        assert ei.value.code == _abi.ERR_NOTDIR
     d = tmp_path / "nl"
     d.mkdir()
     (d / "a\nb.go").write_text("x")

@@ -5,9 +5,11 @@ only its built-in record table.
 
 The file is named so that pytest collects it last: if it fails, a run that stops at the first
 failure has already run everything else.  It is checked against the existing entry point
-(m2k_detect) on two calls in a row, the second on a smaller and different tree, so records left in
-the shared table by the first call cannot leak into the second answer.  Bit-exact, like every other
-test here.
+(m2k_detect) AND against the CPU oracle's per-file flags on two calls in a row, the second on a
+smaller and different tree, so records left in the shared table by the first call cannot leak into
+the second answer.  Bit-exact, like every other test here.  "Allocates nothing" is checked with the
+driver's own count of free device memory (cudaMemGetInfo), which sees a cudaMalloc made by any
+library -- torch's allocator statistics would not.
 """
 import ctypes as C
 
@@ -40,13 +42,35 @@ def _run_noalloc(torch, L, tree):
     d_first = torch.tensor(first, dtype=torch.int32).cuda()
     d_flags = torch.full((max(nf, 1),), 0xEE, dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
-    before = torch.cuda.memory_allocated()
-    rc = L.m2k_scan_flags_noalloc(0, None, d_bytes.data_ptr(), d_off.data_ptr(), d_len.data_ptr(), d_first.data_ptr(),
+    # the caller's stream, not the default one; the first call on the device (the set-up call) is made by
+    # whichever test reaches this first, outside any measurement
+    stream = torch.cuda.Stream()
+    rc = L.m2k_scan_flags_noalloc(0, stream.cuda_stream, d_bytes.data_ptr(), d_off.data_ptr(), d_len.data_ptr(), d_first.data_ptr(),
                                   nf, first[-1], d_flags.data_ptr())
     assert rc == 0, L.m2k_global_error()
+    stream.synchronize()
+    d_flags.fill_(0xEE)
     torch.cuda.synchronize()
-    assert torch.cuda.memory_allocated() == before
+    free_before = torch.cuda.mem_get_info()[0]
+    dev_before = torch.cuda.current_device()
+    rc = L.m2k_scan_flags_noalloc(0, stream.cuda_stream, d_bytes.data_ptr(), d_off.data_ptr(), d_len.data_ptr(), d_first.data_ptr(),
+                                  nf, first[-1], d_flags.data_ptr())
+    assert rc == 0, L.m2k_global_error()
+    stream.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free_before, "the call changed the device's free memory"
+    assert torch.cuda.current_device() == dev_before
     return d_flags.cpu().tolist()[:nf], first[-1]
+
+
+def _oracle_flags(tree):
+    """HAS_MAIN | LONG_LINE of every file from the CPU oracle (memmem / line lengths over the host bytes)."""
+    import oracle_lib
+    t = tree.contents
+    out = []
+    for f in range(t.n_files):
+        data = C.string_at(C.addressof(t.bytes.contents) + t.file_off[f], t.file_len[f]) if t.file_len[f] else b""
+        out.append(oracle_lib.file_flags(data) & (_abi.FILE_HAS_MAIN | _abi.FILE_LONG_LINE))
+    return out
 
 
 def test_no_alloc_scan_matches_the_allocating_path_twice_in_a_row():
@@ -61,6 +85,7 @@ def test_no_alloc_scan_matches_the_allocating_path_twice_in_a_row():
             want = [x & (_abi.FILE_HAS_MAIN | _abi.FILE_LONG_LINE) for x in res.contents.file_flags[0:res.contents.n_files]]
             got, n_chunks = _run_noalloc(torch, L, tree)
             assert got == want
+            assert got == _oracle_flags(tree)
             assert any(x & _abi.FILE_HAS_MAIN for x in want)
             if seed == 21:
                 assert n_chunks > n_files and any(x & _abi.FILE_LONG_LINE for x in want)
