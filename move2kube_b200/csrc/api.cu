@@ -299,12 +299,13 @@ extern "C" void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree) {
 
 // ---- device trees ---------------------------------------------------------------------------
 static void devtree_release(DevTree* t) {
-  void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->level_dirs, t->dir_flags, t->entry_dir, t->entry_name_off,
+  // (dir_direct, dir_content, dir_subtree, file_flags, df_counters, special, dir_first_war, dir_main and
+  // dir_main_sub live inside the slab)
+  void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
-                  t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->dir_direct, t->dir_first_war, t->dir_content,
-                  t->dir_main, t->dir_subtree, t->dir_main_sub, t->dir_opts, t->dir_ignore, t->dir_state,
-                  t->dir_descend, t->file_flags, t->df_counters, t->cand_file, t->cand_first, t->cand_err, t->cand_body,
-                  t->cand_esc, t->stripe_state, t->ign_blob, t->special, t->pieces};
+                  t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->slab, t->dir_opts, t->dir_ignore, t->dir_state,
+                  t->dir_descend, t->cand_file, t->cand_tile0, t->cand_err, t->cand_left, t->cand_body,
+                  t->cand_esc, t->tile_state, t->ign_blob, t->pieces};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -379,15 +380,6 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   t->n_dirs = tree->n_dirs; t->n_entries = tree->n_entries; t->n_files = tree->n_files; t->max_depth = tree->max_depth;
   t->file_begin = file_begin; t->file_end = file_end; t->first_skip = first_skip; t->last_end = last_end;
   const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files, ns = file_end - file_begin;
-  // levels (host): directories grouped by depth for the bottom-up / top-down sweeps
-  std::vector<uint32_t> level_dirs(nd ? nd : 1);
-  t->level_off.assign((size_t)t->max_depth + 2, 0);
-  for (uint32_t d = 0; d < nd; d++) t->level_off[tree->dir_depth[d] + 1]++;
-  for (size_t L = 1; L < t->level_off.size(); L++) t->level_off[L] += t->level_off[L - 1];
-  {
-    std::vector<uint32_t> cur(t->level_off.begin(), t->level_off.end() - 1);
-    for (uint32_t d = 0; d < nd; d++) level_dirs[cur[tree->dir_depth[d]]++] = d;
-  }
   // chunk prefix over the shard
   std::vector<uint32_t> chunk_first((size_t)ns + 1);
   uint64_t nchunks = 0, content = 0;
@@ -417,7 +409,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   t->shard_bytes = r1 - r0 + 16;
 
   CU(dev_alloc(&t->dir_parent, nd)); CU(dev_alloc(&t->dir_entry, nd)); CU(dev_alloc(&t->dir_depth, nd));
-  CU(dev_alloc(&t->level_dirs, nd)); CU(dev_alloc(&t->dir_flags, nd));
+  CU(dev_alloc(&t->dir_flags, nd));
   CU(dev_alloc(&t->entry_dir, ne)); CU(dev_alloc(&t->entry_name_off, (size_t)ne + 1)); CU(dev_alloc(&t->entry_child, ne));
   CU(dev_alloc(&t->entry_type, ne)); CU(dev_alloc(&t->names, (size_t)tree->n_name_bytes));
   CU(dev_alloc(&t->file_entry, nf)); CU(dev_alloc(&t->file_off, nf)); CU(dev_alloc(&t->file_len, nf));
@@ -425,29 +417,51 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne)); CU(dev_alloc(&t->pieces, 2));
   {
-    uint64_t cap = (t->shard_bytes + kDfStripe - 1) / kDfStripe + ns + 1;  // stripes over every file body, rounded up per file
-    if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile stripe table");
-    t->stripe_cap = (uint32_t)cap;
-    CU(dev_alloc(&t->df_counters, 2)); CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_first, (size_t)ns + 1));
+    // isDockerFile scratch: a candidate per file at worst, a word per 64 KiB tile of candidate body
+    uint64_t cap = (t->shard_bytes + kDfTile - 1) / kDfTile + ns + 1;  // tiles over every file body, rounded up per file
+    if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile tile table");
+    t->tile_cap = (uint32_t)cap;
+    CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_tile0, ns)); CU(dev_alloc(&t->cand_left, ns));
     CU(dev_alloc(&t->cand_err, ns)); CU(dev_alloc(&t->cand_body, ns)); CU(dev_alloc(&t->cand_esc, ns));
-    CU(dev_alloc(&t->stripe_state, cap));
+    CU(dev_alloc(&t->tile_state, cap));
+    CU(cudaMemsetAsync(t->tile_state, 0, 4ull * cap, C->stream));  // once: pass numbers start at 1
   }
-  CU(dev_alloc(&t->dir_direct, nd)); CU(dev_alloc(&t->dir_first_war, nd)); CU(dev_alloc(&t->dir_content, nd));
-  CU(dev_alloc(&t->dir_main, nd)); CU(dev_alloc(&t->dir_subtree, nd)); CU(dev_alloc(&t->dir_main_sub, nd));
+  {
+    // the slab (DevTree::slab): zero region, the list part of `special`, all-ones region
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t nd4 = up(4ull * (nd ? nd : 1));
+    size_t off = 0;
+    const size_t o_direct = off; off += nd4;
+    const size_t o_content = off; off += nd4;
+    const size_t o_subtree = off; off += nd4;
+    const size_t o_flags = off; off += up(nf ? nf : 1);
+    const size_t o_ctr = off; off += up(sizeof(DfCounters));
+    const size_t o_special = off; off += up(4ull * ((size_t)kSpecialCap + 1));
+    t->slab_zero_bytes = o_special + 4;  // up to and including special[0], the count
+    t->slab_ff_off = off;
+    const size_t o_war = off; off += nd4;
+    const size_t o_main = off; off += nd4;
+    const size_t o_main_sub = off; off += nd4;
+    t->slab_ff_bytes = off - t->slab_ff_off;
+    CU(cudaMalloc((void**)&t->slab, off));
+    t->dir_direct = (uint32_t*)(t->slab + o_direct); t->dir_content = (uint32_t*)(t->slab + o_content);
+    t->dir_subtree = (uint32_t*)(t->slab + o_subtree); t->file_flags = t->slab + o_flags;
+    t->df_counters = (DfCounters*)(t->slab + o_ctr); t->special = (uint32_t*)(t->slab + o_special);
+    t->dir_first_war = (uint32_t*)(t->slab + o_war); t->dir_main = (uint32_t*)(t->slab + o_main);
+    t->dir_main_sub = (uint32_t*)(t->slab + o_main_sub);
+  }
   CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_ignore, nd));
-  CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd)); CU(dev_alloc(&t->file_flags, nf));
+  CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd));
 
   CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
   CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
   CU(cudaHostAlloc((void**)&dt->h_results, 22ull * (nd ? nd : 1) + nf + 64, cudaHostAllocDefault));
-  CU(dev_alloc(&t->special, (size_t)kSpecialCap + 1));
   t->special_cap = kSpecialCap;
   cudaStream_t s = C->stream;
   CU(cudaEventRecord(C->ev[0], s));
   auto H2D = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess; };
   CU(H2D(t->dir_parent, tree->dir_parent, 4ull * nd)); CU(H2D(t->dir_entry, tree->dir_entry, 4ull * nd));
   CU(H2D(t->dir_depth, tree->dir_depth, 4ull * nd)); CU(H2D(t->dir_flags, tree->dir_flags, nd));
-  CU(H2D(t->level_dirs, level_dirs.data(), 4ull * nd));
   CU(H2D(t->entry_dir, tree->entry_dir, 4ull * ne)); CU(H2D(t->entry_name_off, tree->entry_name_off, 4ull * ((size_t)ne + 1)));
   CU(H2D(t->entry_child, tree->entry_child, 4ull * ne)); CU(H2D(t->entry_type, tree->entry_type, ne));
   CU(H2D(t->names, tree->names, tree->n_name_bytes));
@@ -457,7 +471,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   if (tree->bytes && t->shard_bytes > 16) { if (int rc = copy_to_device(C, s, t->bytes, tree->bytes + t->shard_byte0, t->shard_bytes - 16)) return rc; }
   CU(cudaMemsetAsync(t->bytes + (t->shard_bytes - 16), 0, 16, s));
   CU(cudaEventRecord(C->ev[1], s));
-  CU(cudaStreamSynchronize(s));  // level_dirs / chunk_first are stack-owned host vectors
+  CU(cudaStreamSynchronize(s));  // chunk_first is a stack-owned host vector
   CU(cudaEventElapsedTime(&dt->ms_h2d, C->ev[0], C->ev[1]));
   guard.keep = true;
   *out = dt;
@@ -574,12 +588,12 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   const bool content = !(params && params->skip_content);
   CU(cudaStreamWaitEvent(s, C->ev_feat, 0));   // a previous pass's copy of the name features may still be reading them
   CU(cudaStreamWaitEvent(s, C->ev_early, 0));  // ... and its directory-level kernels the arrays cleared below
-  CU(cudaMemsetAsync(t->dir_direct, 0, 4ull * t->n_dirs, s));
-  CU(cudaMemsetAsync(t->dir_first_war, 0xFF, 4ull * t->n_dirs, s));
-  CU(cudaMemsetAsync(t->dir_content, 0, 4ull * t->n_dirs, s));
-  CU(cudaMemsetAsync(t->dir_main, 0xFF, 4ull * t->n_dirs, s));
-  CU(cudaMemsetAsync(t->file_flags, 0, t->n_files, s));
-  CU(cudaMemsetAsync(t->special, 0, 4, s));
+  CU(cudaMemsetAsync(t->slab, 0, t->slab_zero_bytes, s));
+  CU(cudaMemsetAsync(t->slab + t->slab_ff_off, 0xFF, t->slab_ff_bytes, s));
+  if (++t->epoch >= 0x7FFFFFFFu) {  // the tile table is tagged with the pass number: start over
+    CU(cudaMemsetAsync(t->tile_state, 0, 4ull * t->tile_cap, s));
+    t->epoch = 1;
+  }
   dt->prep.ready = false;
   CU(cudaEventRecord(C->ev[8], s));
   launch_name_features(C, t);
@@ -595,9 +609,9 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   if (content) {
     launch_scan_bytes(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[3], s));
-    launch_file_combine(C, t, t->chunk_rec);
+    launch_file_phase(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[9], s));
-    launch_dockerfile(C, t);
+    launch_df_body(C, t);
     CU(cudaEventRecord(C->ev[10], s));
   }
   CU(cudaGetLastError());
@@ -1089,9 +1103,7 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     CU(cudaStreamWaitEvent(ss, C->ev_names, 0));
     CU(cudaStreamWaitEvent(ss, C->ev_blob, 0));
     CU(cudaEventRecord(C->ev_side0, ss));
-    launch_subtree(C, t, ss);
-    launch_combine_opts(C, t, P.sh_flavor, ss);
-    launch_walk(C, t, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore, ss);
+    launch_walk(C, t, P.sh_flavor, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore, ss);
     CU(cudaEventRecord(C->ev_side1, ss));
     CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, ss));
     CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, ss));

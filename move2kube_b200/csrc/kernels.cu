@@ -43,15 +43,17 @@ void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n) {
 // ---------------------------------------------------------------------------------------------
 // Kernel 1: name features.  One thread per directory entry; the signature table (exact names,
 // suffixes) is staged in shared memory; a warp-level segmented OR (match_any + redux) folds the
-// entries of one directory before a single atomicOr per (warp, directory).
+// entries of one directory before a single atomicOr per (warp, directory) -- and the same lane then
+// pushes the bits up the directory's ancestor chain (dir_subtree = OR over the subtree: what the
+// scripts' `find "$1"/. -name` computes by re-walking every subtree).
 // Replaces: [ -f D/name ] / find -name "*.ext" / "$1/"*.war of the 18 detect scripts
 // (internal/assets/*/m2k*detect.sh) and GetFilesByName's basename test (utils.go:108-113).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_name_features(
     uint32_t n_entries, const uint32_t* __restrict__ entry_dir, const uint32_t* __restrict__ entry_name_off,
     const uint8_t* __restrict__ entry_type, const uint8_t* __restrict__ names, const NameSig* __restrict__ sigs, int n_sigs,
-    uint32_t* __restrict__ entry_feat, uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_first_war,
-    uint32_t* __restrict__ special, uint32_t special_cap) {
+    const uint32_t* __restrict__ dir_parent, uint32_t* __restrict__ entry_feat, uint32_t* __restrict__ dir_direct,
+    uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_first_war, uint32_t* __restrict__ special, uint32_t special_cap) {
   __shared__ NameSig s_sigs[kMaxNameSigs];
   for (int i = threadIdx.x; i < n_sigs; i += blockDim.x) s_sigs[i] = sigs[i];
   __syncthreads();
@@ -95,15 +97,25 @@ __global__ void __launch_bounds__(256) k_name_features(
   uint32_t peers = __match_any_sync(FULL, dir);
   uint32_t dirfeat = feat & ~(1u << M2K_N_WAR);  // the war bit of a directory is decided from dir_first_war
   uint32_t ored = __reduce_or_sync(peers, dirfeat);
-  if (valid && ored && (uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicOr(&dir_direct[dir], ored);
+  if (valid && ored && (uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31)) {
+    atomicOr(&dir_direct[dir], ored);
+    // find's recursion, once for all directories: the bits climb the ancestor chain.  A level that already
+    // holds all of them ends the climb -- whoever put a bit there first carries it further up (it saw the
+    // bit missing, so it went on), which makes the whole pass close to linear in the number of entries.
+    for (uint32_t x = dir;;) {
+      const uint32_t old = atomicOr(&dir_subtree[x], ored);
+      if ((old & ored) == ored || x == 0) break;
+      x = dir_parent[x];
+    }
+  }
 }
 
 void launch_name_features(Ctx* c, DevTree* t) {
   if (!t->n_entries) return;
   uint32_t blocks = (t->n_entries + 255) / 256;
   k_name_features<<<blocks, 256, 0, c->stream>>>(t->n_entries, t->entry_dir, t->entry_name_off, t->entry_type, t->names,
-                                                 c->d_sigs, c->n_sigs, t->entry_feat, t->dir_direct, t->dir_first_war,
-                                                 t->special, t->special_cap);
+                                                 c->d_sigs, c->n_sigs, t->dir_parent, t->entry_feat, t->dir_direct, t->dir_subtree,
+                                                 t->dir_first_war, t->special, t->special_cap);
   c->launches++;
 }
 
@@ -355,18 +367,29 @@ __host__ __device__ __forceinline__ uint32_t acc_long(uint64_t bytes, uint64_t l
 
 constexpr uint32_t kCombineWarpChunks = 128;  // files with more chunks are folded by the whole warp
 
-struct CombineArgs {
+// isDockerFile works on the candidates' bodies in tiles of 256 stripes of 256 bytes (64 KiB): one
+// block per tile, one thread per stripe (k_df_body)
+constexpr uint32_t kDfTileStripes = 256;
+constexpr uint32_t kDfTileBytes = kDfTileStripes * df::kStripe;
+
+// everything the per-file kernels (combine + head, body tiles) look at
+struct FileArgs {
   uint32_t n_shard_files, file_begin, first_skip, last_end;  // chunks of the first file before the shard; end chunk of the last file (M2K_NONE: all)
   const uint32_t* chunk_first; const ChunkRec* chunk_rec;
-  const uint64_t* file_len;
+  const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
   const uint32_t* file_entry; const uint32_t* entry_dir; const uint32_t* entry_name_off; const uint8_t* names;
   uint8_t* file_flags; uint32_t* dir_content; uint32_t* dir_main;
   PieceSummary* pieces;  // [2]: the shard's first / last file when only part of it is here
+  // isDockerFile scratch: FROM-first candidates and their body tiles
+  DfCounters* ctr;
+  uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_tile0; uint32_t* cand_err; uint32_t* cand_left;
+  uint32_t* tile_state;  // per tile: (epoch << 1) | line state at the end of the tile
+  uint32_t epoch;
 };
 
 // fold records [k0, k1) (indices into the file's records present in this shard, the first of which
 // covers file bytes from `byte0`); *has_main / *not_df accumulate the flag bits
-__device__ __forceinline__ RunAcc fold_records(const CombineArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t byte0, uint64_t len,
+__device__ __forceinline__ RunAcc fold_records(const FileArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t byte0, uint64_t len,
                                                uint32_t* has_main, uint32_t* not_df) {
   RunAcc acc{0, 0, 0, 0};
   for (uint32_t k = k0; k < k1; k++) {
@@ -393,28 +416,61 @@ __device__ __forceinline__ void note_main_file(uint32_t f, const uint32_t* file_
   }
 }
 
-// i: index of the file in the shard.  A file all of whose chunks are here gets its final flags; the
-// part of a file that continues on another GPU becomes a piece summary for k_merge_pieces.
-__device__ __forceinline__ void finish_file(const CombineArgs& a, uint32_t i, uint32_t f, const RunAcc& tot, uint64_t len,
-                                            uint32_t has_main, uint32_t not_df) {
+__device__ __forceinline__ void note_dockerfile(const FileArgs& a, uint32_t f) {
+  atomicOr(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
+}
+
+// i: index of the file in the shard.  A file all of whose chunks are here gets its final HAS_MAIN /
+// LONG_LINE flags, and its head is parsed for isDockerFile right away (nearly every file was already
+// ruled out by the scan kernel's look at its first word; a FROM-first file becomes a candidate whose
+// body k_df_body validates).  The part of a file that continues on another GPU becomes a piece
+// summary for k_merge_pieces instead; when that part starts the file, its head is settled as far as
+// it can be from here.
+__device__ __noinline__ void finish_file(const FileArgs& a, uint32_t i, uint32_t f, const RunAcc& tot, uint64_t len,
+                                         uint32_t has_main, uint32_t not_df) {
   const bool cut_front = i == 0 && a.first_skip != 0;
   const bool cut_back = i + 1 == a.n_shard_files && a.last_end != M2K_NONE;
+  const uint8_t* fbytes = a.bytes + (a.file_off[f] - a.shard_byte0);
+  uint64_t body = 0;
+  uint32_t esc = '\\';
   if (cut_front || cut_back) {
     PieceSummary ps;
     ps.file = f;
     ps.flags = (has_main ? PIECE_HAS_MAIN : 0u) | (tot.longf ? PIECE_LONG : 0u) | (cut_front ? 0u : PIECE_FIRST) | (not_df ? PIECE_NOT_DF : 0u);
     ps.bytes = tot.bytes; ps.lead = tot.lead; ps.trail = tot.trail;
+    if (!cut_front && !not_df) {
+      // the body of a FROM-first file cannot be validated from a piece (see k_merge_pieces)
+      const uint64_t n_here = (uint64_t)a.last_end * kChunkBytes;  // cut_back holds, so this is < len
+      bool touched_end = false;
+      const bool from = df::head(fbytes, n_here, false, &body, &esc, &touched_end);
+      ps.flags |= touched_end ? PIECE_HEAD_TRUNC : (from ? PIECE_HEAD_FROM : PIECE_HEAD_NOT_FROM);
+    }
     a.pieces[i == 0 ? 0 : 1] = ps;
     a.file_flags[f] = 0;
     return;
   }
   const uint32_t longf = acc_long(tot.bytes, tot.lead, tot.trail, tot.longf);
-  // bit 7 is internal: "the first word already rules out a Dockerfile" (cleared again by k_df_head)
-  a.file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0) | (longf ? M2K_FILE_LONG_LINE : 0) | (not_df ? 0x80 : 0));
+  uint32_t flags = (has_main ? M2K_FILE_HAS_MAIN : 0u) | (longf ? M2K_FILE_LONG_LINE : 0u);
   if (has_main) note_main_file(f, a.file_entry, a.entry_dir, a.entry_name_off, a.names, a.dir_content, a.dir_main);
+  if (!not_df && df::head(fbytes, len, longf != 0, &body, &esc)) {
+    flags |= M2K_FILE_FROM_FIRST;
+    const uint64_t n_tiles = (len - body + kDfTileBytes - 1) / kDfTileBytes;
+    if (n_tiles == 0) {  // nothing after the FROM line: nothing left that could fail to parse
+      flags |= M2K_FILE_DOCKERFILE;
+      note_dockerfile(a, f);
+    } else {
+      // candidate number and first tile number from ONE counter (high / low half), so that the tile
+      // offsets increase with the candidate number and a tile finds its candidate by bisection
+      const unsigned long long old = atomicAdd(&a.ctr->cand_tiles, (1ull << 32) | n_tiles);
+      const uint32_t c = (uint32_t)(old >> 32);
+      a.cand_file[c] = f; a.cand_body[c] = body; a.cand_esc[c] = (uint8_t)esc;
+      a.cand_tile0[c] = (uint32_t)old; a.cand_err[c] = 0; a.cand_left[c] = (uint32_t)n_tiles;
+    }
+  }
+  a.file_flags[f] = (uint8_t)flags;
 }
 
-__global__ void __launch_bounds__(256) k_file_combine(CombineArgs a) {
+__global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = i < a.n_shard_files;
@@ -458,229 +514,131 @@ __global__ void __launch_bounds__(256) k_file_combine(CombineArgs a) {
   }
 }
 
-void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
+// ---------------------------------------------------------------------------------------------
+// Kernel 4: the bodies of the isDockerFile candidates (dockerfile_dev.cuh) in ONE launch, whatever
+// their size.  A tile is 256 stripes of 256 bytes; blocks draw tile numbers from a counter, one
+// thread per stripe:
+//   1. every thread composes the line-state map of its stripe (does a physical line start a logical
+//      line? one bit of state carried from the line before), a block scan composes them;
+//   2. the tile waits for the state at the end of the tile before it (published in tile_state,
+//      tagged with the pass number so that the table never needs clearing) and publishes its own at
+//      once -- a chained scan: the maps of all tiles are computed in parallel, only one word per
+//      tile travels along the file, so a body of hundreds of MB is bounded by its tile count times a
+//      flag round trip, not walked by one thread;
+//   3. every thread checks the logical lines starting in its stripe (ENV / LABEL / ONBUILD syntax);
+//   4. the block that finishes a candidate's last tile sets its DOCKERFILE bit.
+// Tickets are handed out in order and a block holds a ticket only while it is running, so the tile a
+// block waits for is always held by a running block: no deadlock, whatever the grid size.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kDfTileStripes) k_df_body(FileArgs a) {
+  __shared__ uint32_t s_ticket, s_in;
+  __shared__ uint32_t s_warp_map[kDfTileStripes / 32];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned long long ct = a.ctr->cand_tiles;  // final: k_file_combine has finished
+  const uint32_t n_cand = (uint32_t)(ct >> 32), n_tiles = (uint32_t)ct;
+  for (;;) {
+    if (tid == 0) s_ticket = atomicAdd(&a.ctr->next_tile, 1u);
+    __syncthreads();
+    const uint32_t t = s_ticket;
+    if (t >= n_tiles) break;
+    uint32_t c = 0, h = n_cand;  // the last candidate whose first tile is <= t
+    while (h - c > 1) { uint32_t m = (c + h) >> 1; if (a.cand_tile0[m] <= t) c = m; else h = m; }
+    const uint32_t k = t - a.cand_tile0[c], f = a.cand_file[c];
+    const df::File file{a.bytes + (a.file_off[f] - a.shard_byte0), a.file_len[f], a.cand_esc[c]};
+    const uint64_t body = a.cand_body[c];
+    const uint64_t lo = body + (uint64_t)k * kDfTileBytes + (uint64_t)tid * df::kStripe;
+    const bool live = lo < file.n;
+    const uint64_t hi = lo + df::kStripe < file.n ? lo + df::kStripe : file.n;
+    const uint32_t m = live ? df::stripe_map(file, body, lo, hi) : 0x2u;  // identity past the end
+    uint32_t inc = m;  // inclusive scan (composition, earlier stripe first) over the warp
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(FULL, inc, d);
+      if ((int)lane >= d) inc = df::map_compose(o, inc);
+    }
+    uint32_t exc = __shfl_up_sync(FULL, inc, 1);
+    if (lane == 0) exc = 0x2u;
+    if (lane == 31) s_warp_map[warp] = inc;
+    __syncthreads();
+    uint32_t pre = 0x2u;
+    for (uint32_t w = 0; w < warp; w++) pre = df::map_compose(pre, s_warp_map[w]);
+    exc = df::map_compose(pre, exc);
+    if (tid == 0) {
+      uint32_t agg = 0x2u;
+      for (uint32_t w = 0; w < kDfTileStripes / 32; w++) agg = df::map_compose(agg, s_warp_map[w]);
+      uint32_t sin = 0;  // a body starts outside any continuation
+      if (k != 0) {
+        uint32_t v;
+        while (((v = ld_acquire(a.tile_state + (t - 1))) >> 1) != a.epoch) __nanosleep(40);
+        sin = v & 1u;
+      }
+      st_release(a.tile_state + t, (a.epoch << 1) | df::map_apply(agg, sin));
+      s_in = sin;
+    }
+    __syncthreads();
+    const bool ok = !live || df::stripe_validate(file, body, lo, hi, df::map_apply(exc, s_in));
+    const int bad = __syncthreads_or(!ok);
+    if (tid == 0) {
+      if (bad) atomicExch(&a.cand_err[c], 1u);
+      __threadfence();
+      if (atomicSub(&a.cand_left[c], 1u) == 1u) {  // this was the candidate's last open tile
+        __threadfence();
+        if (atomicAdd(&a.cand_err[c], 0u) == 0u) {
+          a.file_flags[f] |= M2K_FILE_DOCKERFILE;
+          note_dockerfile(a, f);
+        }
+      }
+    }
+  }
+}
+
+static FileArgs file_args(DevTree* t, const ChunkRec* chunk_rec) {
+  return FileArgs{t->file_end - t->file_begin, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec,
+                  t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
+                  t->file_flags, t->dir_content, t->dir_main, t->pieces, t->df_counters, t->cand_file, t->cand_body, t->cand_esc,
+                  t->cand_tile0, t->cand_err, t->cand_left, t->tile_state, t->epoch};
+}
+
+// per-file combine + Dockerfile heads, then the candidates' bodies: two launches
+void launch_file_phase(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
   uint32_t nf = t->file_end - t->file_begin;
   cudaMemsetAsync(t->pieces, 0xFF, 2 * sizeof(PieceSummary), c->stream);  // file == M2K_NONE: unused slot
   if (!nf) return;
-  CombineArgs a{nf, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec, t->file_len,
-                t->file_entry, t->entry_dir, t->entry_name_off, t->names, t->file_flags, t->dir_content, t->dir_main, t->pieces};
+  FileArgs a = file_args(t, chunk_rec);
   k_file_combine<<<(nf + 255) / 256, 256, 0, c->stream>>>(a);
+  c->launches++;
+}
+void launch_df_body(Ctx* c, DevTree* t) {
+  if (t->file_end == t->file_begin) return;
+  FileArgs a = file_args(t, nullptr);
+  k_df_body<<<c->sm_count * 4, kDfTileStripes, 0, c->stream>>>(a);
   c->launches++;
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 4: isDockerFile (dockerfile_dev.cuh), in five small launches so that no single thread ever
-// walks a whole file:
-//   k_df_head     one thread per file: directives, comments, ARGs, first instruction.  Nearly every
-//                 file leaves after a few bytes; FROM-first files become candidates (scratch list).
-//   k_df_prefix   one block: exclusive prefix of the candidates' stripe counts.
-//   k_df_maps     one thread per 256-byte stripe of candidate bodies: composed line-state map.
-//   k_df_scan     one thread per candidate: state at every stripe start.
-//   k_df_validate one thread per stripe: parse errors of the logical lines starting in it;
-//   k_df_finish   one thread per candidate: DOCKERFILE bit + per-directory content bit.
-// Grids are fixed multiples of the SM count and read the candidate counts from device memory, so the
-// host never waits for them.
+// Kernel 5: what the byte scan adds to the per-directory results.  The content results are sparse
+// (directories holding a python main file or a Dockerfile): each such directory pushes its bits and
+// its lowest main-file id up its ancestor chain, and stops where nothing new arrives (the thread
+// that brought the same or better continues from there).
 // ---------------------------------------------------------------------------------------------
-struct DfArgs {
-  uint32_t n_shard_files, file_begin, first_skip, last_end;
-  PieceSummary* pieces;
-  const uint64_t* file_off; const uint64_t* file_len; const uint8_t* bytes; uint64_t shard_byte0;
-  const uint32_t* file_entry; const uint32_t* entry_dir;
-  uint8_t* file_flags; uint32_t* dir_content;
-  uint32_t* counters;     // [0] candidates, [1] total stripes
-  uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_first; uint32_t* cand_err;
-  uint8_t* stripe_state;  // per stripe: bits 0-1 composed map, bit 2 state at the stripe start
-  uint32_t stripe_cap;
-};
-
-__device__ __forceinline__ df::File df_file(const DfArgs& a, uint32_t f, uint32_t esc) {
-  return df::File{a.bytes + (a.file_off[f] - a.shard_byte0), a.file_len[f], esc};
-}
-
-__global__ void __launch_bounds__(128) k_df_head(DfArgs a) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n_shard_files) return;
-  uint32_t f = a.file_begin + i;
-  uint64_t body = 0, n = a.file_len[f];
-  uint32_t esc = '\\';
-  const bool cut_front = i == 0 && a.first_skip != 0;
-  const bool cut_back = i + 1 == a.n_shard_files && a.last_end != M2K_NONE;
-  if (cut_front || cut_back) {
-    // only part of this file is here.  When that part starts the file, settle what its head can settle;
-    // the body of a FROM-first file cannot be validated from a piece (see k_merge_pieces).
-    PieceSummary* ps = &a.pieces[i == 0 ? 0 : 1];
-    if (!cut_front && !(ps->flags & PIECE_NOT_DF)) {
-      uint64_t n_here = (uint64_t)a.last_end * kChunkBytes;  // cut_back holds, so this is < n
-      bool touched_end = false;
-      bool from = df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n_here, false, &body, &esc, &touched_end);
-      ps->flags |= touched_end ? PIECE_HEAD_TRUNC : (from ? PIECE_HEAD_FROM : PIECE_HEAD_NOT_FROM);
-    }
-    return;
-  }
-  uint32_t flags = a.file_flags[f];
-  if (flags & 0x80) { a.file_flags[f] = (uint8_t)(flags & 0x7F); return; }  // ruled out by the scan kernel (first word)
-  if (!df::head(a.bytes + (a.file_off[f] - a.shard_byte0), n, (flags & M2K_FILE_LONG_LINE) != 0, &body, &esc)) return;
-  a.file_flags[f] = (uint8_t)(flags | M2K_FILE_FROM_FIRST);
-  uint32_t c = atomicAdd(&a.counters[0], 1u);
-  a.cand_file[c] = f;
-  a.cand_body[c] = body;
-  a.cand_esc[c] = (uint8_t)esc;
-  a.cand_err[c] = 0;
-  a.cand_first[c] = (uint32_t)((n - body + df::kStripe - 1) / df::kStripe);  // stripe count, prefix-summed next
-}
-
-__global__ void __launch_bounds__(1024) k_df_prefix(DfArgs a) {
-  __shared__ uint32_t s_part[1024];
-  __shared__ uint32_t s_carry;
-  const uint32_t n = a.counters[0];
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
-  for (uint32_t base = 0; base < n; base += 1024) {
-    uint32_t i = base + threadIdx.x;
-    uint32_t v = i < n ? a.cand_first[i] : 0;
-    s_part[threadIdx.x] = v;
-    __syncthreads();
-    for (uint32_t off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
-      uint32_t t = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0;
-      __syncthreads();
-      s_part[threadIdx.x] += t;
-      __syncthreads();
-    }
-    uint32_t incl = s_part[threadIdx.x], carry = s_carry;
-    if (i < n) a.cand_first[i] = carry + incl - v;
-    __syncthreads();
-    if (threadIdx.x == 1023) s_carry = carry + incl;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    uint32_t total = s_carry;
-    a.cand_first[n] = total;
-    a.counters[1] = total <= a.stripe_cap ? total : 0xFFFFFFFFu;  // cannot happen: the cap is the worst case
-  }
-}
-
-__device__ __forceinline__ bool df_stripe(const DfArgs& a, uint32_t s, uint32_t* c, uint64_t* lo, uint64_t* hi) {
-  uint32_t nc = a.counters[0];
-  uint32_t l = 0, h = nc;  // last candidate with cand_first <= s
-  while (h - l > 1) { uint32_t m = (l + h) >> 1; if (a.cand_first[m] <= s) l = m; else h = m; }
-  *c = l;
-  uint64_t body = a.cand_body[l];
-  *lo = body + (uint64_t)(s - a.cand_first[l]) * df::kStripe;
-  uint64_t n = a.file_len[a.cand_file[l]];
-  *hi = *lo + df::kStripe < n ? *lo + df::kStripe : n;
-  return true;
-}
-
-__global__ void __launch_bounds__(128) k_df_maps(DfArgs a) {
-  const uint32_t total = a.counters[1];
-  if (total == 0xFFFFFFFFu) return;
-  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < total; s += gridDim.x * blockDim.x) {
-    uint32_t c; uint64_t lo, hi;
-    df_stripe(a, s, &c, &lo, &hi);
-    df::File f = df_file(a, a.cand_file[c], a.cand_esc[c]);
-    a.stripe_state[s] = (uint8_t)df::stripe_map(f, a.cand_body[c], lo, hi);
-  }
-}
-
-__global__ void __launch_bounds__(128) k_df_scan(DfArgs a) {
-  const uint32_t nc = a.counters[0];
-  if (a.counters[1] == 0xFFFFFFFFu) return;
-  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
-    uint32_t state = 0;
-    for (uint32_t s = a.cand_first[c]; s < a.cand_first[c + 1]; s++) {
-      uint32_t m = a.stripe_state[s] & 3u;
-      a.stripe_state[s] = (uint8_t)(m | (state << 2));
-      state = df::map_apply(m, state);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(128) k_df_validate(DfArgs a) {
-  const uint32_t total = a.counters[1];
-  if (total == 0xFFFFFFFFu) return;
-  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < total; s += gridDim.x * blockDim.x) {
-    uint32_t c; uint64_t lo, hi;
-    df_stripe(a, s, &c, &lo, &hi);
-    df::File f = df_file(a, a.cand_file[c], a.cand_esc[c]);
-    if (!df::stripe_validate(f, a.cand_body[c], lo, hi, (a.stripe_state[s] >> 2) & 1u)) a.cand_err[c] = 1;
-  }
-}
-
-__global__ void __launch_bounds__(128) k_df_finish(DfArgs a) {
-  const uint32_t nc = a.counters[0];
-  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
-    if (a.cand_err[c] || a.counters[1] == 0xFFFFFFFFu) continue;
-    uint32_t f = a.cand_file[c];
-    a.file_flags[f] |= M2K_FILE_DOCKERFILE;
-    atomicOr(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
-  }
-}
-
-void launch_dockerfile(Ctx* c, DevTree* t) {
-  uint32_t nf = t->file_end - t->file_begin;
-  if (!nf) return;
-  DfArgs a{nf, t->file_begin, t->first_skip, t->last_end, t->pieces, t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir,
-           t->file_flags, t->dir_content, t->df_counters, t->cand_file, t->cand_body, t->cand_esc, t->cand_first, t->cand_err,
-           t->stripe_state, t->stripe_cap};
-  cudaMemsetAsync(t->df_counters, 0, 8, c->stream);
-  k_df_head<<<(nf + 127) / 128, 128, 0, c->stream>>>(a);
-  k_df_prefix<<<1, 1024, 0, c->stream>>>(a);
-  const int grid = c->sm_count * 8;
-  k_df_maps<<<grid, 128, 0, c->stream>>>(a);
-  k_df_scan<<<grid, 128, 0, c->stream>>>(a);
-  k_df_validate<<<grid, 128, 0, c->stream>>>(a);
-  k_df_finish<<<grid, 128, 0, c->stream>>>(a);
-  c->launches += 6;
-}
-
-// ---------------------------------------------------------------------------------------------
-// Kernel 5: subtree OR / MIN, bottom-up one level per launch (find's recursion, done once for all
-// directories instead of once per visited directory).
-// ---------------------------------------------------------------------------------------------
-__global__ void k_subtree_init(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, uint32_t* __restrict__ dir_subtree,
-                               uint32_t* __restrict__ dir_main_sub) {
-  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= n_dirs) return;
-  dir_subtree[d] = dir_direct[d];   // name features; the content bits are added by k_content_up once the bytes are scanned
-  dir_main_sub[d] = M2K_NONE;
-}
-// The content results are sparse (directories holding a python main file or a Dockerfile): each such
-// directory pushes its bits and its lowest main-file id up its ancestor chain.
 __global__ void k_content_up(uint32_t n_dirs, const uint32_t* __restrict__ dir_parent, const uint32_t* __restrict__ dir_content,
                              const uint32_t* __restrict__ dir_main, uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
   uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n_dirs) return;
-  const uint32_t bits = dir_content[d], mf = dir_main[d];
-  if (!bits && mf == M2K_NONE) return;
-  for (uint32_t x = d;; x = dir_parent[x]) {
-    if (bits) atomicOr(&dir_subtree[x], bits);
-    if (mf != M2K_NONE) atomicMin(&dir_main_sub[x], mf);
+  uint32_t bits = dir_content[d], mf = dir_main[d];
+  for (uint32_t x = d; bits || mf != M2K_NONE; x = dir_parent[x]) {
+    if (bits && (atomicOr(&dir_subtree[x], bits) & bits) == bits) bits = 0;
+    if (mf != M2K_NONE && atomicMin(&dir_main_sub[x], mf) <= mf) mf = M2K_NONE;
     if (x == 0) break;
-  }
-}
-__global__ void k_subtree_level(const uint32_t* __restrict__ level_dirs, uint32_t n, const uint32_t* __restrict__ dir_parent,
-                                uint32_t* __restrict__ dir_subtree, uint32_t* __restrict__ dir_main_sub) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint32_t d = level_dirs[i], p = dir_parent[d];
-  uint32_t s = dir_subtree[d];
-  if (s) atomicOr(&dir_subtree[p], s);
-  uint32_t m = dir_main_sub[d];
-  if (m != M2K_NONE) atomicMin(&dir_main_sub[p], m);
-}
-
-// name features up the tree (find's recursion): needs only the name kernel's output, so it runs on the
-// side stream while the bytes are still being scanned
-void launch_subtree(Ctx* c, DevTree* t, cudaStream_t st) {
-  if (!t->n_dirs) return;
-  k_subtree_init<<<(t->n_dirs + 255) / 256, 256, 0, st>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_main_sub);
-  c->launches++;
-  for (uint32_t L = t->max_depth; L >= 1; L--) {
-    uint32_t a = t->level_off[L], b = t->level_off[L + 1];
-    if (b > a) {
-      k_subtree_level<<<(b - a + 255) / 256, 256, 0, st>>>(t->level_dirs + a, b - a, t->dir_parent, t->dir_subtree, t->dir_main_sub);
-      c->launches++;
-    }
   }
 }
 void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st) {
@@ -690,19 +648,12 @@ void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 6: the 18 built-in predicates per directory (SURVEY.md App. A truth table).
-// D = features of the directory's own entries, S = OR over the subtree.
+// Kernel 6: the 18 built-in predicates of a directory (SURVEY.md App. A truth table), evaluated inside
+// the walk kernel below.  D = features of the directory's own entries, S = OR over the subtree.
 // ---------------------------------------------------------------------------------------------
-__global__ void k_combine_opts(uint32_t n_dirs, const uint32_t* __restrict__ dir_direct, const uint32_t* __restrict__ dir_subtree,
-                               const uint32_t* __restrict__ dir_first_war, const uint8_t* __restrict__ entry_type,
-                               uint32_t sh_flavor, uint32_t* __restrict__ dir_opts) {
-  uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= n_dirs) return;
-  uint32_t D = dir_direct[d], S = dir_subtree[d];
+__device__ __forceinline__ uint32_t dir_options(uint32_t D, uint32_t S, uint32_t W, uint32_t sh_flavor) {
   auto F = [&](int b) { return (D >> b) & 1u; };
   auto R = [&](int b) { return (S >> b) & 1u; };
-  uint32_t fw = dir_first_war[d];
-  uint32_t W = (fw != M2K_NONE && (entry_type[fw] >> 4) != M2K_T_ERR) ? 1u : 0u;  // [ -e first match ]
   uint32_t py = (sh_flavor == M2K_SH_BASH) ? (F(M2K_F_REQUIREMENTS) | F(M2K_F_SETUP_PY) | F(M2K_F_ENVIRONMENT_YML) | F(M2K_F_PIPFILE)) : 0u;
   uint32_t m = 0;
   m |= F(M2K_F_PIPFILE) << M2K_DF_DJANGO;
@@ -721,19 +672,12 @@ __global__ void k_combine_opts(uint32_t n_dirs, const uint32_t* __restrict__ dir
   m |= R(M2K_R_PHP) << M2K_S2I_PHP;
   m |= py << M2K_S2I_PYTHON;
   m |= F(M2K_F_GEMFILE) << M2K_S2I_RUBY;
-  dir_opts[d] = m;
-}
-
-void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor, cudaStream_t st) {
-  if (!t->n_dirs) return;
-  k_combine_opts<<<(t->n_dirs + 255) / 256, 256, 0, st>>>(t->n_dirs, t->dir_direct, t->dir_subtree, t->dir_first_war,
-                                                                t->entry_type, sh_flavor, t->dir_opts);
-  c->launches++;
+  return m;
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 7: the walk (any2kube.go:58-98) in two launches.  k_walk_local: per directory, the
-// case-folded hash of its path, a probe of the ignore table (an exact hash join in place of
+// Kernel 7: the walk (any2kube.go:58-98) in two launches.  k_walk_local: per directory, its option
+// bits (kernel 6), the case-folded hash of its path, a probe of the ignore table (an exact hash join in place of
 // O(#dirs x #entries) EqualFold scans, utils.go:308-315; a hash hit is confirmed rune by rune against
 // the folded entry, so 64-bit collisions cannot change a decision) and the walk's local rule.
 // k_walk_reach: a directory is visited iff the walk descends below all of its ancestors.
@@ -747,7 +691,9 @@ struct WalkArgs {
   const uint32_t* prefix_runes;   // folded runes of the path prefix shared by depth-1 directories
   uint32_t prefix_len;
   uint64_t depth1_state; uint32_t root_ignore;
-  const uint32_t* dir_opts;
+  const uint32_t* dir_direct; const uint32_t* dir_subtree; const uint32_t* dir_first_war; const uint8_t* entry_type;
+  uint32_t sh_flavor;
+  uint32_t* dir_opts;
   uint8_t* dir_ignore; uint8_t* dir_state; uint8_t* dir_descend;
 };
 
@@ -789,13 +735,17 @@ __device__ __forceinline__ uint64_t hash_dir_name(const WalkArgs& a, uint64_t h,
   return hash_fold_bytes(h, a.names + off, a.entry_name_off[e + 1] - off, a.fold_from, a.fold_to, M2K_CASEFOLD_N);
 }
 
-// Step 1, one thread per directory, no dependency between directories: the case-folded hash of the
-// directory's own path (hashing down its ancestor chain), the ignore-table probe with exact
-// confirmation, and the walk's LOCAL rule -- what any2kube.go:58-98 does with this directory if it
-// is reached, and whether the walk would descend below it.
+// Step 1, one thread per directory, no dependency between directories: the 18 predicates, the
+// case-folded hash of the directory's own path (hashing down its ancestor chain), the ignore-table
+// probe with exact confirmation, and the walk's LOCAL rule -- what any2kube.go:58-98 does with this
+// directory if it is reached, and whether the walk would descend below it.
 __global__ void __launch_bounds__(128) k_walk_local(uint32_t n_dirs, const uint32_t* __restrict__ dir_depth, WalkArgs a) {
   uint32_t d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n_dirs) return;
+  const uint32_t fw = a.dir_first_war[d];
+  const uint32_t W = (fw != M2K_NONE && (a.entry_type[fw] >> 4) != M2K_T_ERR) ? 1u : 0u;  // [ -e first match ]
+  const uint32_t opts = dir_options(a.dir_direct[d], a.dir_subtree[d], W, a.sh_flavor);
+  a.dir_opts[d] = opts;
   uint32_t ign = 0;
   if (d == 0) {
     ign = a.root_ignore;  // the root path is compared on the host exactly as given
@@ -828,7 +778,7 @@ __global__ void __launch_bounds__(128) k_walk_local(uint32_t n_dirs, const uint3
   if (a.dir_flags[d] & 1) state = M2K_DIR_WALK_ERROR;
   else if (ign & 4) state = M2K_DIR_PRECONTAINERIZED;
   else if (ign & 1) { if (ign & 2) state = M2K_DIR_IGNORED_PRUNE; else { state = M2K_DIR_IGNORED_DESCEND; descend = 1; } }
-  else if (a.dir_opts[d] == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
+  else if (opts == 0) { if (ign & 2) state = M2K_DIR_NOMATCH_PRUNE; else { state = M2K_DIR_NOMATCH_DESCEND; descend = 1; } }
   else state = M2K_DIR_SERVICE;
   a.dir_state[d] = (uint8_t)state;
   a.dir_descend[d] = (uint8_t)descend;
@@ -844,11 +794,12 @@ __global__ void __launch_bounds__(128) k_walk_reach(uint32_t n_dirs, WalkArgs a)
   }
 }
 
-void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
+void launch_walk(Ctx* c, DevTree* t, uint32_t sh_flavor, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
                  const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore, cudaStream_t st) {
   if (!t->n_dirs) return;
   WalkArgs a{t->dir_parent, t->dir_entry, t->dir_flags, t->entry_name_off, t->names, c->d_fold_from, c->d_fold_to,
-             table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore, t->dir_opts,
+             table, table_mask, runes, prefix_runes, prefix_len, depth1_state, root_ignore,
+             t->dir_direct, t->dir_subtree, t->dir_first_war, t->entry_type, sh_flavor, t->dir_opts,
              t->dir_ignore, t->dir_state, t->dir_descend};
   uint32_t blocks = (t->n_dirs + 127) / 128;
   k_walk_local<<<blocks, 128, 0, st>>>(t->n_dirs, t->dir_depth, a);

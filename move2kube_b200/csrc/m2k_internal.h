@@ -12,6 +12,7 @@ namespace m2k {
 constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
 constexpr uint32_t kDfStripe = 256;      // bytes of one stripe of the parallel Dockerfile validation
+constexpr uint32_t kDfTile = 256 * kDfStripe;  // bytes of one tile (one block of k_df_body)
 constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
 // per-chunk record written by the byte-scan kernel: scratch memory, 8 bytes per 64 KiB chunk, exact
 // to the byte so that records of one file can be stitched anywhere (another kernel, another GPU)
@@ -47,6 +48,10 @@ enum : uint32_t {
   PIECE_HEAD_TRUNC = 64      // the head runs past this piece
 };
 
+// counters of the isDockerFile phase: candidates in the high half and body tiles in the low half of
+// ONE word (so both numberings grow together), and the next tile ticket
+struct DfCounters { unsigned long long cand_tiles; uint32_t next_tile; uint32_t _pad; };
+
 // name signature table staged into shared memory by the name-feature kernel
 struct NameSig {
   uint64_t lo, hi;       // the last <=16 bytes of the pattern, right aligned (byte 0 of `lo` = last character)
@@ -78,9 +83,8 @@ struct DevTree {
   uint64_t shard_byte0 = 0;               // file_off[file_begin]
   uint32_t n_chunks = 0;
   // metadata
-  uint32_t *dir_parent = nullptr, *dir_entry = nullptr, *dir_depth = nullptr, *level_dirs = nullptr;
+  uint32_t *dir_parent = nullptr, *dir_entry = nullptr, *dir_depth = nullptr;
   uint8_t* dir_flags = nullptr;
-  std::vector<uint32_t> level_off;        // host: dirs of depth L are level_dirs[level_off[L] .. level_off[L+1])
   uint32_t *entry_dir = nullptr, *entry_name_off = nullptr, *entry_child = nullptr;
   uint8_t *entry_type = nullptr, *names = nullptr;
   uint32_t* file_entry = nullptr;
@@ -92,14 +96,23 @@ struct DevTree {
   uint64_t* synth_inject = nullptr;
   // work buffers
   ChunkRec* chunk_rec = nullptr;          // [n_chunks] scratch
-  // isDockerFile scratch: candidate list and per-stripe line states (worst case: every file a candidate)
-  uint32_t* df_counters = nullptr;        // [2]
-  uint32_t *cand_file = nullptr, *cand_first = nullptr, *cand_err = nullptr;
+  // isDockerFile scratch: the FROM-first candidates (worst case: every file) and one word per 64 KiB
+  // tile of their bodies (the chained scan of k_df_body; tagged with `epoch`, so never cleared)
+  DfCounters* df_counters = nullptr;      // in the slab's zero region
+  uint32_t *cand_file = nullptr, *cand_tile0 = nullptr, *cand_err = nullptr, *cand_left = nullptr;
   uint64_t* cand_body = nullptr;
-  uint8_t *cand_esc = nullptr, *stripe_state = nullptr;
-  uint32_t stripe_cap = 0;
+  uint8_t* cand_esc = nullptr;
+  uint32_t* tile_state = nullptr;
+  uint32_t tile_cap = 0;
+  uint32_t epoch = 0;                     // pass number on this device tree (m2k_scan increments it)
   uint32_t* special = nullptr;            // [0] count, then ids of entries with a special name (compacted by k_name_features)
   uint32_t special_cap = 0;
+  // One allocation holds every array a pass starts from a known value, so that a pass begins with two
+  // memsets instead of nine: a zero region (dir_direct, dir_content, dir_subtree, file_flags, the
+  // isDockerFile counters, special[0]) followed by the list part of `special`, then an all-ones
+  // region (dir_first_war, dir_main, dir_main_sub: "none yet" for the MIN reductions).
+  uint8_t* slab = nullptr;
+  size_t slab_zero_bytes = 0, slab_ff_off = 0, slab_ff_bytes = 0;
   void* ign_blob = nullptr;               // ignore table + folded runes of the last finalize (grow-only)
   size_t ign_blob_cap = 0;
   uint32_t* entry_feat = nullptr;         // [n_entries]
@@ -147,12 +160,10 @@ struct Ctx {
 // ---- kernel launchers (kernels.cu) ----
 void launch_name_features(Ctx* c, DevTree* t);
 void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec);
-void launch_file_combine(Ctx* c, DevTree* t, const ChunkRec* chunk_rec);
-void launch_dockerfile(Ctx* c, DevTree* t);
-void launch_subtree(Ctx* c, DevTree* t, cudaStream_t st);
+void launch_file_phase(Ctx* c, DevTree* t, const ChunkRec* chunk_rec);
+void launch_df_body(Ctx* c, DevTree* t);
 void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st);
-void launch_combine_opts(Ctx* c, DevTree* t, uint32_t sh_flavor, cudaStream_t st);
-void launch_walk(Ctx* c, DevTree* t, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
+void launch_walk(Ctx* c, DevTree* t, uint32_t sh_flavor, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
                  const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore, cudaStream_t st);
 void fold_runes(const std::string& s, std::vector<uint32_t>* out);
 std::string fast_dir_path(const m2k_tree* t, uint32_t d, const std::string& clean_root);
