@@ -303,9 +303,9 @@ static void devtree_release(DevTree* t) {
   // dir_main_sub live inside the slab)
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
-                  t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->slab, t->dir_opts, t->dir_ignore, t->dir_state,
-                  t->dir_descend, t->cand_file, t->cand_tile0, t->cand_err, t->cand_left, t->cand_body,
-                  t->cand_esc, t->tile_state, t->ign_blob, t->pieces};
+                  t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->slab, t->early,
+                  t->dir_descend, t->head_list, t->cand_file, t->cand_stripe0, t->cand_err, t->cand_done, t->cand_body,
+                  t->cand_esc, t->stripe_state, t->tile_state, t->ign_blob, t->pieces};
   for (void* p : ptrs) if (p) cudaFree(p);
 }
 
@@ -325,6 +325,8 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
   devtree_release(&dt->t);
   free_devtree_shell(dt);
 }
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 template <typename T>
 static cudaError_t dev_alloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
@@ -417,18 +419,20 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne)); CU(dev_alloc(&t->pieces, 2));
   {
-    // isDockerFile scratch: a candidate per file at worst, a word per 64 KiB tile of candidate body
-    uint64_t cap = (t->shard_bytes + kDfTile - 1) / kDfTile + ns + 1;  // tiles over every file body, rounded up per file
-    if (cap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile tile table");
+    // isDockerFile scratch (DevTree): sized for the worst case, every file a candidate
+    uint64_t scap = (t->shard_bytes + kDfStripe - 1) / kDfStripe + ns + 1;  // stripes over every file body, rounded up per file
+    if (scap > 0xFFFFFFF0ull) return fail(C, M2K_ERR_LIMIT, "shard too large for the Dockerfile stripe table");
+    t->stripe_cap = (uint32_t)scap;
+    const uint64_t cap = scap / kDfTileStripes + 2;
     t->tile_cap = (uint32_t)cap;
-    CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_tile0, ns)); CU(dev_alloc(&t->cand_left, ns));
+    CU(dev_alloc(&t->head_list, ns)); CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_stripe0, ns)); CU(dev_alloc(&t->cand_done, ns));
     CU(dev_alloc(&t->cand_err, ns)); CU(dev_alloc(&t->cand_body, ns)); CU(dev_alloc(&t->cand_esc, ns));
-    CU(dev_alloc(&t->tile_state, cap));
+    CU(dev_alloc(&t->stripe_state, scap)); CU(dev_alloc(&t->tile_state, cap));
     CU(cudaMemsetAsync(t->tile_state, 0, 4ull * cap, C->stream));  // once: pass numbers start at 1
   }
   {
     // the slab (DevTree::slab): zero region, the list part of `special`, all-ones region
-    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    auto up = [](size_t x) { return align256(x); };
     const size_t nd4 = up(4ull * (nd ? nd : 1));
     size_t off = 0;
     const size_t o_direct = off; off += nd4;
@@ -450,12 +454,18 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
     t->dir_first_war = (uint32_t*)(t->slab + o_war); t->dir_main = (uint32_t*)(t->slab + o_main);
     t->dir_main_sub = (uint32_t*)(t->slab + o_main_sub);
   }
-  CU(dev_alloc(&t->dir_opts, nd)); CU(dev_alloc(&t->dir_ignore, nd));
-  CU(dev_alloc(&t->dir_state, nd)); CU(dev_alloc(&t->dir_descend, nd));
+  {
+    // what the walk produces early, in the order of the host result (one copy down): options, states, ignore flags
+    const size_t nd4 = align256(4ull * (nd ? nd : 1)), nd1 = align256(nd ? nd : 1);
+    CU(cudaMalloc((void**)&t->early, nd4 + 2 * nd1));
+    t->dir_opts = (uint32_t*)t->early; t->dir_state = t->early + nd4; t->dir_ignore = t->early + nd4 + nd1;
+    t->early_bytes = nd4 + 2 * nd1;
+  }
+  CU(dev_alloc(&t->dir_descend, nd));
 
   CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
   CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
-  CU(cudaHostAlloc((void**)&dt->h_results, 22ull * (nd ? nd : 1) + nf + 64, cudaHostAllocDefault));
+  CU(cudaHostAlloc((void**)&dt->h_results, 5 * align256(4ull * (nd ? nd : 1)) + 2 * align256(nd ? nd : 1) + nf + 256, cudaHostAllocDefault));
   t->special_cap = kSpecialCap;
   cudaStream_t s = C->stream;
   CU(cudaEventRecord(C->ev[0], s));
@@ -590,7 +600,7 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaStreamWaitEvent(s, C->ev_early, 0));  // ... and its directory-level kernels the arrays cleared below
   CU(cudaMemsetAsync(t->slab, 0, t->slab_zero_bytes, s));
   CU(cudaMemsetAsync(t->slab + t->slab_ff_off, 0xFF, t->slab_ff_bytes, s));
-  if (++t->epoch >= 0x7FFFFFFFu) {  // the tile table is tagged with the pass number: start over
+  if (++t->epoch >= 0x1FFFFFFFu) {  // the tile table is tagged with the pass number: start over
     CU(cudaMemsetAsync(t->tile_state, 0, 4ull * t->tile_cap, s));
     t->epoch = 1;
   }
@@ -607,11 +617,11 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   CU(cudaEventRecord(C->ev[2], s));
   dt->content = content;
   if (content) {
-    launch_scan_bytes(C, t, t->chunk_rec);
+    launch_scan_bytes(C, t, t->chunk_rec, &t->df_counters->scan_ticket);
     CU(cudaEventRecord(C->ev[3], s));
     launch_file_phase(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[9], s));
-    launch_df_body(C, t);
+    launch_dockerfile(C, t);
     CU(cudaEventRecord(C->ev[10], s));
   }
   CU(cudaGetLastError());
@@ -1077,15 +1087,15 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
     m2k_result* r = static_cast<m2k_result*>(calloc(1, sizeof(m2k_result)));
     r->n_dirs = nd; r->n_files = nf; r->n_entries = ne;
-    // layout of dt->h_results: five uint32 arrays of n_dirs, two byte arrays of n_dirs, one of n_files
+    // layout of dt->h_results: the device's early block (options, states, ignore flags) and its
+    // [dir_subtree | file_flags] stretch are mirrored, so that each comes down in one copy
+    const size_t nd4 = align256(4ull * (nd ? nd : 1)), nd1 = align256(nd ? nd : 1);
     uint8_t* b = dt->h_results;
-    r->dir_opts = (uint32_t*)b; b += 4ull * nd;
-    r->dir_direct = (uint32_t*)b; b += 4ull * nd;
-    r->dir_subtree = (uint32_t*)b; b += 4ull * nd;
-    r->dir_main_file = (uint32_t*)b; b += 4ull * nd;
-    r->service_dirs = (uint32_t*)b; b += 4ull * nd;
-    r->dir_state = b; b += nd;
-    r->dir_ignore = b; b += nd;
+    r->dir_opts = (uint32_t*)b; r->dir_state = b + nd4; r->dir_ignore = b + nd4 + nd1; b += nd4 + 2 * nd1;
+    r->dir_direct = (uint32_t*)b; b += nd4;
+    r->dir_main_file = (uint32_t*)b; b += nd4;
+    r->service_dirs = (uint32_t*)b; b += nd4;
+    r->dir_subtree = (uint32_t*)b; b += nd4;
     r->file_flags = b;
     r->entry_feat = dt->h_entry_feat;
     r->ignore_dirs = list_from_arenas(P.arenas, 1, &r->n_ignore_dirs);
@@ -1105,10 +1115,8 @@ static int prepare_ignore(Ctx* C, m2k_devtree* dt, const m2k_detect_params* para
     CU(cudaEventRecord(C->ev_side0, ss));
     launch_walk(C, t, P.sh_flavor, P.d_table, P.table_mask, P.d_runes, P.d_prefix, P.prefix_len, P.depth1_state, P.root_ignore, ss);
     CU(cudaEventRecord(C->ev_side1, ss));
-    CU(cudaMemcpyAsync(r->dir_opts, t->dir_opts, 4ull * nd, cudaMemcpyDeviceToHost, ss));
+    CU(cudaMemcpyAsync(r->dir_opts, t->early, t->early_bytes, cudaMemcpyDeviceToHost, ss));  // options, states, ignore flags
     CU(cudaMemcpyAsync(r->dir_direct, t->dir_direct, 4ull * nd, cudaMemcpyDeviceToHost, ss));
-    CU(cudaMemcpyAsync(r->dir_state, t->dir_state, nd, cudaMemcpyDeviceToHost, ss));
-    CU(cudaMemcpyAsync(r->dir_ignore, t->dir_ignore, nd, cudaMemcpyDeviceToHost, ss));
     CU(cudaEventRecord(C->ev_early, ss));
     CU(cudaGetLastError());
   }
@@ -1189,13 +1197,9 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaEventRecord(C->ev[4], s));
   launch_content_up(C, t, s);
   CU(cudaEventRecord(C->ev[5], s));
-  CU(cudaEventRecord(C->ev_fork, s));
-  CU(cudaStreamWaitEvent(C->copy_stream, C->ev_fork, 0));
-  CU(cudaMemcpyAsync(r->file_flags, t->file_flags, nf, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaEventRecord(C->ev_join, C->copy_stream));
-  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, 4ull * nd, cudaMemcpyDeviceToHost, s));
+  // dir_subtree and file_flags are neighbours in the slab and in the host block: one copy
+  CU(cudaMemcpyAsync(r->dir_subtree, t->dir_subtree, (size_t)(t->file_flags - (uint8_t*)t->dir_subtree) + nf, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(r->dir_main_file, t->dir_main_sub, 4ull * nd, cudaMemcpyDeviceToHost, s));
-  CU(cudaStreamWaitEvent(s, C->ev_join, 0));
   CU(cudaStreamWaitEvent(s, C->ev_feat, 0));  // r->entry_feat
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);

@@ -438,7 +438,10 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 // state from IN.  Stripes of the body compute their composed map (k_df_maps), a per-file scan turns
 // the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
 // lines that start inside it (k_df_validate).
-constexpr uint32_t kStripe = 256;   // == kDfStripe (m2k_internal.h)
+#ifndef M2K_DF_STRIPE
+#define M2K_DF_STRIPE 256
+#endif
+constexpr uint32_t kStripe = M2K_DF_STRIPE;   // == kDfStripe (m2k_internal.h)
 
 __device__ inline uint32_t line_map(const File& f, uint64_t lb, uint64_t le) {
   // from IN: comment and blank lines are dropped and the continuation goes on
@@ -458,19 +461,31 @@ __device__ __forceinline__ uint32_t map_compose(uint32_t first, uint32_t then) {
   return map_apply(then, map_apply(first, 0)) | (map_apply(then, map_apply(first, 1)) << 1);
 }
 
-// first physical-line start at or after `a` (a line starts at `body` or right after a '\n')
-__device__ inline uint64_t first_line_start(const File& f, uint64_t body, uint64_t a) {
+// first physical-line start in [a, b) (a line starts at `body` or right after a '\n'); >= b when no line
+// starts there -- the search never leaves the stripe, however long the line that runs through it
+__device__ inline uint64_t first_line_start(const File& f, uint64_t body, uint64_t a, uint64_t b) {
   if (a <= body) return body;
-  uint64_t q = a;
-  if (f.p[q - 1] == '\n') return q;
-  while (q < f.n && f.p[q] != '\n') q++;
+  uint64_t q = a - 1;  // a '\n' at a - 1 makes `a` itself a line start
+  const uint64_t end = b - 1 < f.n ? b - 1 : f.n;  // a '\n' at b - 1 starts a line at b: the next stripe's
+  while (q < end && (q & 7) && f.p[q] != '\n') q++;
+  if (q < end && !(q & 7) && f.p[q] != '\n') {
+    const uint64_t ones = 0x0101010101010101ull, nl = 0x0A0A0A0A0A0A0A0Aull;
+    for (;;) {  // aligned 8-byte words; the file is zero padded to 16 bytes, so a word never leaves it
+      uint64_t w = *reinterpret_cast<const uint64_t*>(f.p + q) ^ nl;
+      uint64_t z = (w - ones) & ~w & 0x8080808080808080ull;
+      if (z) { q += (uint64_t)(__ffsll((long long)z) - 1) >> 3; break; }
+      q += 8;
+      if (q >= end) break;
+    }
+  }
+  if (q >= end) return b;
   return q + 1;
 }
 
 // composed map of the lines that START in [a, b)
 __device__ inline uint32_t stripe_map(const File& f, uint64_t body, uint64_t a, uint64_t b) {
   uint32_t m = 0x2;  // identity: OUT->OUT, IN->IN
-  uint64_t q = first_line_start(f, body, a);
+  uint64_t q = first_line_start(f, body, a, b);
   while (q < b && q < f.n) {
     uint64_t le, next = phys_line(f, q, &le);
     m = map_compose(m, line_map(f, q, le));
@@ -481,7 +496,7 @@ __device__ inline uint32_t stripe_map(const File& f, uint64_t body, uint64_t a, 
 
 // checks every logical line that starts in [a, b), given the state at the first line start; false = parse error
 __device__ inline bool stripe_validate(const File& f, uint64_t body, uint64_t a, uint64_t b, uint32_t state) {
-  uint64_t q = first_line_start(f, body, a);
+  uint64_t q = first_line_start(f, body, a, b);
   while (q < b && q < f.n) {
     uint64_t le, next = phys_line(f, q, &le);
     if (state == 0) {

@@ -146,6 +146,9 @@ void launch_name_features(Ctx* c, DevTree* t) {
 #ifndef M2K_SCAN_WAVES
 #define M2K_SCAN_WAVES 32
 #endif
+#ifndef M2K_SCAN_TICKET
+#define M2K_SCAN_TICKET 1  // one resident wave of blocks, further chunks drawn from a counter (13.60 vs 13.75 ms on config C, 0.163 vs 0.171 on B)
+#endif
 constexpr int kScanRows = M2K_SCAN_ROWS;        // rows (512 B each) loaded before use
 constexpr int kScanThreads = M2K_SCAN_THREADS;
 
@@ -228,109 +231,251 @@ __device__ __noinline__ bool first_word_rules_out_dockerfile(uint4 v) {
   return false;
 }
 
-__global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes(
-    uint32_t n_chunks, uint32_t n_shard_files, const uint32_t* __restrict__ chunk_first,
-    const uint64_t* __restrict__ file_off, const uint64_t* __restrict__ file_len, uint32_t file_begin,
-    const uint8_t* __restrict__ bytes, uint64_t shard_byte0, uint32_t first_skip, ChunkRec* __restrict__ chunk_rec) {
+struct ScanArgs {
+  uint32_t n_chunks, n_shard_files;
+  const uint32_t* chunk_first; const uint64_t* file_off; const uint64_t* file_len;
+  uint32_t file_begin;
+  const uint8_t* bytes; uint64_t shard_byte0;
+  uint32_t first_skip;
+  ChunkRec* chunk_rec;
+  uint32_t* ticket;  // work items beyond the first wave are drawn from this counter (NULL: strided)
+};
+
+// where work item `item` (a 64 KiB chunk of one file) lies
+struct ChunkCtx {
+  const uint8_t* fbase;  // byte 0 of the file; may point before the shard, only [start - 16, ...) is touched
+  uint64_t flen, start;  // file length; offset of the chunk in the file
+  uint32_t range, n_units;
+  const uint4* src;
+};
+__device__ __forceinline__ ChunkCtx locate_chunk(const ScanArgs& a, uint32_t item) {
+  // which file: last f with chunk_first[f] <= item (empty files share their successor's value)
+  uint32_t lo = 0, hi = a.n_shard_files;
+  while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (a.chunk_first[mid] <= item) lo = mid; else hi = mid; }
+  const uint32_t f = a.file_begin + lo;
+  ChunkCtx c;
+  c.flen = a.file_len[f];
+  // the shard may begin `first_skip` chunks into its first file (the rest of it is on another GPU)
+  c.start = (uint64_t)(item - a.chunk_first[lo] + (lo == 0 ? a.first_skip : 0u)) * kChunkBytes;
+  c.fbase = a.bytes + (a.file_off[f] - a.shard_byte0);
+  c.range = (uint32_t)(c.flen - c.start < kChunkBytes ? c.flen - c.start : kChunkBytes);
+  c.n_units = (c.range + 15) >> 4;
+  c.src = reinterpret_cast<const uint4*>(c.fbase + c.start);
+  return c;
+}
+
+// Inside one 64 KiB chunk a newline-free run that is closed on both sides is shorter than 64 KiB,
+// so only the first and the last newline of the chunk matter: the first is looked for until it is
+// found, the last in the final batch of rows (walking back from there in the rare case it has none).
+struct ChunkAcc { uint32_t lead, last_nl, found, not_df; };  // byte offsets inside the chunk; M2K_NONE: not seen
+
+// one batch of kScanRows rows (row r, lane l holds unit u0 + r * 32 + l; units past the end are zero)
+__device__ __forceinline__ void scan_batch(const uint4 (&v)[kScanRows], uint32_t u0, uint32_t lane, const ChunkCtx& c, ChunkAcc& acc) {
+  if (c.start == 0 && u0 == 0 && lane == 0) acc.not_df = first_word_rules_out_dockerfile(v[0]) ? 1u : 0u;
+  bool hit_any = false;
+#pragma unroll
+  for (int r = 0; r < kScanRows; r++)
+    hit_any = hit_any || main_word(v[r].x) || main_word(v[r].y) || main_word(v[r].z) || main_word(v[r].w);
+  if (__any_sync(FULL, hit_any)) {  // rare: confirm bytewise, file bounds respected
+    bool ok = false;
+#pragma unroll
+    for (int r = 0; r < kScanRows; r++) {
+      uint64_t pos = c.start + (uint64_t)(u0 + r * 32 + lane) * 16;
+      if (main_word(v[r].x)) ok = ok || confirm_main(c.fbase, c.flen, pos);
+      if (main_word(v[r].y)) ok = ok || confirm_main(c.fbase, c.flen, pos + 4);
+      if (main_word(v[r].z)) ok = ok || confirm_main(c.fbase, c.flen, pos + 8);
+      if (main_word(v[r].w)) ok = ok || confirm_main(c.fbase, c.flen, pos + 12);
+    }
+    if (__any_sync(FULL, ok)) acc.found = 1;
+  }
+  if (acc.lead == M2K_NONE) {  // warp-uniform: first newline, rows in order
+#pragma unroll
+    for (int r = 0; r < kScanRows; r++) {
+      if (acc.lead == M2K_NONE) {
+        uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);  // rows past the end are zero: no newline
+        if (B) {
+          int l = __ffs(B) - 1;
+          acc.lead = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, first_nl_byte(v[r]), l);
+        }
+      }
+    }
+  }
+  if (u0 + 32 * kScanRows >= c.n_units) {  // warp-uniform: last newline, rows in reverse
+#pragma unroll
+    for (int r = kScanRows - 1; r >= 0; r--) {
+      if (acc.last_nl == M2K_NONE) {
+        uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);
+        if (B) {
+          int l = 31 - __clz(B);
+          acc.last_nl = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, last_nl_byte(v[r]), l);
+        }
+      }
+    }
+  }
+}
+
+// the chunk's 8-byte record, once all its batches are through
+__device__ __forceinline__ ChunkRec chunk_record(const ChunkCtx& c, ChunkAcc acc, uint32_t lane) {
+  uint32_t trail;
+  if (acc.lead == M2K_NONE) {
+    acc.lead = trail = c.range;  // no newline in the whole chunk
+  } else {
+    if (acc.last_nl == M2K_NONE) {
+      // the last batch has no newline (rare): walk back row by row; the newline at `lead` stops the search
+      uint32_t ubase = ((c.n_units - 1) / (32 * kScanRows)) * (32 * kScanRows);
+      while (acc.last_nl == M2K_NONE) {
+        ubase -= 32;
+        uint4 w = ldg_stream(c.src + ubase + lane);
+        uint32_t B = __ballot_sync(FULL, has_newline(w) != 0);
+        if (B) {
+          int l = 31 - __clz(B);
+          acc.last_nl = (ubase + l) * 16 + __shfl_sync(FULL, last_nl_byte(w), l);
+        }
+      }
+    }
+    trail = c.range - 1 - acc.last_nl;
+  }
+  return rec_pack(acc.lead, trail, acc.found, acc.not_df);
+}
+
+__global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes(ScanArgs a) {
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t warps_per_block = kScanThreads / 32;
   const uint32_t n_warps = gridDim.x * warps_per_block;
-  for (uint32_t item = blockIdx.x * warps_per_block + (threadIdx.x >> 5); item < n_chunks; item += n_warps) {
-    // which file: last f with chunk_first[f] <= item (empty files share their successor's value)
-    uint32_t lo = 0, hi = n_shard_files;
-    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (chunk_first[mid] <= item) lo = mid; else hi = mid; }
-    const uint32_t f = file_begin + lo;
-    const uint64_t flen = file_len[f];
-    // the shard may begin `first_skip` chunks into its first file (the rest of it is on another GPU)
-    const uint64_t start = (uint64_t)(item - chunk_first[lo] + (lo == 0 ? first_skip : 0u)) * kChunkBytes;
-    const uint8_t* fbase = bytes + (file_off[f] - shard_byte0);  // may point before the shard; only [start - 16, ...) is touched
-    const uint32_t range = (uint32_t)(flen - start < kChunkBytes ? flen - start : kChunkBytes);
-    const uint32_t n_units = (range + 15) >> 4;
-    const uint4* src = reinterpret_cast<const uint4*>(fbase + start);
-    // Inside one 64 KiB chunk a newline-free run that is closed on both sides is shorter than 64 KiB,
-    // so only the first and the last newline of the chunk matter: the first is looked for until it is
-    // found, the last in the final batch of rows (walking back from there in the rare case it has none).
-    uint32_t lead = M2K_NONE, last_nl = M2K_NONE, found = 0, not_df = 0;  // byte offsets inside the chunk
-    for (uint32_t u0 = 0; u0 < n_units; u0 += 32 * kScanRows) {
+  uint32_t item = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  while (item < a.n_chunks) {
+    const ChunkCtx c = locate_chunk(a, item);
+    ChunkAcc acc{M2K_NONE, M2K_NONE, 0, 0};
+    for (uint32_t u0 = 0; u0 < c.n_units; u0 += 32 * kScanRows) {
       uint4 v[kScanRows];
 #pragma unroll
       for (int r = 0; r < kScanRows; r++) {
         uint32_t u = u0 + r * 32 + lane;
-        v[r] = u < n_units ? ldg_stream(src + u) : make_uint4(0, 0, 0, 0);
+        v[r] = u < c.n_units ? ldg_stream(c.src + u) : make_uint4(0, 0, 0, 0);
       }
-      if (start == 0 && u0 == 0 && lane == 0) not_df = first_word_rules_out_dockerfile(v[0]) ? 1u : 0u;
-      bool hit_any = false;
-#pragma unroll
-      for (int r = 0; r < kScanRows; r++)
-        hit_any = hit_any || main_word(v[r].x) || main_word(v[r].y) || main_word(v[r].z) || main_word(v[r].w);
-      if (__any_sync(FULL, hit_any)) {  // rare: confirm bytewise, file bounds respected
-        bool ok = false;
-#pragma unroll
-        for (int r = 0; r < kScanRows; r++) {
-          uint64_t pos = start + (uint64_t)(u0 + r * 32 + lane) * 16;
-          if (main_word(v[r].x)) ok = ok || confirm_main(fbase, flen, pos);
-          if (main_word(v[r].y)) ok = ok || confirm_main(fbase, flen, pos + 4);
-          if (main_word(v[r].z)) ok = ok || confirm_main(fbase, flen, pos + 8);
-          if (main_word(v[r].w)) ok = ok || confirm_main(fbase, flen, pos + 12);
-        }
-        if (__any_sync(FULL, ok)) found = 1;
-      }
-      if (lead == M2K_NONE) {  // warp-uniform: first newline, rows in order
-#pragma unroll
-        for (int r = 0; r < kScanRows; r++) {
-          if (lead == M2K_NONE) {
-            uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);  // rows past the end are zero: no newline
-            if (B) {
-              int l = __ffs(B) - 1;
-              lead = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, first_nl_byte(v[r]), l);
-            }
-          }
-        }
-      }
-      if (u0 + 32 * kScanRows >= n_units) {  // warp-uniform: last newline, rows in reverse
-#pragma unroll
-        for (int r = kScanRows - 1; r >= 0; r--) {
-          if (last_nl == M2K_NONE) {
-            uint32_t B = __ballot_sync(FULL, has_newline(v[r]) != 0);
-            if (B) {
-              int l = 31 - __clz(B);
-              last_nl = (u0 + r * 32 + l) * 16 + __shfl_sync(FULL, last_nl_byte(v[r]), l);
-            }
-          }
-        }
-      }
+      scan_batch(v, u0, lane, c, acc);
     }
-    uint32_t trail;
-    if (lead == M2K_NONE) {
-      lead = trail = range;  // no newline in the whole chunk
+    const ChunkRec rec = chunk_record(c, acc, lane);
+    if (lane == 0) a.chunk_rec[item] = rec;
+    if (a.ticket) {  // chunks differ in size (the last chunk of a file): hand the rest out as warps come free
+      uint32_t nx = 0;
+      if (lane == 0) nx = n_warps + atomicAdd(a.ticket, 1u);
+      item = __shfl_sync(FULL, nx, 0);
     } else {
-      if (last_nl == M2K_NONE) {
-        // the last batch has no newline (rare): walk back row by row; the newline at `lead` stops the search
-        uint32_t ubase = ((n_units - 1) / (32 * kScanRows)) * (32 * kScanRows);
-        while (last_nl == M2K_NONE) {
-          ubase -= 32;
-          uint4 w = ldg_stream(src + ubase + lane);
-          uint32_t B = __ballot_sync(FULL, has_newline(w) != 0);
-          if (B) {
-            int l = 31 - __clz(B);
-            last_nl = (ubase + l) * 16 + __shfl_sync(FULL, last_nl_byte(w), l);
-          }
-        }
-      }
-      trail = range - 1 - last_nl;
+      item += n_warps;
     }
-    if (lane == 0) chunk_rec[item] = rec_pack(lead, trail, found, not_df);
   }
 }
 
-void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec) {
+// Measured alternative (tools/scan_variants.py, -DM2K_SCAN_BULK=1): the same scan fed by the bulk-copy
+// engine.  Every warp owns a ring of kBulkStages stages of one batch (kScanRows x 512 bytes) in shared
+// memory; lane 0 issues `cp.async.bulk` global -> shared copies that complete on the stage's mbarrier,
+// kBulkStages batches ahead of where the warp is reading, across chunk boundaries (the warp's
+// sequence of chunks is fixed: item, item + n_warps, ...).  Rows are then read from shared memory with
+// conflict-free 16-byte loads.
+#ifndef M2K_BULK_WARPS
+#define M2K_BULK_WARPS 16
+#endif
+#ifndef M2K_BULK_STAGES
+#define M2K_BULK_STAGES 3
+#endif
+constexpr uint32_t kBulkWarps = M2K_BULK_WARPS, kBulkStages = M2K_BULK_STAGES;
+constexpr uint32_t kBulkStageBytes = kScanRows * 512;
+constexpr size_t kBulkSmem = (size_t)kBulkWarps * kBulkStages * (kBulkStageBytes + 8);
+static_assert(kBulkSmem <= 227 * 1024, "the rings of one block must fit the SM's shared memory");
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n .reg .pred p;\n WAIT_%=:\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      " @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// a cursor over the batches of a warp's chunk sequence
+struct BatchCursor { uint32_t item, u0; ChunkCtx c; };
+
+__global__ void __launch_bounds__(kBulkWarps * 32, 1) k_scan_bytes_bulk(ScanArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t n_warps = gridDim.x * kBulkWarps;
+  uint8_t* ring = smem + (size_t)warp * kBulkStages * kBulkStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kBulkWarps * kBulkStages * kBulkStageBytes) + warp * kBulkStages;
+  if (lane == 0) for (uint32_t st = 0; st < kBulkStages; st++) mbar_init(&bars[st], 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncwarp();
+  const uint32_t first = blockIdx.x * kBulkWarps + warp;
+  if (first >= a.n_chunks) return;
+  // the fetch cursor runs kBulkStages batches ahead of the read cursor
+  BatchCursor fc{first, 0, locate_chunk(a, first)};
+  auto issue = [&](uint32_t stage) {  // copy the fetch cursor's batch into `stage`, advance the cursor
+    if (fc.item >= a.n_chunks) return;
+    if (fc.c.n_units == 0) {  // cannot happen (an empty file has no chunk), kept for safety
+      fc.item = a.n_chunks; return;
+    }
+    const uint32_t units = fc.c.n_units - fc.u0 < 32u * kScanRows ? fc.c.n_units - fc.u0 : 32u * kScanRows;
+    if (lane == 0) bulk_load(ring + (size_t)stage * kBulkStageBytes, fc.c.src + fc.u0, units * 16, &bars[stage]);
+    fc.u0 += 32 * kScanRows;
+    if (fc.u0 >= fc.c.n_units) {
+      fc.item += n_warps; fc.u0 = 0;
+      if (fc.item < a.n_chunks) fc.c = locate_chunk(a, fc.item);
+    }
+  };
+  for (uint32_t st = 0; st < kBulkStages; st++) issue(st);
+  uint32_t stage = 0, parity = 0;
+  for (uint32_t item = first; item < a.n_chunks; item += n_warps) {
+    const ChunkCtx c = locate_chunk(a, item);
+    ChunkAcc acc{M2K_NONE, M2K_NONE, 0, 0};
+    for (uint32_t u0 = 0; u0 < c.n_units; u0 += 32 * kScanRows) {
+      mbar_wait(&bars[stage], parity);
+      const uint4* rows = reinterpret_cast<const uint4*>(ring + (size_t)stage * kBulkStageBytes);
+      uint4 v[kScanRows];
+#pragma unroll
+      for (int r = 0; r < kScanRows; r++) {
+        uint32_t u = u0 + r * 32 + lane;
+        v[r] = u < c.n_units ? rows[r * 32 + lane] : make_uint4(0, 0, 0, 0);
+      }
+      __syncwarp();  // every lane has its rows in registers: the stage can be refilled
+      issue(stage);
+      if (++stage == kBulkStages) { stage = 0; parity ^= 1; }
+      scan_batch(v, u0, lane, c, acc);
+    }
+    const ChunkRec rec = chunk_record(c, acc, lane);
+    if (lane == 0) a.chunk_rec[item] = rec;
+  }
+}
+
+void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket) {
   if (!t->n_chunks) return;
+  ScanArgs a{t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off, t->file_len, t->file_begin,
+             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket};
+#if defined(M2K_SCAN_BULK) && M2K_SCAN_BULK
+  static bool attr_set = false;
+  if (!attr_set) { cudaFuncSetAttribute(k_scan_bytes_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBulkSmem); attr_set = true; }
+  uint32_t want = (t->n_chunks + kBulkWarps - 1) / kBulkWarps;
+  uint32_t cap = (uint32_t)c->sm_count;  // one block per SM, persistent over its warps' chunk sequences
+  a.ticket = nullptr;
+  k_scan_bytes_bulk<<<want < cap ? want : cap, kBulkWarps * 32, kBulkSmem, c->stream>>>(a);
+#else
   uint32_t warps_per_block = kScanThreads / 32;
   uint32_t want = (t->n_chunks + warps_per_block - 1) / warps_per_block;
   uint32_t cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS * M2K_SCAN_WAVES;  // resident blocks x waves
+#if M2K_SCAN_TICKET
+  if (a.ticket) cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS;  // one resident wave; the rest is drawn from the counter
+#else
+  a.ticket = nullptr;
+#endif
   uint32_t blocks = want < cap ? want : cap;
-  k_scan_bytes<<<blocks, kScanThreads, 0, c->stream>>>(t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off,
-                                                       t->file_len, t->file_begin, t->bytes, t->shard_byte0, t->first_skip, chunk_rec);
+  k_scan_bytes<<<blocks, kScanThreads, 0, c->stream>>>(a);
+#endif
   c->launches++;
 }
 
@@ -367,12 +512,7 @@ __host__ __device__ __forceinline__ uint32_t acc_long(uint64_t bytes, uint64_t l
 
 constexpr uint32_t kCombineWarpChunks = 128;  // files with more chunks are folded by the whole warp
 
-// isDockerFile works on the candidates' bodies in tiles of 256 stripes of 256 bytes (64 KiB): one
-// block per tile, one thread per stripe (k_df_body)
-constexpr uint32_t kDfTileStripes = 256;
-constexpr uint32_t kDfTileBytes = kDfTileStripes * df::kStripe;
-
-// everything the per-file kernels (combine + head, body tiles) look at
+// everything the per-file kernels (combine, Dockerfile heads, body stripes) look at
 struct FileArgs {
   uint32_t n_shard_files, file_begin, first_skip, last_end;  // chunks of the first file before the shard; end chunk of the last file (M2K_NONE: all)
   const uint32_t* chunk_first; const ChunkRec* chunk_rec;
@@ -380,10 +520,12 @@ struct FileArgs {
   const uint32_t* file_entry; const uint32_t* entry_dir; const uint32_t* entry_name_off; const uint8_t* names;
   uint8_t* file_flags; uint32_t* dir_content; uint32_t* dir_main;
   PieceSummary* pieces;  // [2]: the shard's first / last file when only part of it is here
-  // isDockerFile scratch: FROM-first candidates and their body tiles
+  // isDockerFile scratch
   DfCounters* ctr;
-  uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_tile0; uint32_t* cand_err; uint32_t* cand_left;
-  uint32_t* tile_state;  // per tile: (epoch << 1) | line state at the end of the tile
+  uint32_t* head_list;   // shard-local indices of the files whose head must be parsed
+  uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_stripe0; uint32_t* cand_err; uint32_t* cand_done;
+  uint8_t* stripe_state; // per 256-byte stripe of candidate body: the line state at its first line start
+  uint32_t* tile_state;  // per tile of 256 stripes: (pass number << 3) | 4: end state known | map (2 bits) or end state (bit 0)
   uint32_t epoch;
 };
 
@@ -421,53 +563,27 @@ __device__ __forceinline__ void note_dockerfile(const FileArgs& a, uint32_t f) {
 }
 
 // i: index of the file in the shard.  A file all of whose chunks are here gets its final HAS_MAIN /
-// LONG_LINE flags, and its head is parsed for isDockerFile right away (nearly every file was already
-// ruled out by the scan kernel's look at its first word; a FROM-first file becomes a candidate whose
-// body k_df_body validates).  The part of a file that continues on another GPU becomes a piece
-// summary for k_merge_pieces instead; when that part starts the file, its head is settled as far as
-// it can be from here.
-__device__ __noinline__ void finish_file(const FileArgs& a, uint32_t i, uint32_t f, const RunAcc& tot, uint64_t len,
-                                         uint32_t has_main, uint32_t not_df) {
+// LONG_LINE flags; the part of a file that continues on another GPU becomes a piece summary for
+// k_merge_pieces instead.  Nearly every file was already ruled out as a Dockerfile by the scan
+// kernel's look at its first word; the others are listed for k_df_head.
+__device__ __forceinline__ void finish_file(const FileArgs& a, uint32_t i, uint32_t f, const RunAcc& tot, uint64_t len,
+                                            uint32_t has_main, uint32_t not_df) {
   const bool cut_front = i == 0 && a.first_skip != 0;
   const bool cut_back = i + 1 == a.n_shard_files && a.last_end != M2K_NONE;
-  const uint8_t* fbytes = a.bytes + (a.file_off[f] - a.shard_byte0);
-  uint64_t body = 0;
-  uint32_t esc = '\\';
   if (cut_front || cut_back) {
     PieceSummary ps;
     ps.file = f;
     ps.flags = (has_main ? PIECE_HAS_MAIN : 0u) | (tot.longf ? PIECE_LONG : 0u) | (cut_front ? 0u : PIECE_FIRST) | (not_df ? PIECE_NOT_DF : 0u);
     ps.bytes = tot.bytes; ps.lead = tot.lead; ps.trail = tot.trail;
-    if (!cut_front && !not_df) {
-      // the body of a FROM-first file cannot be validated from a piece (see k_merge_pieces)
-      const uint64_t n_here = (uint64_t)a.last_end * kChunkBytes;  // cut_back holds, so this is < len
-      bool touched_end = false;
-      const bool from = df::head(fbytes, n_here, false, &body, &esc, &touched_end);
-      ps.flags |= touched_end ? PIECE_HEAD_TRUNC : (from ? PIECE_HEAD_FROM : PIECE_HEAD_NOT_FROM);
-    }
     a.pieces[i == 0 ? 0 : 1] = ps;
     a.file_flags[f] = 0;
+    if (!cut_front && !not_df) a.head_list[atomicAdd(&a.ctr->n_heads, 1u)] = i;  // this part starts the file: its head can be looked at
     return;
   }
   const uint32_t longf = acc_long(tot.bytes, tot.lead, tot.trail, tot.longf);
-  uint32_t flags = (has_main ? M2K_FILE_HAS_MAIN : 0u) | (longf ? M2K_FILE_LONG_LINE : 0u);
+  a.file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0u) | (longf ? M2K_FILE_LONG_LINE : 0u));
   if (has_main) note_main_file(f, a.file_entry, a.entry_dir, a.entry_name_off, a.names, a.dir_content, a.dir_main);
-  if (!not_df && df::head(fbytes, len, longf != 0, &body, &esc)) {
-    flags |= M2K_FILE_FROM_FIRST;
-    const uint64_t n_tiles = (len - body + kDfTileBytes - 1) / kDfTileBytes;
-    if (n_tiles == 0) {  // nothing after the FROM line: nothing left that could fail to parse
-      flags |= M2K_FILE_DOCKERFILE;
-      note_dockerfile(a, f);
-    } else {
-      // candidate number and first tile number from ONE counter (high / low half), so that the tile
-      // offsets increase with the candidate number and a tile finds its candidate by bisection
-      const unsigned long long old = atomicAdd(&a.ctr->cand_tiles, (1ull << 32) | n_tiles);
-      const uint32_t c = (uint32_t)(old >> 32);
-      a.cand_file[c] = f; a.cand_body[c] = body; a.cand_esc[c] = (uint8_t)esc;
-      a.cand_tile0[c] = (uint32_t)old; a.cand_err[c] = 0; a.cand_left[c] = (uint32_t)n_tiles;
-    }
-  }
-  a.file_flags[f] = (uint8_t)flags;
+  if (!not_df && !longf && len) a.head_list[atomicAdd(&a.ctr->n_heads, 1u)] = i;  // a long line fails the parse anyway
 }
 
 __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
@@ -515,21 +631,61 @@ __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Kernel 4: the bodies of the isDockerFile candidates (dockerfile_dev.cuh) in ONE launch, whatever
-// their size.  A tile is 256 stripes of 256 bytes; blocks draw tile numbers from a counter, one
-// thread per stripe:
-//   1. every thread composes the line-state map of its stripe (does a physical line start a logical
-//      line? one bit of state carried from the line before), a block scan composes them;
-//   2. the tile waits for the state at the end of the tile before it (published in tile_state,
-//      tagged with the pass number so that the table never needs clearing) and publishes its own at
-//      once -- a chained scan: the maps of all tiles are computed in parallel, only one word per
-//      tile travels along the file, so a body of hundreds of MB is bounded by its tile count times a
-//      flag round trip, not walked by one thread;
-//   3. every thread checks the logical lines starting in its stripe (ENV / LABEL / ONBUILD syntax);
-//   4. the block that finishes a candidate's last tile sets its DOCKERFILE bit.
-// Tickets are handed out in order and a block holds a ticket only while it is running, so the tile a
-// block waits for is always held by a running block: no deadlock, whatever the grid size.
+// Kernel 4: isDockerFile (dockerfile_dev.cuh) in three launches, none of which ever has a thread walk
+// a whole file, and all of which work on dense lists (grids are multiples of the SM count and read
+// their sizes from device memory, so the host never waits for a count):
+//   k_df_head     one thread per listed file: directives, comments, ARGs, first instruction.
+//                 FROM-first files become candidates; a candidate's number and the number of its
+//                 first 256-byte body stripe come from ONE 64-bit counter (high / low half), so the
+//                 stripe offsets grow with the candidate number and a stripe finds its candidate
+//                 by bisection -- no prefix-sum launch.
+//   k_df_states   one thread per stripe, in tiles of 256 consecutive stripes (whatever candidates
+//                 they belong to) drawn from a counter: the composed line-state map of each stripe
+//                 (does a physical line start a logical line?  one bit carried from the line
+//                 before), a segmented block scan, and a decoupled look-back over the tiles before
+//                 it for the state a body that began in an earlier tile arrives with.  A tile
+//                 publishes its map at once and its end state as soon as it knows it (tagged with
+//                 the pass number: the table is never cleared); tickets are handed out in order and
+//                 a block holds one only while it runs, so the tile a block waits for is always
+//                 held by a running block.  A body of hundreds of MB costs its tiles a few flag
+//                 reads each: nothing walks it serially.
+//   k_df_validate one thread per stripe: ENV / LABEL / ONBUILD syntax of the logical lines that
+//                 start in it; the thread that completes a candidate's last stripe sets its
+//                 DOCKERFILE bit and the directory's content bit.
 // ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_df_head(FileArgs a) {
+  const uint32_t n = a.ctr->n_heads;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const uint32_t i = a.head_list[j], f = a.file_begin + i;
+    const uint8_t* fbytes = a.bytes + (a.file_off[f] - a.shard_byte0);
+    const uint64_t len = a.file_len[f];
+    uint64_t body = 0;
+    uint32_t esc = '\\';
+    if (i + 1 == a.n_shard_files && a.last_end != M2K_NONE) {
+      // only the first part of this file is here: settle what its head can settle; the body of a
+      // FROM-first file cannot be validated from a piece (see k_merge_pieces)
+      const uint64_t n_here = (uint64_t)a.last_end * kChunkBytes;  // < len
+      bool touched_end = false;
+      const bool from = df::head(fbytes, n_here, false, &body, &esc, &touched_end);
+      a.pieces[i == 0 ? 0 : 1].flags |= touched_end ? PIECE_HEAD_TRUNC : (from ? PIECE_HEAD_FROM : PIECE_HEAD_NOT_FROM);
+      continue;
+    }
+    if (!df::head(fbytes, len, false, &body, &esc)) continue;
+    uint32_t flags = a.file_flags[f] | M2K_FILE_FROM_FIRST;
+    const uint64_t n_stripes = (len - body + df::kStripe - 1) / df::kStripe;
+    if (n_stripes == 0) {  // nothing after the FROM line: nothing left that could fail to parse
+      flags |= M2K_FILE_DOCKERFILE;
+      note_dockerfile(a, f);
+    } else {
+      const unsigned long long old = atomicAdd(&a.ctr->cand_stripes, (1ull << 32) | n_stripes);
+      const uint32_t c = (uint32_t)(old >> 32);
+      a.cand_file[c] = f; a.cand_body[c] = body; a.cand_esc[c] = (uint8_t)esc;
+      a.cand_stripe0[c] = (uint32_t)old; a.cand_err[c] = 0; a.cand_done[c] = 0;
+    }
+    a.file_flags[f] = (uint8_t)flags;
+  }
+}
+
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -539,60 +695,129 @@ __device__ __forceinline__ void st_release(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(kDfTileStripes) k_df_body(FileArgs a) {
+// stripe s: its candidate, and the byte range [lo, hi) of the body it covers
+struct StripeRef { uint32_t c, k; uint64_t body, lo, hi; };
+__device__ __forceinline__ StripeRef df_stripe(const FileArgs& a, uint32_t n_cand, uint32_t s) {
+  uint32_t c = 0, h = n_cand;  // the last candidate whose first stripe is <= s
+  while (h - c > 1) { uint32_t m = (c + h) >> 1; if (a.cand_stripe0[m] <= s) c = m; else h = m; }
+  StripeRef r;
+  r.c = c; r.k = s - a.cand_stripe0[c];
+  r.body = a.cand_body[c];
+  r.lo = r.body + (uint64_t)r.k * df::kStripe;
+  const uint64_t n = a.file_len[a.cand_file[c]];
+  r.hi = r.lo + df::kStripe < n ? r.lo + df::kStripe : n;
+  return r;
+}
+__device__ __forceinline__ df::File df_file(const FileArgs& a, uint32_t c) {
+  const uint32_t f = a.cand_file[c];
+  return df::File{a.bytes + (a.file_off[f] - a.shard_byte0), a.file_len[f], a.cand_esc[c]};
+}
+
+// segmented scan element: a line-state map and "a body starts at or before this stripe inside the span"
+__device__ __forceinline__ uint32_t seg_join(uint32_t first, uint32_t then) {  // bit 2 = segment flag, bits 0-1 = map
+  if (then & 4u) return then;
+  return (first & 4u) | df::map_compose(first & 3u, then & 3u);
+}
+
+__global__ void __launch_bounds__(kDfTileStripes) k_df_states(FileArgs a) {
   __shared__ uint32_t s_ticket, s_in;
-  __shared__ uint32_t s_warp_map[kDfTileStripes / 32];
+  __shared__ uint32_t s_warp[kDfTileStripes / 32];
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned long long ct = a.ctr->cand_tiles;  // final: k_file_combine has finished
-  const uint32_t n_cand = (uint32_t)(ct >> 32), n_tiles = (uint32_t)ct;
+  const unsigned long long cs = a.ctr->cand_stripes;  // final: k_df_head has finished
+  const uint32_t n_cand = (uint32_t)(cs >> 32), n_stripes = (uint32_t)cs;
+  const uint32_t n_tiles = (n_stripes + kDfTileStripes - 1) / kDfTileStripes;
+  const uint32_t tag = a.epoch << 3;
   for (;;) {
     if (tid == 0) s_ticket = atomicAdd(&a.ctr->next_tile, 1u);
     __syncthreads();
     const uint32_t t = s_ticket;
     if (t >= n_tiles) break;
-    uint32_t c = 0, h = n_cand;  // the last candidate whose first tile is <= t
-    while (h - c > 1) { uint32_t m = (c + h) >> 1; if (a.cand_tile0[m] <= t) c = m; else h = m; }
-    const uint32_t k = t - a.cand_tile0[c], f = a.cand_file[c];
-    const df::File file{a.bytes + (a.file_off[f] - a.shard_byte0), a.file_len[f], a.cand_esc[c]};
-    const uint64_t body = a.cand_body[c];
-    const uint64_t lo = body + (uint64_t)k * kDfTileBytes + (uint64_t)tid * df::kStripe;
-    const bool live = lo < file.n;
-    const uint64_t hi = lo + df::kStripe < file.n ? lo + df::kStripe : file.n;
-    const uint32_t m = live ? df::stripe_map(file, body, lo, hi) : 0x2u;  // identity past the end
-    uint32_t inc = m;  // inclusive scan (composition, earlier stripe first) over the warp
+    const uint32_t s = t * kDfTileStripes + tid;
+    const bool live = s < n_stripes;
+    uint32_t el = 0x2u;  // identity map, no segment start
+    if (live) {
+      const StripeRef r = df_stripe(a, n_cand, s);
+      el = df::stripe_map(df_file(a, r.c), r.body, r.lo, r.hi) | (r.k == 0 ? 4u : 0u);
+    }
+    uint32_t inc = el;  // inclusive segmented scan over the warp (earlier stripe first)
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const uint32_t o = __shfl_up_sync(FULL, inc, d);
-      if ((int)lane >= d) inc = df::map_compose(o, inc);
+      if ((int)lane >= d) inc = seg_join(o, inc);
     }
     uint32_t exc = __shfl_up_sync(FULL, inc, 1);
     if (lane == 0) exc = 0x2u;
-    if (lane == 31) s_warp_map[warp] = inc;
+    if (lane == 31) s_warp[warp] = inc;
     __syncthreads();
     uint32_t pre = 0x2u;
-    for (uint32_t w = 0; w < warp; w++) pre = df::map_compose(pre, s_warp_map[w]);
-    exc = df::map_compose(pre, exc);
-    if (tid == 0) {
+    for (uint32_t w = 0; w < warp; w++) pre = seg_join(pre, s_warp[w]);
+    exc = seg_join(pre, exc);  // everything before this stripe in the tile
+    if (warp == 0) {
       uint32_t agg = 0x2u;
-      for (uint32_t w = 0; w < kDfTileStripes / 32; w++) agg = df::map_compose(agg, s_warp_map[w]);
-      uint32_t sin = 0;  // a body starts outside any continuation
-      if (k != 0) {
-        uint32_t v;
-        while (((v = ld_acquire(a.tile_state + (t - 1))) >> 1) != a.epoch) __nanosleep(40);
-        sin = v & 1u;
+      for (uint32_t w = 0; w < kDfTileStripes / 32; w++) agg = seg_join(agg, s_warp[w]);
+      // the state the tile's first stripe starts in: 0 when a body starts right there, else what the
+      // tiles before it leave behind
+      const bool starts_body = (__shfl_sync(FULL, el, 0) & 4u) != 0;  // lane 0 of warp 0 is stripe 0 of the tile
+      uint32_t sin = 0;
+      if (agg & 4u) {
+        // a body starts inside this tile: what the tile leaves behind does not depend on what came in
+        if (lane == 0) st_release(a.tile_state + t, tag | 4u | df::map_apply(agg & 3u, 0u));
+      } else if (lane == 0) {
+        st_release(a.tile_state + t, tag | (agg & 3u));  // bit 2 clear: a map, the end state is not known yet
       }
-      st_release(a.tile_state + t, (a.epoch << 1) | df::map_apply(agg, sin));
-      s_in = sin;
+      if (!starts_body && t != 0) {
+        uint32_t suffix = 0x2u;  // composed map of the tiles between the window and this one
+        for (uint32_t back = 1, done = 0; !done; back += 32) {
+          const bool in_range = back + lane <= t;
+          uint32_t v = 0;
+          if (in_range) while (((v = ld_acquire(a.tile_state + (t - back - lane))) >> 3) != a.epoch) __nanosleep(20);
+          const uint32_t known = __ballot_sync(FULL, in_range && (v & 4u));  // nearest tile (lowest lane) whose end state is known
+          const uint32_t stop = known ? (uint32_t)(__ffs(known) - 1) : 32u;
+          uint32_t window = 0x2u;  // maps of lanes stop-1 .. 0 in file order (farther tile first)
+          for (int l = 31; l >= 0; l--) {
+            const uint32_t mv = __shfl_sync(FULL, v, l);
+            if ((uint32_t)l < stop && back + (uint32_t)l <= t) window = df::map_compose(window, mv & 3u);
+          }
+          suffix = df::map_compose(window, suffix);
+          if (known) { sin = df::map_apply(suffix, __shfl_sync(FULL, v, stop) & 1u); done = 1; }
+          else if (back + 32 > t) { sin = df::map_apply(suffix, 0u); done = 1; }  // cannot happen: tile 0 starts a body
+        }
+      }
+      if (lane == 0) {
+        if (!(agg & 4u)) st_release(a.tile_state + t, tag | 4u | df::map_apply(agg & 3u, sin));
+        s_in = sin;
+      }
     }
     __syncthreads();
-    const bool ok = !live || df::stripe_validate(file, body, lo, hi, df::map_apply(exc, s_in));
-    const int bad = __syncthreads_or(!ok);
-    if (tid == 0) {
-      if (bad) atomicExch(&a.cand_err[c], 1u);
+    // this stripe's own start state: from the start of its body when that lies in the tile, else from the tile's
+    if (live) a.stripe_state[s] = (el & 4u) ? (uint8_t)0 : (uint8_t)df::map_apply(exc & 3u, (exc & 4u) ? 0u : s_in);
+  }
+}
+
+__global__ void __launch_bounds__(128) k_df_validate(FileArgs a) {
+  const unsigned long long cs = a.ctr->cand_stripes;
+  const uint32_t n_cand = (uint32_t)(cs >> 32), n_stripes = (uint32_t)cs;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t n_round = (n_stripes + 31) & ~31u;  // whole warps stay together for the vote below
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
+    const bool live = s < n_stripes;
+    uint32_t c = M2K_NONE;
+    if (live) {
+      const StripeRef r = df_stripe(a, n_cand, s);
+      c = r.c;
+      if (!df::stripe_validate(df_file(a, c), r.body, r.lo, r.hi, a.stripe_state[s])) atomicExch(&a.cand_err[c], 1u);
+    }
+    // count finished stripes per candidate, one atomic per (warp, candidate); whoever completes a
+    // candidate publishes its verdict
+    const uint32_t peers = __match_any_sync(FULL, c);
+    if (live && (uint32_t)(__ffs(peers) - 1) == lane) {
+      const uint32_t mine = (uint32_t)__popc(peers);
+      const uint32_t total = (c + 1 < n_cand ? a.cand_stripe0[c + 1] : n_stripes) - a.cand_stripe0[c];
       __threadfence();
-      if (atomicSub(&a.cand_left[c], 1u) == 1u) {  // this was the candidate's last open tile
+      if (atomicAdd(&a.cand_done[c], mine) + mine == total) {
         __threadfence();
         if (atomicAdd(&a.cand_err[c], 0u) == 0u) {
+          const uint32_t f = a.cand_file[c];
           a.file_flags[f] |= M2K_FILE_DOCKERFILE;
           note_dockerfile(a, f);
         }
@@ -604,11 +829,11 @@ __global__ void __launch_bounds__(kDfTileStripes) k_df_body(FileArgs a) {
 static FileArgs file_args(DevTree* t, const ChunkRec* chunk_rec) {
   return FileArgs{t->file_end - t->file_begin, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec,
                   t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
-                  t->file_flags, t->dir_content, t->dir_main, t->pieces, t->df_counters, t->cand_file, t->cand_body, t->cand_esc,
-                  t->cand_tile0, t->cand_err, t->cand_left, t->tile_state, t->epoch};
+                  t->file_flags, t->dir_content, t->dir_main, t->pieces, t->df_counters, t->head_list, t->cand_file, t->cand_body,
+                  t->cand_esc, t->cand_stripe0, t->cand_err, t->cand_done, t->stripe_state, t->tile_state, t->epoch};
 }
 
-// per-file combine + Dockerfile heads, then the candidates' bodies: two launches
+// per-file combine, then isDockerFile: heads, stripe states, validation
 void launch_file_phase(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
   uint32_t nf = t->file_end - t->file_begin;
   cudaMemsetAsync(t->pieces, 0xFF, 2 * sizeof(PieceSummary), c->stream);  // file == M2K_NONE: unused slot
@@ -617,11 +842,13 @@ void launch_file_phase(Ctx* c, DevTree* t, const ChunkRec* chunk_rec) {
   k_file_combine<<<(nf + 255) / 256, 256, 0, c->stream>>>(a);
   c->launches++;
 }
-void launch_df_body(Ctx* c, DevTree* t) {
+void launch_dockerfile(Ctx* c, DevTree* t) {
   if (t->file_end == t->file_begin) return;
   FileArgs a = file_args(t, nullptr);
-  k_df_body<<<c->sm_count * 4, kDfTileStripes, 0, c->stream>>>(a);
-  c->launches++;
+  k_df_head<<<c->sm_count * 8, 128, 0, c->stream>>>(a);
+  k_df_states<<<c->sm_count * 4, kDfTileStripes, 0, c->stream>>>(a);
+  k_df_validate<<<c->sm_count * 8, 128, 0, c->stream>>>(a);
+  c->launches += 3;
 }
 
 // ---------------------------------------------------------------------------------------------

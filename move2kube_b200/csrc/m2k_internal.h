@@ -11,8 +11,11 @@ namespace m2k {
 
 constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
-constexpr uint32_t kDfStripe = 256;      // bytes of one stripe of the parallel Dockerfile validation
-constexpr uint32_t kDfTile = 256 * kDfStripe;  // bytes of one tile (one block of k_df_body)
+#ifndef M2K_DF_STRIPE
+#define M2K_DF_STRIPE 256
+#endif
+constexpr uint32_t kDfStripe = M2K_DF_STRIPE;  // bytes of one stripe of the parallel Dockerfile validation
+constexpr uint32_t kDfTileStripes = 256;  // stripes per tile (one block of k_df_states)
 constexpr uint32_t kLongLine = 65536;    // bufio.MaxScanTokenSize: a line of >= this many bytes fails
 // per-chunk record written by the byte-scan kernel: scratch memory, 8 bytes per 64 KiB chunk, exact
 // to the byte so that records of one file can be stitched anywhere (another kernel, another GPU)
@@ -50,7 +53,7 @@ enum : uint32_t {
 
 // counters of the isDockerFile phase: candidates in the high half and body tiles in the low half of
 // ONE word (so both numberings grow together), and the next tile ticket
-struct DfCounters { unsigned long long cand_tiles; uint32_t next_tile; uint32_t _pad; };
+struct DfCounters { unsigned long long cand_stripes; uint32_t next_tile; uint32_t scan_ticket; uint32_t n_heads; uint32_t _pad; };  // scan_ticket: see ScanArgs::ticket
 
 // name signature table staged into shared memory by the name-feature kernel
 struct NameSig {
@@ -96,14 +99,15 @@ struct DevTree {
   uint64_t* synth_inject = nullptr;
   // work buffers
   ChunkRec* chunk_rec = nullptr;          // [n_chunks] scratch
-  // isDockerFile scratch: the FROM-first candidates (worst case: every file) and one word per 64 KiB
-  // tile of their bodies (the chained scan of k_df_body; tagged with `epoch`, so never cleared)
+  // isDockerFile scratch: the files whose head must be parsed and the FROM-first candidates among
+  // them (worst case: every file), one byte per 256-byte stripe of candidate body (worst case: every
+  // byte of the shard), one word per tile of 256 stripes (tagged with `epoch`, so never cleared)
   DfCounters* df_counters = nullptr;      // in the slab's zero region
-  uint32_t *cand_file = nullptr, *cand_tile0 = nullptr, *cand_err = nullptr, *cand_left = nullptr;
+  uint32_t *head_list = nullptr, *cand_file = nullptr, *cand_stripe0 = nullptr, *cand_err = nullptr, *cand_done = nullptr;
   uint64_t* cand_body = nullptr;
-  uint8_t* cand_esc = nullptr;
+  uint8_t *cand_esc = nullptr, *stripe_state = nullptr;
   uint32_t* tile_state = nullptr;
-  uint32_t tile_cap = 0;
+  uint32_t stripe_cap = 0, tile_cap = 0;
   uint32_t epoch = 0;                     // pass number on this device tree (m2k_scan increments it)
   uint32_t* special = nullptr;            // [0] count, then ids of entries with a special name (compacted by k_name_features)
   uint32_t special_cap = 0;
@@ -111,6 +115,8 @@ struct DevTree {
   // memsets instead of nine: a zero region (dir_direct, dir_content, dir_subtree, file_flags, the
   // isDockerFile counters, special[0]) followed by the list part of `special`, then an all-ones
   // region (dir_first_war, dir_main, dir_main_sub: "none yet" for the MIN reductions).
+  uint8_t* early = nullptr;               // dir_opts | dir_state | dir_ignore: one allocation, one copy to the host
+  size_t early_bytes = 0;
   uint8_t* slab = nullptr;
   size_t slab_zero_bytes = 0, slab_ff_off = 0, slab_ff_bytes = 0;
   void* ign_blob = nullptr;               // ignore table + folded runes of the last finalize (grow-only)
@@ -159,9 +165,9 @@ struct Ctx {
 
 // ---- kernel launchers (kernels.cu) ----
 void launch_name_features(Ctx* c, DevTree* t);
-void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec);
+void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket);
 void launch_file_phase(Ctx* c, DevTree* t, const ChunkRec* chunk_rec);
-void launch_df_body(Ctx* c, DevTree* t);
+void launch_dockerfile(Ctx* c, DevTree* t);
 void launch_content_up(Ctx* c, DevTree* t, cudaStream_t st);
 void launch_walk(Ctx* c, DevTree* t, uint32_t sh_flavor, const IgnoreSlot* table, uint32_t table_mask, const uint32_t* runes,
                  const uint32_t* prefix_runes, uint32_t prefix_len, uint64_t depth1_state, uint8_t root_ignore, cudaStream_t st);

@@ -15,7 +15,9 @@
 // The first call on a device resolves the array's device address (cudaGetSymbolAddress) and reads
 // the SM count; make that first call before starting any stream capture.  All calls share the one
 // array: it keeps whatever the previous call left, which is harmless because every record a call
-// reads is written by that same call first -- nothing in it has to start at zero.  Two calls whose
+// reads is written by that same call first -- nothing in it has to start at zero.  The one word that
+// must start at zero, the counter the scan draws its chunks from, is cleared on the caller's stream
+// by every call.  Two calls whose
 // kernels overlap on the GPU (different streams, or different threads) would overwrite each other's
 // records: run them one after the other.
 #include <cuda_runtime.h>
@@ -32,10 +34,13 @@ constexpr uint32_t kNoAllocMaxChunks = 262144;  // 2 MiB of records
 
 // In host code this name is only a handle for the runtime, not an address a kernel can use.
 static __device__ __align__(256) ChunkRec g_noalloc_records[kNoAllocMaxChunks];
+// the scan hands out chunks from a counter; it lives next to the table and IS cleared by every call
+static __device__ uint32_t g_noalloc_ticket;
 
 constexpr int kMaxDevices = 64;
 static std::mutex g_setup_mutex;
 static ChunkRec* g_records_ptr[kMaxDevices];  // device address of g_noalloc_records, per device
+static uint32_t* g_ticket_ptr[kMaxDevices];   // ... and of g_noalloc_ticket
 static int g_sm_count[kMaxDevices];
 
 // Per-file flags from the chunk records: one thread per file walks its records in order and keeps
@@ -110,6 +115,11 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
       e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_records);
       if (e != cudaSuccess || !ptr)
         return noalloc_fail(M2K_ERR_CUDA, "cudaGetSymbolAddress(record table) on device %d: %s", device, cudaGetErrorString(e));
+      uint32_t* tptr = nullptr;
+      e = cudaGetSymbolAddress((void**)&tptr, g_noalloc_ticket);
+      if (e != cudaSuccess || !tptr)
+        return noalloc_fail(M2K_ERR_CUDA, "cudaGetSymbolAddress(chunk counter) on device %d: %s", device, cudaGetErrorString(e));
+      g_ticket_ptr[device] = tptr;
       int sms = 0;
       e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
       if (e != cudaSuccess || sms <= 0)
@@ -134,7 +144,9 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
   t.file_len = const_cast<uint64_t*>(d_file_len);
   t.bytes = const_cast<uint8_t*>(d_bytes);
   t.shard_byte0 = 0;
-  launch_scan_bytes(&c, &t, g_records_ptr[device]);
+  e = cudaMemsetAsync(g_ticket_ptr[device], 0, sizeof(uint32_t), c.stream);  // a memset node, not an allocation
+  if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: clearing the chunk counter: %s", cudaGetErrorString(e));
+  launch_scan_bytes(&c, &t, g_records_ptr[device], g_ticket_ptr[device]);
   k_noalloc_file_flags<<<(n_files + 127) / 128, 128, 0, c.stream>>>(n_files, n_chunks, d_chunk_first, d_file_len, d_file_flags);
   e = cudaGetLastError();
   if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: kernel launch: %s", cudaGetErrorString(e));

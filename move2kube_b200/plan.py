@@ -20,6 +20,15 @@ SourceDirectoryBuildArtifactType = "SourceCode"
 
 
 @dataclass
+class RepoInfo:
+    """plantypes.RepoInfo (plan.go:194-199): filled by Service.GatherGitInfo (go-git, host only)."""
+    GitRepoDir: str = ""
+    GitRepoURL: str = ""
+    GitRepoBranch: str = ""
+    TargetPath: str = ""
+
+
+@dataclass
 class Service:
     """plantypes.Service (plan.go:202-215)."""
     ServiceName: str = ""
@@ -33,6 +42,7 @@ class Service:
     UpdateContainerBuildPipeline: bool = False
     UpdateDeployPipeline: bool = False
     ServiceRelPath: str = ""
+    RepoInfo: "RepoInfo" = field(default_factory=RepoInfo)
 
     def AddSourceType(self, st: str) -> bool:
         if st not in self.SourceTypes:
@@ -81,18 +91,48 @@ def NewService(servicename: str, translationtype: str) -> Service:
 
 @dataclass
 class Inputs:
+    """plan.go:185-191"""
     RootDir: str = ""
+    K8sFiles: List[str] = field(default_factory=list)
+    QACaches: List[str] = field(default_factory=list)
     Services: Dict[str, List[Service]] = field(default_factory=dict)
+    TargetInfoArtifacts: Dict[str, List[str]] = field(default_factory=dict)
+
+
+@dataclass
+class TargetClusterType:
+    """plan.go:162-165"""
+    Type: str = ""
+    Path: str = ""
+
+
+@dataclass
+class KubernetesOutput:
+    """plan.go:151-157"""
+    RegistryURL: str = ""
+    RegistryNamespace: str = ""
+    ArtifactType: str = "Yamls"
+    TargetCluster: "TargetClusterType" = field(default_factory=lambda: TargetClusterType(Type="Kubernetes"))
+    IgnoreUnsupportedKinds: bool = False
+
+
+@dataclass
+class Outputs:
+    Kubernetes: "KubernetesOutput" = field(default_factory=KubernetesOutput)
 
 
 @dataclass
 class Spec:
     Inputs: "Inputs" = field(default_factory=Inputs)
+    Outputs: "Outputs" = field(default_factory=Outputs)
 
 
 @dataclass
 class Plan:
-    """plantypes.Plan, as far as source detection looks at it (plan.go:133-160)."""
+    """plantypes.Plan (plan.go:133-160); NewPlan's defaults (plan.go:400-426).  The wire format
+    (ReadPlan / WritePlan, planutils.go:164-201) is in planio.py."""
+    APIVersion: str = "move2kube.konveyor.io/v1alpha1"
+    Kind: str = "Plan"
     Name: str = "myproject"
     Spec: "Spec" = field(default_factory=Spec)
 

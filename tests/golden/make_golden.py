@@ -207,7 +207,9 @@ def reference_plans(out_dir):
     out = {}
     for key, (rel_path, tree) in files.items():
         y = yaml.safe_load(open(os.path.join(REF, rel_path)))
-        out[key] = {"source": rel_path, "tree": tree, "services": y["spec"]["inputs"]["services"]}
+        # "text": the golden file as the reference's WritePlan stored it (planio's writer is compared with it byte for byte)
+        out[key] = {"source": rel_path, "tree": tree, "services": y["spec"]["inputs"]["services"],
+                    "text": open(os.path.join(REF, rel_path)).read()}
     with open(os.path.join(out_dir, "_reference_plans.json"), "w") as f:
         json.dump(out, f, indent=1, sort_keys=True)
     print("reference plans: %d" % len(out))

@@ -16,13 +16,18 @@ OUTDIR = os.path.join(REPO, "move2kube_b200", "variants")
 
 VARIANTS = {
     "base": [],
-    "w32": ["M2K_SCAN_WAVES=32"],
-    "w128": ["M2K_SCAN_WAVES=128"],
-    "w512": ["M2K_SCAN_WAVES=512"],
-    "w4096": ["M2K_SCAN_WAVES=4096"],
-    "w4096_t128": ["M2K_SCAN_WAVES=4096", "M2K_SCAN_THREADS=128", "M2K_SCAN_MINBLOCKS=8"],
-    "w4096_t64": ["M2K_SCAN_WAVES=8192", "M2K_SCAN_THREADS=64", "M2K_SCAN_MINBLOCKS=16"],
-    "w128_rows4_b6": ["M2K_SCAN_WAVES=128", "M2K_SCAN_ROWS=4", "M2K_SCAN_MINBLOCKS=6"],
+    # round 2: work items drawn from a counter instead of strided; the bulk-copy engine (cp.async.bulk + mbarrier
+    # rings in shared memory) feeding the same scan
+    "strided": ["M2K_SCAN_TICKET=0"],  # round 1's distribution: item += number of warps, 32 waves of blocks
+    "bulk_w16_s3": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=3"],
+    "bulk_w24_s2": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=24", "M2K_BULK_STAGES=2"],
+    "bulk_w12_s4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=12", "M2K_BULK_STAGES=4"],
+    "bulk_w16_s6_r4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=6", "M2K_SCAN_ROWS=4"],
+    "bulk_w32_s3_r4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=32", "M2K_BULK_STAGES=3", "M2K_SCAN_ROWS=4"],
+    # Dockerfile body stripes (the product uses 256 bytes)
+    "df_stripe128": ["M2K_DF_STRIPE=128"],
+    "df_stripe64": ["M2K_DF_STRIPE=64"],
+    # round 1 (kept for the record; "base" won): M2K_SCAN_WAVES 32/128/512/4096, 128- and 64-thread blocks, 4 rows
 }
 
 
@@ -30,19 +35,24 @@ def main():
     from move2kube_b200 import build as b
     os.makedirs(OUTDIR, exist_ok=True)
     if "--build" in sys.argv:
+        only = sys.argv[sys.argv.index("--only") + 1].split(",") if "--only" in sys.argv else list(VARIANTS)
         for name, defs in VARIANTS.items():
+            if name not in only:
+                continue
             b.build(force=True, defines=defs, out=os.path.join(OUTDIR, "libm2kdetect_%s.so" % name))
             print("built", name)
     if "--run" in sys.argv:
-        wl = "C"
-        for name in VARIANTS:
+        wl = sys.argv[sys.argv.index("--workload") + 1] if "--workload" in sys.argv else "C"
+        only = sys.argv[sys.argv.index("--only") + 1].split(",") if "--only" in sys.argv else list(VARIANTS)
+        for name in only:
             env = dict(os.environ, M2K_LIB=os.path.join(OUTDIR, "libm2kdetect_%s.so" % name))
             p = subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), "--workload", wl, "--steps", "5", "--warmup", "3",
                                 "--no-e2e", "--no-cpu"], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
             try:
                 j = json.loads(p.stdout.strip().splitlines()[-1])
-                print("%-12s scan %.3f ms  %.0f GB/s  frac %.3f  step %.2f ms" % (name, j["roofline"]["kernel_ms"], j["roofline"]["achieved"],
-                                                                                j["roofline"]["frac"], j["ms_per_step"]), flush=True)
+                print("%-14s scan %.3f ms  %.0f GB/s  frac %.3f  step %.3f ms  combine %.3f  dockerfile %.3f" % (
+                    name, j["roofline"]["kernel_ms"], j["roofline"]["achieved"], j["roofline"]["frac"], j["ms_per_step"],
+                    j["breakdown_ms"]["combine"], j["breakdown_ms"]["dockerfile"]), flush=True)
             except Exception as e:
                 print(name, "FAILED", e, p.stderr[-300:], flush=True)
 
