@@ -262,6 +262,25 @@ int m2k_merge_pieces(m2k_ctx* ctx, m2k_devtree* dt, const void* d_all_pieces /* 
 int m2k_export_async(m2k_ctx* ctx, m2k_devtree* dt, uint32_t* d_content, uint32_t* d_main, void* d_pieces, uint8_t* d_flags);
 int m2k_import_async(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t* d_all_content, const uint32_t* d_all_main,
                      const void* d_all_pieces, const uint8_t* d_flags, uint32_t n_ranks);
+/* -- the exchange of a sharded pass over PEER MEMORY (NVLink / NVSwitch), no collective library in the data
+ * path ("fused peer atomicOr into rank 0's buffer").  One rank -- the root, rank 0, the one
+ * that calls m2k_prepare / m2k_finalize -- opens the exchange on its device tree; every other rank attaches its own
+ * device tree (same packed tree, another shard) to the root's memory: through the 192-byte handle when it lives
+ * in another process (CUDA IPC; ship the bytes any way you like, e.g. one broadcast at set-up), or directly when
+ * it lives in the same process on another (or the same) device.  From then on m2k_scan on an attached rank skips
+ * the name kernel and, once the root has cleared its arrays for the pass, its per-file kernels OR / MIN their
+ * per-directory results straight into the ROOT's arrays; its own range of the per-file flags and its two piece
+ * summaries follow, then a flag in the root's mailbox.  The root calls m2k_exchange_collect between its m2k_scan
+ * and m2k_finalize: it waits (on the device) for every rank's flag and stitches the files that were cut between
+ * ranks.  All ranks must call m2k_scan the same number of times.  A rank that never arrives makes the pass fail
+ * after 30 s (m2k_finalize returns M2K_ERR_CUDA) instead of hanging the GPU. -- */
+typedef struct m2k_exchange_handle { uint8_t opaque[192]; } m2k_exchange_handle;
+int m2k_exchange_open(m2k_ctx* ctx, m2k_devtree* root_dt, uint32_t n_ranks, m2k_exchange_handle* out);
+int m2k_exchange_attach(m2k_ctx* ctx, m2k_devtree* dt, uint32_t rank, const m2k_exchange_handle* handle);
+int m2k_exchange_attach_local(m2k_ctx* ctx, m2k_devtree* dt, uint32_t rank, m2k_ctx* root_ctx, m2k_devtree* root_dt);
+int m2k_exchange_collect(m2k_ctx* ctx, m2k_devtree* root_dt);
+/* an attached rank: block (without spinning) until its part of the current pass has been delivered */
+int m2k_exchange_wait(m2k_ctx* ctx, m2k_devtree* dt);
 /* which file holds global chunk `chunk`, and which of its chunks that is (a cut at chunk_in_file != 0 splits the file) */
 int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* file, uint32_t* chunk_in_file);
 /* one file's flags on the device, read back (synchronises); and, before m2k_finalize, the flags a

@@ -4,6 +4,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <atomic>
@@ -213,6 +214,7 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
   for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
+  if (C->ev_idle) cudaEventDestroy(C->ev_idle);
   if (C->side_stream) cudaStreamDestroy(C->side_stream);
   for (int k = 0; k < 2; k++) { if (C->stage[k]) cudaFreeHost(C->stage[k]); if (C->stage_ev[k]) cudaEventDestroy(C->stage_ev[k]); }
   if (C->stream) cudaStreamDestroy(C->stream);
@@ -299,6 +301,7 @@ extern "C" void m2k_tree_free(m2k_ctx* ctx, m2k_tree* tree) {
 
 // ---- device trees ---------------------------------------------------------------------------
 static void devtree_release(DevTree* t) {
+  if (t->link.ipc_base) { cudaIpcCloseMemHandle(t->link.ipc_base); t->link.ipc_base = nullptr; }
   // (dir_direct, dir_content, dir_subtree, file_flags, df_counters, special, dir_first_war, dir_main and
   // dir_main_sub live inside the slab)
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
@@ -447,7 +450,13 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
     const size_t o_main = off; off += nd4;
     const size_t o_main_sub = off; off += nd4;
     t->slab_ff_bytes = off - t->slab_ff_off;
+    const size_t o_mailbox = off; off += up(sizeof(Mailbox));
+    const size_t o_all_pieces = off; off += up(2 * kMaxRanks * sizeof(PieceSummary));
+    t->slab_bytes = off;
     CU(cudaMalloc((void**)&t->slab, off));
+    t->mailbox = (Mailbox*)(t->slab + o_mailbox); t->all_pieces = (PieceSummary*)(t->slab + o_all_pieces);
+    CU(cudaMemsetAsync(t->mailbox, 0, sizeof(Mailbox), C->stream));
+    CU(cudaMemsetAsync(t->all_pieces, 0xFF, 2 * kMaxRanks * sizeof(PieceSummary), C->stream));
     t->dir_direct = (uint32_t*)(t->slab + o_direct); t->dir_content = (uint32_t*)(t->slab + o_content);
     t->dir_subtree = (uint32_t*)(t->slab + o_subtree); t->file_flags = t->slab + o_flags;
     t->df_counters = (DfCounters*)(t->slab + o_ctr); t->special = (uint32_t*)(t->slab + o_special);
@@ -604,25 +613,42 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
     CU(cudaMemsetAsync(t->tile_state, 0, 4ull * t->tile_cap, s));
     t->epoch = 1;
   }
+  // multi-GPU over peer memory: a rank attached to a root only scans its shard and reduces into the
+  // root's arrays; names, ignore rules and the walk are the root's business
+  PeerLink& L = t->link;
+  const bool remote = L.attached && !L.is_root;
+  if (L.attached) {
+    L.pass++;
+    if (L.is_root) launch_signal(C, &t->mailbox->ready, L.pass, s);  // my arrays are cleared: contributions for this pass may come
+  }
   dt->prep.ready = false;
   CU(cudaEventRecord(C->ev[8], s));
-  launch_name_features(C, t);
-  // the host needs the name features (which entries are .m2kignore files) while the byte scan runs:
-  // they go down on the copy stream, so the byte scan starts right behind the name kernel
-  CU(cudaEventRecord(C->ev_names, s));
-  CU(cudaStreamWaitEvent(C->copy_stream, C->ev_names, 0));
-  CU(cudaMemcpyAsync(dt->h_special, t->special, 4ull * (kSpecialCap + 1), cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, C->copy_stream));
-  CU(cudaEventRecord(C->ev_feat, C->copy_stream));
+  if (!remote) {
+    launch_name_features(C, t);
+    // the host needs the name features (which entries are .m2kignore files) while the byte scan runs:
+    // they go down on the copy stream, so the byte scan starts right behind the name kernel
+    CU(cudaEventRecord(C->ev_names, s));
+    CU(cudaStreamWaitEvent(C->copy_stream, C->ev_names, 0));
+    CU(cudaMemcpyAsync(dt->h_special, t->special, 4ull * (kSpecialCap + 1), cudaMemcpyDeviceToHost, C->copy_stream));
+    CU(cudaMemcpyAsync(dt->h_entry_feat, t->entry_feat, 4ull * t->n_entries, cudaMemcpyDeviceToHost, C->copy_stream));
+    CU(cudaEventRecord(C->ev_feat, C->copy_stream));
+  }
   CU(cudaEventRecord(C->ev[2], s));
   dt->content = content;
   if (content) {
     launch_scan_bytes(C, t, t->chunk_rec, &t->df_counters->scan_ticket);
     CU(cudaEventRecord(C->ev[3], s));
+    if (remote) launch_wait_ge(C, &L.mailbox->ready, 1, L.pass, &L.mailbox->abort, s);  // the root has cleared its arrays for this pass
     launch_file_phase(C, t, t->chunk_rec);
     CU(cudaEventRecord(C->ev[9], s));
     launch_dockerfile(C, t);
     CU(cudaEventRecord(C->ev[10], s));
+  } else if (remote) {
+    CU(cudaMemsetAsync(t->pieces, 0xFF, 2 * sizeof(PieceSummary), s));
+  }
+  if (remote) {
+    launch_contribute(C, t, s);
+    launch_signal(C, &L.mailbox->done[L.rank], L.pass, s);
   }
   CU(cudaGetLastError());
   // no synchronisation here: m2k_finalize overlaps its host work with these kernels
@@ -760,6 +786,128 @@ extern "C" int m2k_merge_partials(m2k_ctx* ctx, m2k_devtree* dt, const uint32_t*
   launch_merge_partials(C, &dt->t, d_all_content, d_all_main, n_ranks);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+// ---- multi-GPU over peer memory ---------------------------------------------------------------
+namespace {
+struct XHandle {  // what m2k_exchange_open hands to the other ranks (fits m2k_exchange_handle)
+  uint32_t magic, n_ranks;
+  int32_t device, pid;
+  uint32_t n_dirs, n_files;
+  uint64_t slab_bytes, off_content, off_main, off_flags, off_mailbox, off_pieces;
+  cudaIpcMemHandle_t ipc;
+};
+static_assert(sizeof(XHandle) <= sizeof(m2k_exchange_handle), "handle blob too small");
+constexpr uint32_t kXMagic = 0x4D324B58u;  // "M2KX"
+
+void link_from_base(PeerLink& L, uint8_t* base, const XHandle& h) {
+  L.dir_content = (uint32_t*)(base + h.off_content); L.dir_main = (uint32_t*)(base + h.off_main);
+  L.file_flags = base + h.off_flags; L.mailbox = (Mailbox*)(base + h.off_mailbox); L.pieces = (PieceSummary*)(base + h.off_pieces);
+}
+XHandle describe_root(const Ctx* C, const DevTree* t, uint32_t n_ranks) {
+  XHandle h;
+  memset(&h, 0, sizeof h);
+  h.magic = kXMagic; h.n_ranks = n_ranks; h.device = C->device; h.pid = (int32_t)getpid();
+  h.n_dirs = t->n_dirs; h.n_files = t->n_files; h.slab_bytes = t->slab_bytes;
+  h.off_content = (uint8_t*)t->dir_content - t->slab; h.off_main = (uint8_t*)t->dir_main - t->slab;
+  h.off_flags = t->file_flags - t->slab; h.off_mailbox = (uint8_t*)t->mailbox - t->slab; h.off_pieces = (uint8_t*)t->all_pieces - t->slab;
+  return h;
+}
+}  // namespace
+
+extern "C" int m2k_exchange_open(m2k_ctx* ctx, m2k_devtree* dt, uint32_t n_ranks, m2k_exchange_handle* out) {
+  if (!ctx || !dt || !out || n_ranks < 1 || n_ranks > kMaxRanks) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_exchange_open: bad argument (1..%u ranks)", kMaxRanks);
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  CU(cudaSetDevice(C->device));
+  if (int pe = preload_kernels()) return fail(C, M2K_ERR_CUDA, "loading the kernels: %s", cudaGetErrorString((cudaError_t)pe));
+  XHandle h = describe_root(C, t, n_ranks);
+  cudaError_t e = cudaIpcGetMemHandle(&h.ipc, t->slab);
+  if (e != cudaSuccess) { cudaGetLastError(); memset(&h.ipc, 0, sizeof h.ipc); }  // same-process ranks (m2k_exchange_attach_local) do not need it
+  memset(out, 0, sizeof *out);
+  memcpy(out, &h, sizeof h);
+  PeerLink& L = t->link;
+  L = PeerLink();
+  L.attached = true; L.is_root = true; L.rank = 0; L.n_ranks = n_ranks;
+  link_from_base(L, t->slab, h);
+  CU(cudaMemsetAsync(t->mailbox, 0, sizeof(Mailbox), C->stream));
+  CU(cudaStreamSynchronize(C->stream));
+  return M2K_OK;
+}
+
+extern "C" int m2k_exchange_attach(m2k_ctx* ctx, m2k_devtree* dt, uint32_t rank, const m2k_exchange_handle* handle) {
+  if (!ctx || !dt || !handle) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_exchange_attach: NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  XHandle h;
+  memcpy(&h, handle, sizeof h);
+  if (h.magic != kXMagic || rank == 0 || rank >= h.n_ranks) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach: not a handle of m2k_exchange_open, or rank %u outside 1..%u", rank, h.n_ranks - 1);
+  if (h.n_dirs != t->n_dirs || h.n_files != t->n_files) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach: the root holds a different tree (%u dirs / %u files, here %u / %u)", h.n_dirs, h.n_files, t->n_dirs, t->n_files);
+  if (h.pid == (int32_t)getpid()) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach: the root lives in this process: use m2k_exchange_attach_local");
+  CU(cudaSetDevice(C->device));
+  if (int pe = preload_kernels()) return fail(C, M2K_ERR_CUDA, "loading the kernels: %s", cudaGetErrorString((cudaError_t)pe));
+  void* base = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&base, h.ipc, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(C, M2K_ERR_CUDA, "cudaIpcOpenMemHandle (root on device %d): %s", h.device, cudaGetErrorString(e)); }
+  PeerLink& L = t->link;
+  if (L.ipc_base) cudaIpcCloseMemHandle(L.ipc_base);
+  L = PeerLink();
+  L.attached = true; L.is_root = false; L.rank = rank; L.n_ranks = h.n_ranks; L.ipc_base = base;
+  link_from_base(L, static_cast<uint8_t*>(base), h);
+  return M2K_OK;
+}
+
+extern "C" int m2k_exchange_attach_local(m2k_ctx* ctx, m2k_devtree* dt, uint32_t rank, m2k_ctx* root_ctx, m2k_devtree* root_dt) {
+  if (!ctx || !dt || !root_ctx || !root_dt) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_exchange_attach_local: NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree *t = &dt->t, *rt = &root_dt->t;
+  if (!rt->link.attached || !rt->link.is_root) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach_local: m2k_exchange_open was not called on the root");
+  if (rank == 0 || rank >= rt->link.n_ranks) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach_local: rank %u outside 1..%u", rank, rt->link.n_ranks - 1);
+  if (rt->n_dirs != t->n_dirs || rt->n_files != t->n_files) return fail(C, M2K_ERR_ARG, "m2k_exchange_attach_local: the root holds a different tree");
+  CU(cudaSetDevice(C->device));
+  if (int pe = preload_kernels()) return fail(C, M2K_ERR_CUDA, "loading the kernels: %s", cudaGetErrorString((cudaError_t)pe));
+  if (C->device != root_ctx->c.device) {
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, C->device, root_ctx->c.device));
+    if (!can) return fail(C, M2K_ERR_CUDA, "device %d cannot access device %d's memory (no NVLink / PCIe peer path)", C->device, root_ctx->c.device);
+    cudaError_t e = cudaDeviceEnablePeerAccess(root_ctx->c.device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(C, M2K_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d): %s", root_ctx->c.device, cudaGetErrorString(e));
+    cudaGetLastError();
+  }
+  PeerLink& L = t->link;
+  L = PeerLink();
+  L.attached = true; L.is_root = false; L.rank = rank; L.n_ranks = rt->link.n_ranks;
+  link_from_base(L, rt->slab, describe_root(&root_ctx->c, rt, rt->link.n_ranks));
+  return M2K_OK;
+}
+
+// the root, after its own m2k_scan: take in what the other ranks delivered for this pass
+extern "C" int m2k_exchange_collect(m2k_ctx* ctx, m2k_devtree* dt) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  PeerLink& L = t->link;
+  if (!L.attached || !L.is_root) return fail(C, M2K_ERR_ARG, "m2k_exchange_collect: not the root of an exchange");
+  CU(cudaSetDevice(C->device));
+  cudaStream_t s = C->stream;
+  if (dt->content) CU(cudaMemcpyAsync(t->all_pieces, t->pieces, 2 * sizeof(PieceSummary), cudaMemcpyDeviceToDevice, s));
+  else CU(cudaMemsetAsync(t->all_pieces, 0xFF, 2 * sizeof(PieceSummary), s));
+  launch_wait_ge(C, &t->mailbox->done[1], L.n_ranks - 1, L.pass, &t->mailbox->abort, s);
+  launch_merge_pieces(C, t, t->all_pieces, 2 * L.n_ranks);
+  CU(cudaGetLastError());
+  return M2K_OK;
+}
+
+// a rank that only scans: wait until its part of the pass has been delivered (blocks, does not spin)
+extern "C" int m2k_exchange_wait(m2k_ctx* ctx, m2k_devtree* dt) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  if (!C->ev_idle) CU(cudaEventCreateWithFlags(&C->ev_idle, cudaEventBlockingSync | cudaEventDisableTiming));
+  CU(cudaEventRecord(C->ev_idle, C->stream));
+  CU(cudaEventSynchronize(C->ev_idle));
+  if (int rc = collect_scan_timings(C, dt)) return rc;
   return M2K_OK;
 }
 
@@ -1204,6 +1352,11 @@ extern "C" int m2k_finalize(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_para
   CU(cudaEventRecord(C->ev[6], s));
   cudaError_t werr = cudaStreamSynchronize(s);
   if (werr != cudaSuccess) return fail(C, M2K_ERR_CUDA, "detection kernels failed: %s", cudaGetErrorString(werr));
+  if (t->link.attached) {
+    uint32_t aborted = 0;
+    CU(cudaMemcpy(&aborted, &t->mailbox->abort, 4, cudaMemcpyDeviceToHost));
+    if (aborted) return fail(C, M2K_ERR_CUDA, "multi-GPU pass %u: a rank did not deliver its part within 30 s", t->link.pass);
+  }
   if (int rc = collect_scan_timings(C, dt)) return rc;
   float ms_k1 = 0, ms_k2 = 0, ms_d = 0;
   CU(cudaEventElapsedTime(&ms_k1, C->ev_side0, C->ev_side1));  // directory phases on the side stream (under the byte scan)

@@ -439,7 +439,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 // the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
 // lines that start inside it (k_df_validate).
 #ifndef M2K_DF_STRIPE
-#define M2K_DF_STRIPE 256
+#define M2K_DF_STRIPE 128
 #endif
 constexpr uint32_t kStripe = M2K_DF_STRIPE;   // == kDfStripe (m2k_internal.h)
 

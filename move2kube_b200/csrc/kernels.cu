@@ -552,14 +552,15 @@ __device__ __forceinline__ void note_main_file(uint32_t f, const uint32_t* file_
   uint32_t e = file_entry[f];
   uint32_t off = entry_name_off[e], nl = entry_name_off[e + 1] - off;
   if (nl >= 2 && names[off + nl - 2] == 'p' && names[off + nl - 1] == 'y') {  // awk '/.py$/' on the path
+    // system scope: in a multi-GPU pass these arrays are the ROOT's, reached over NVLink (DevTree::link)
     uint32_t d = entry_dir[e];
-    atomicOr(&dir_content[d], 1u << M2K_C_MAIN_PY);
-    atomicMin(&dir_main[d], f);
+    atomicOr_system(&dir_content[d], 1u << M2K_C_MAIN_PY);
+    atomicMin_system(&dir_main[d], f);
   }
 }
 
 __device__ __forceinline__ void note_dockerfile(const FileArgs& a, uint32_t f) {
-  atomicOr(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
+  atomicOr_system(&a.dir_content[a.entry_dir[a.file_entry[f]]], 1u << M2K_C_DOCKERFILE);
 }
 
 // i: index of the file in the shard.  A file all of whose chunks are here gets its final HAS_MAIN /
@@ -827,9 +828,11 @@ __global__ void __launch_bounds__(128) k_df_validate(FileArgs a) {
 }
 
 static FileArgs file_args(DevTree* t, const ChunkRec* chunk_rec) {
+  // a rank that is attached to a root reduces its per-directory contributions straight into the root's arrays
+  const bool remote = t->link.attached && !t->link.is_root;
   return FileArgs{t->file_end - t->file_begin, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec,
                   t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
-                  t->file_flags, t->dir_content, t->dir_main, t->pieces, t->df_counters, t->head_list, t->cand_file, t->cand_body,
+                  t->file_flags, remote ? t->link.dir_content : t->dir_content, remote ? t->link.dir_main : t->dir_main, t->pieces, t->df_counters, t->head_list, t->cand_file, t->cand_body,
                   t->cand_esc, t->cand_stripe0, t->cand_err, t->cand_done, t->stripe_state, t->tile_state, t->epoch};
 }
 
@@ -1034,8 +1037,94 @@ void launch_walk(Ctx* c, DevTree* t, uint32_t sh_flavor, const IgnoreSlot* table
   c->launches += 2;
 }
 
+const void* k_merge_partials_fn();
+const void* k_merge_pieces_fn();
+const void* k_settle_file_fn();
+const void* k_synth_fill_fn();
+
 // ---------------------------------------------------------------------------------------------
-// multi-GPU: fold the gathered per-directory partials (rank-major) into this rank's arrays
+// multi-GPU over peer memory (PeerLink): pass ordering flags in the root's mailbox, and what a rank
+// sends besides its in-kernel reductions -- its own range of the per-file flags and its two piece
+// summaries, written into the root's memory over NVLink.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__global__ void k_signal(uint32_t* flag, uint32_t value) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  __threadfence_system();  // everything this stream did before (kernel boundaries) is visible before the flag
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+// one thread per flag waits until it reaches `value` (pass numbers only grow).  A peer that never
+// arrives must not hang the GPU: after 30 s the wait gives up and raises `abort`, which the host
+// reports as an error of the pass.
+__global__ void k_wait_ge(const uint32_t* flags, uint32_t n_flags, uint32_t value, uint32_t* abort) {
+  if (threadIdx.x >= n_flags || blockIdx.x != 0) return;
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while ((int32_t)(ld_acquire_sys(flags + threadIdx.x) - value) < 0) {
+    __nanosleep(200);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 30000000000ull) { atomicExch_system(abort, 1u); break; }
+  }
+  __threadfence_system();
+}
+__global__ void __launch_bounds__(256) k_contribute(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint32_t lo, uint32_t hi,
+                                                    const PieceSummary* __restrict__ my_pieces, PieceSummary* __restrict__ root_pieces) {
+  // bytes [lo, hi) of the per-file flags: both arrays are 256-byte aligned, so index alignment is address alignment
+  const uint32_t a_lo = (lo + 15) & ~15u, a_hi = hi & ~15u;
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  if (a_lo < a_hi) {
+    for (uint32_t i = a_lo / 16 + tid; i < a_hi / 16; i += nth) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+    for (uint32_t i = lo + tid; i < a_lo; i += nth) dst[i] = src[i];
+    for (uint32_t i = a_hi + tid; i < hi; i += nth) dst[i] = src[i];
+  } else {
+    for (uint32_t i = lo + tid; i < hi; i += nth) dst[i] = src[i];
+  }
+  if (tid < 2) root_pieces[tid] = my_pieces[tid];
+}
+
+// Kernels are loaded lazily, on first launch, and loading can wait for the device to go idle: a first
+// launch made while a k_wait_ge spins for the very work that launch belongs to would never return.
+// Every kernel a pass can launch is therefore loaded when an exchange is set up.
+int preload_kernels() {
+  const void* fns[] = {(const void*)k_fill_u32, (const void*)k_name_features, (const void*)k_scan_bytes, (const void*)k_scan_bytes_bulk,
+                       (const void*)k_file_combine, (const void*)k_df_head, (const void*)k_df_states, (const void*)k_df_validate,
+                       (const void*)k_content_up, (const void*)k_walk_local, (const void*)k_walk_reach, (const void*)k_signal,
+                       (const void*)k_wait_ge, (const void*)k_contribute, (const void*)k_merge_partials_fn(), (const void*)k_merge_pieces_fn(),
+                       (const void*)k_settle_file_fn(), (const void*)k_synth_fill_fn()};
+  for (const void* f : fns) {
+    cudaFuncAttributes attr;
+    cudaError_t e = cudaFuncGetAttributes(&attr, f);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return 0;
+}
+
+void launch_signal(Ctx* c, uint32_t* flag, uint32_t value, cudaStream_t st) {
+  k_signal<<<1, 32, 0, st>>>(flag, value);
+  c->launches++;
+}
+void launch_wait_ge(Ctx* c, const uint32_t* flags, uint32_t n_flags, uint32_t value, uint32_t* abort, cudaStream_t st) {
+  if (!n_flags) return;
+  k_wait_ge<<<1, 64, 0, st>>>(flags, n_flags, value, abort);
+  c->launches++;
+}
+// a non-root rank, after its per-file kernels: its flag range and piece summaries into the root's memory
+void launch_contribute(Ctx* c, DevTree* t, cudaStream_t st) {
+  const uint32_t n = t->file_end - t->file_begin;
+  uint32_t blocks = (n / 16 + 255) / 256 + 1;
+  if (blocks > (uint32_t)c->sm_count * 4) blocks = (uint32_t)c->sm_count * 4;
+  k_contribute<<<blocks, 256, 0, st>>>(t->file_flags, t->link.file_flags, t->file_begin, t->file_end, t->pieces,
+                                        t->link.pieces + 2 * t->link.rank);
+  c->launches++;
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-GPU through a collective library (the caller gathers): fold the gathered per-directory
+// partials (rank-major) into this rank's arrays
 // ---------------------------------------------------------------------------------------------
 __global__ void k_merge_partials(uint32_t n_dirs, uint32_t n_ranks, const uint32_t* __restrict__ all_content,
                                  const uint32_t* __restrict__ all_main, uint32_t* __restrict__ dir_content, uint32_t* __restrict__ dir_main) {
@@ -1168,5 +1257,10 @@ void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed) {
                                                                 t->bytes, t->shard_byte0, t->first_skip, t->last_end);
   c->launches++;
 }
+
+const void* k_merge_partials_fn() { return (const void*)k_merge_partials; }
+const void* k_merge_pieces_fn() { return (const void*)k_merge_pieces; }
+const void* k_settle_file_fn() { return (const void*)k_settle_file; }
+const void* k_synth_fill_fn() { return (const void*)k_synth_fill; }
 
 }  // namespace m2k

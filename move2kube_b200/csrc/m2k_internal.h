@@ -12,7 +12,7 @@ namespace m2k {
 constexpr uint32_t kChunkBytes = 65536;  // bytes of one scan work item (one warp)
 constexpr uint32_t kUnitsPerChunk = kChunkBytes / 16;
 #ifndef M2K_DF_STRIPE
-#define M2K_DF_STRIPE 256
+#define M2K_DF_STRIPE 128
 #endif
 constexpr uint32_t kDfStripe = M2K_DF_STRIPE;  // bytes of one stripe of the parallel Dockerfile validation
 constexpr uint32_t kDfTileStripes = 256;  // stripes per tile (one block of k_df_states)
@@ -73,6 +73,26 @@ __host__ __device__ inline uint32_t slot_pack(uint32_t len, uint32_t flags) { re
 __host__ __device__ inline uint32_t slot_len(uint32_t lf) { return lf & 0x1FFFFFFFu; }
 __host__ __device__ inline uint32_t slot_flags(uint32_t lf) { return lf >> 29; }
 
+// ---- multi-GPU exchange over peer memory (NVLink / NVSwitch) ----
+// The rank that assembles the result (the root) owns a mailbox next to its per-directory arrays; the
+// other ranks map that memory (peer access inside one process, CUDA IPC between processes) and their
+// per-file kernels OR / MIN their sparse per-directory contributions straight into the root's arrays
+// -- the reduction happens in the root's L2, as the contributions are produced, and no collective
+// library is in the data path.  Flags in the mailbox order the passes: `ready` = the root has
+// cleared its arrays for pass p; done[r] = rank r's contributions for pass p have landed.
+constexpr uint32_t kMaxRanks = 62;
+struct Mailbox { uint32_t ready; uint32_t abort; uint32_t done[kMaxRanks]; };  // 256 bytes
+struct PeerLink {
+  bool attached = false, is_root = false;
+  uint32_t rank = 0, n_ranks = 1;
+  uint32_t pass = 0;                 // exchange pass number (every rank counts its m2k_scan calls)
+  Mailbox* mailbox = nullptr;        // the root's, as seen from this rank's device
+  uint32_t *dir_content = nullptr, *dir_main = nullptr;  // the root's arrays
+  uint8_t* file_flags = nullptr;
+  PieceSummary* pieces = nullptr;    // [2 * n_ranks] on the root, rank order
+  void* ipc_base = nullptr;          // mapping opened with cudaIpcOpenMemHandle (other process), to close
+};
+
 // a tree (metadata replicated) plus the bytes of file ids [file_begin, file_end) resident in HBM
 struct DevTree {
   const m2k_tree* host = nullptr;
@@ -118,7 +138,11 @@ struct DevTree {
   uint8_t* early = nullptr;               // dir_opts | dir_state | dir_ignore: one allocation, one copy to the host
   size_t early_bytes = 0;
   uint8_t* slab = nullptr;
-  size_t slab_zero_bytes = 0, slab_ff_off = 0, slab_ff_bytes = 0;
+  size_t slab_zero_bytes = 0, slab_ff_off = 0, slab_ff_bytes = 0, slab_bytes = 0;
+  // behind the all-ones region, never cleared by a pass: the exchange mailbox and the gathered piece summaries
+  Mailbox* mailbox = nullptr;
+  PieceSummary* all_pieces = nullptr;     // [2 * kMaxRanks]
+  PeerLink link;
   void* ign_blob = nullptr;               // ignore table + folded runes of the last finalize (grow-only)
   size_t ign_blob_cap = 0;
   uint32_t* entry_feat = nullptr;         // [n_entries]
@@ -150,6 +174,7 @@ struct Ctx {
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_side0 = nullptr, ev_side1 = nullptr;  // timing on: the span of those kernels
   cudaEvent_t ev_early = nullptr;                      // ... and their results are on the host
+  cudaEvent_t ev_idle = nullptr;                       // blocking-sync event for ranks that only wait (m2k_exchange_wait)
   // two pinned blocks through which bytes held in pageable host memory are streamed to the device
   void* stage[2] = {nullptr, nullptr};
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
@@ -177,6 +202,11 @@ void launch_merge_partials(Ctx* c, DevTree* t, const uint32_t* all_content, cons
 void launch_merge_pieces(Ctx* c, DevTree* t, const PieceSummary* all_pieces, uint32_t n_pieces);
 void launch_settle_file(Ctx* c, DevTree* t, uint32_t f, uint32_t flags);
 void launch_synth_fill(Ctx* c, DevTree* t, uint64_t seed);
+// exchange (kernels.cu): flag writes / waits at system scope, this rank's flags + pieces into the root's memory
+void launch_signal(Ctx* c, uint32_t* flag, uint32_t value, cudaStream_t st);
+void launch_wait_ge(Ctx* c, const uint32_t* flags, uint32_t n_flags, uint32_t value, uint32_t* abort, cudaStream_t st);
+void launch_contribute(Ctx* c, DevTree* t, cudaStream_t st);
+int preload_kernels();  // 0 or a cudaError_t
 void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
 
 void set_global_error(const char* msg);  // api.cu: what m2k_global_error() returns on this thread

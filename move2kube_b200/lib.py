@@ -31,6 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait",
 ]
 
 
@@ -101,6 +102,11 @@ def load():
     L.m2k_export_async.argtypes = [vp, vp, vp, vp, vp, vp]
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
+    L.m2k_exchange_open.argtypes = [vp, vp, C.c_uint32, vp]
+    L.m2k_exchange_attach.argtypes = [vp, vp, C.c_uint32, vp]
+    L.m2k_exchange_attach_local.argtypes = [vp, vp, C.c_uint32, vp, vp]
+    L.m2k_exchange_collect.argtypes = [vp, vp]
+    L.m2k_exchange_wait.argtypes = [vp, vp]
     L.m2k_is_dockerfile.argtypes = [vp, C.c_char_p, C.c_uint64, _abi.u32p]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
@@ -222,6 +228,26 @@ class Context:
 
     def import_async(self, dt, all_content_ptr, all_main_ptr, all_pieces_ptr, flags_ptr, n_ranks):
         _check(self.L.m2k_import_async(self.h, dt, all_content_ptr, all_main_ptr, all_pieces_ptr, flags_ptr, n_ranks), self.h)
+
+    # -- exchange over peer memory
+    def exchange_open(self, dt, n_ranks) -> bytes:
+        """Root: returns the 192-byte handle the other ranks attach with."""
+        buf = C.create_string_buffer(192)
+        _check(self.L.m2k_exchange_open(self.h, dt, n_ranks, buf), self.h)
+        return buf.raw
+
+    def exchange_attach(self, dt, rank, handle: bytes):
+        buf = C.create_string_buffer(bytes(handle), 192)
+        _check(self.L.m2k_exchange_attach(self.h, dt, rank, buf), self.h)
+
+    def exchange_attach_local(self, dt, rank, root_ctx, root_dt):
+        _check(self.L.m2k_exchange_attach_local(self.h, dt, rank, root_ctx.h, root_dt), self.h)
+
+    def exchange_collect(self, dt):
+        _check(self.L.m2k_exchange_collect(self.h, dt), self.h)
+
+    def exchange_wait(self, dt):
+        _check(self.L.m2k_exchange_wait(self.h, dt), self.h)
 
     def shard_content_bytes(self, dt) -> int:
         return self.L.m2k_devtree_content_bytes(dt)

@@ -332,6 +332,44 @@ def run_chunk_sharded(ctx, tree, cuts, fill_seed=None):
     return ctx.finalize(dts[0]), dts, settled
 
 
+def run_chunk_sharded_peer(ctx, tree, cuts, fill_seed=None):
+    """The same N-rank pass with the exchange over peer memory (m2k_exchange_*): every rank has its own
+    context and stream (all on this one GPU: the root's arrays are then simply local memory, the
+    protocol is the one real peers run), ranks 1.. reduce straight into rank 0's arrays from inside
+    their per-file kernels, rank 0 collects, settles and finalises."""
+    from move2kube_b200 import multi
+    n = len(cuts) - 1
+    ctxs = [ctx] + [lib.Context(0) for _ in range(n - 1)]
+    dts = []
+    for r in range(n):
+        dt = ctxs[r].upload_chunks(tree, cuts[r], cuts[r + 1])
+        if fill_seed is not None:
+            ctxs[r].synth_fill_device(dt, fill_seed)
+        dts.append(dt)
+    ctx.exchange_open(dts[0], n)
+    for r in range(1, n):
+        ctxs[r].exchange_attach_local(dts[r], r, ctx, dts[0])
+    res = None
+    for _ in range(2):  # twice: the second pass reuses the mailbox and every buffer of the first
+        if res is not None:
+            ctx.result_free(res)
+        for r in reversed(range(n)):  # the root last: the others must wait for its "arrays cleared" flag
+            ctxs[r].scan(dts[r])
+        ctx.exchange_collect(dts[0])
+        for r in range(1, n):
+            ctxs[r].exchange_wait(dts[r])
+        settled = multi.settle_undecided(ctx, tree, dts[0], multi.split_files(tree, cuts), fill_seed)
+        res = ctx.finalize(dts[0])
+    for r in range(1, n):
+        ctxs[r].devtree_free(dts[r])
+        ctxs[r].close()
+    return res, dts[:1], settled
+
+
+def sharded_runner(kind):
+    return run_chunk_sharded if kind == "gather" else run_chunk_sharded_peer
+
+
 def assert_same_result(tree, got, want):
     t, g, w = tree.contents, got.contents, want.contents
     nd, nf = t.n_dirs, t.n_files
@@ -341,8 +379,9 @@ def assert_same_result(tree, got, want):
     assert g.service_dirs[0:g.n_services] == w.service_dirs[0:w.n_services]
 
 
+@pytest.mark.parametrize("exchange", ["gather", "peer"])
 @pytest.mark.parametrize("world", [2, 3, 5])
-def test_chunk_shards_of_a_synthetic_tree_merge_to_the_whole(ctx, oracle, world):
+def test_chunk_shards_of_a_synthetic_tree_merge_to_the_whole(ctx, oracle, world, exchange):
     """Multi-MiB files spread over several shards, bytes generated on the device shard by shard."""
     p = _abi.SynthParams(seed=21, n_files=1500, n_dirs=90, max_depth=5, n_ignore_files=3, total_bytes=60 << 20,
                          n_huge=3, huge_bytes=9 << 20, n_large=2, large_bytes=3 << 20)
@@ -370,7 +409,7 @@ def test_chunk_shards_of_a_synthetic_tree_merge_to_the_whole(ctx, oracle, world)
         for cuts in plans:
             n_split += len(multi.split_files(tree, cuts))
             for seed in (None, p.seed):  # bytes uploaded from the host / generated in HBM
-                res, dts, _ = run_chunk_sharded(ctx, tree, cuts, fill_seed=seed)
+                res, dts, _ = sharded_runner(exchange)(ctx, tree, cuts, fill_seed=seed)
                 assert_same_result(tree, res, whole)
                 ctx.result_free(res)
                 for dt in dts:
@@ -412,7 +451,8 @@ def _big_file_tree(root):
     return root
 
 
-def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path):
+@pytest.mark.parametrize("exchange", ["gather", "peer"])
+def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path, exchange):
     """Two shards with the cut at every chunk of the tree, and a few three-way cuts: "__main__", long
     lines and Dockerfile heads that straddle the cut come out as in one pass."""
     root = os.fsencode(str(_big_file_tree(tmp_path / "big")))
@@ -434,7 +474,7 @@ def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path):
                                                             [0, total // 2, total // 2, total]]
         settled_any = False
         for cuts in plans:
-            res, dts, settled = run_chunk_sharded(ctx, tree, cuts)
+            res, dts, settled = sharded_runner(exchange)(ctx, tree, cuts)
             settled_any = settled_any or bool(settled)
             assert_same_result(tree, res, whole)
             ctx.result_free(res)

@@ -24,8 +24,8 @@ VARIANTS = {
     "bulk_w12_s4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=12", "M2K_BULK_STAGES=4"],
     "bulk_w16_s6_r4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=6", "M2K_SCAN_ROWS=4"],
     "bulk_w32_s3_r4": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=32", "M2K_BULK_STAGES=3", "M2K_SCAN_ROWS=4"],
-    # Dockerfile body stripes (the product uses 256 bytes)
-    "df_stripe128": ["M2K_DF_STRIPE=128"],
+    # Dockerfile body stripes (the product uses 128 bytes)
+    "df_stripe256": ["M2K_DF_STRIPE=256"],  # B: dockerfile phase 0.165 ms (256) / 0.116 (128) / 0.087 (64); C: 0.392 / 0.383 / 0.419
     "df_stripe64": ["M2K_DF_STRIPE=64"],
     # round 1 (kept for the record; "base" won): M2K_SCAN_WAVES 32/128/512/4096, 128- and 64-thread blocks, 4 rows
 }
