@@ -235,6 +235,9 @@ int m2k_is_dockerfile(m2k_ctx* ctx, const uint8_t* data, uint64_t len, uint32_t*
 
 /* -- staged form (bench, multi-GPU): a shard = file ids [file_begin, file_end) -- */
 int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out);
+/* the same shard again, host to device, into the buffers m2k_upload / m2k_upload_chunks allocated (no allocation:
+ * for a caller that keeps its device buffers between calls); `tree` must have the shape of the original */
+int m2k_reupload(m2k_ctx* ctx, m2k_devtree* dt, const m2k_tree* tree);
 /* -- a shard as a range of 64 KiB chunks, so that one multi-GB file can be spread over several GPUs
  * (SURVEY.md section 8e).  Chunks are numbered over the whole tree: files in id order, each
  * ceil(file_len / 65536) chunks (m2k_chunk_count = the total).  A shard may begin and end inside a

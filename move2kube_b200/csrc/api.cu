@@ -369,6 +369,8 @@ static int copy_to_device(Ctx* C, cudaStream_t s, void* dst, const void* src, si
   return M2K_OK;
 }
 
+static int copy_shard(Ctx* C, m2k_devtree* dt, const m2k_tree* tree);
+
 static inline uint64_t file_chunks(const m2k_tree* tree, uint32_t f) { return (tree->file_len[f] + kChunkBytes - 1) / kChunkBytes; }
 
 // the shard: files [file_begin, file_end), of which the first starts `first_skip` chunks in and the
@@ -476,6 +478,18 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
   CU(cudaHostAlloc((void**)&dt->h_results, 5 * align256(4ull * (nd ? nd : 1)) + 2 * align256(nd ? nd : 1) + nf + 256, cudaHostAllocDefault));
   t->special_cap = kSpecialCap;
+  CU(cudaMemcpyAsync(t->chunk_first, chunk_first.data(), 4ull * ((size_t)ns + 1), cudaMemcpyHostToDevice, C->stream));
+  CU(cudaStreamSynchronize(C->stream));  // chunk_first is a stack-owned host vector
+  if (int rc = copy_shard(C, dt, tree)) return rc;
+  guard.keep = true;
+  *out = dt;
+  return M2K_OK;
+}
+
+// metadata and the shard's bytes, host to device, into the buffers of an existing device tree; timed
+static int copy_shard(Ctx* C, m2k_devtree* dt, const m2k_tree* tree) {
+  DevTree* t = &dt->t;
+  const uint32_t nd = t->n_dirs, ne = t->n_entries, nf = t->n_files;
   cudaStream_t s = C->stream;
   CU(cudaEventRecord(C->ev[0], s));
   auto H2D = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess; };
@@ -486,15 +500,26 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(H2D(t->names, tree->names, tree->n_name_bytes));
   CU(H2D(t->file_entry, tree->file_entry, 4ull * nf)); CU(H2D(t->file_off, tree->file_off, 8ull * nf));
   CU(H2D(t->file_len, tree->file_len, 8ull * nf));
-  CU(H2D(t->chunk_first, chunk_first.data(), 4ull * ((size_t)ns + 1)));
   if (tree->bytes && t->shard_bytes > 16) { if (int rc = copy_to_device(C, s, t->bytes, tree->bytes + t->shard_byte0, t->shard_bytes - 16)) return rc; }
   CU(cudaMemsetAsync(t->bytes + (t->shard_bytes - 16), 0, 16, s));
   CU(cudaEventRecord(C->ev[1], s));
-  CU(cudaStreamSynchronize(s));  // chunk_first is a stack-owned host vector
+  CU(cudaStreamSynchronize(s));
   CU(cudaEventElapsedTime(&dt->ms_h2d, C->ev[0], C->ev[1]));
-  guard.keep = true;
-  *out = dt;
   return M2K_OK;
+}
+
+// The same shard again from the host (a tree whose files changed in place, or a plugin that keeps its
+// device buffers between calls): no allocation, only the copies of m2k_upload.
+extern "C" int m2k_reupload(m2k_ctx* ctx, m2k_devtree* dt, const m2k_tree* tree) {
+  if (!ctx || !dt || !tree) return fail(ctx ? &ctx->c : nullptr, M2K_ERR_ARG, "m2k_reupload: NULL argument");
+  Ctx* C = &ctx->c;
+  DevTree* t = &dt->t;
+  if (tree->n_dirs != t->n_dirs || tree->n_entries != t->n_entries || tree->n_files != t->n_files)
+    return fail(C, M2K_ERR_ARG, "m2k_reupload: the tree has another shape than the one this device tree was made for");
+  CU(cudaSetDevice(C->device));
+  CU(cudaStreamSynchronize(C->stream));
+  t->host = tree;
+  return copy_shard(C, dt, tree);
 }
 
 extern "C" int m2k_upload(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, uint32_t file_end, m2k_devtree** out) {

@@ -31,7 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
-    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload",
 ]
 
 
@@ -102,6 +102,7 @@ def load():
     L.m2k_export_async.argtypes = [vp, vp, vp, vp, vp, vp]
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
+    L.m2k_reupload.argtypes = [vp, vp, TP]
     L.m2k_exchange_open.argtypes = [vp, vp, C.c_uint32, vp]
     L.m2k_exchange_attach.argtypes = [vp, vp, C.c_uint32, vp]
     L.m2k_exchange_attach_local.argtypes = [vp, vp, C.c_uint32, vp, vp]
@@ -211,6 +212,9 @@ class Context:
         h = C.c_void_p()
         _check(self.L.m2k_upload(self.h, tree, file_begin, file_end, C.byref(h)), self.h)
         return h
+
+    def reupload(self, dt, tree):
+        _check(self.L.m2k_reupload(self.h, dt, tree), self.h)
 
     def upload_chunks(self, tree, chunk_begin, chunk_end):
         h = C.c_void_p()

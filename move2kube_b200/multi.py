@@ -1,5 +1,11 @@
 """Multi-GPU plumbing of the path: one process per GPU, one tiny exchange at the end.
 
+Two exchanges exist.  PeerExchange (the default of bench.py) has no collective in the data path: the
+ranks' kernels reduce straight into rank 0's arrays over NVLink (CUDA IPC peer memory, include/m2kdetect.h
+m2k_exchange_*); torch.distributed only carries the 192-byte handle once, at set-up.  RankExchange gathers
+with NCCL collectives and merges on rank 0; it is kept as the comparison and as the road for boxes where
+peer memory between processes is not available.
+
 The unit of work is the 64 KiB chunk: each rank scans a contiguous range of
 chunks of near-equal bytes (lib.plan_shards / Context.upload_chunks); large files may be cut between
 ranks, everything else goes whole to one rank; the directory table is replicated.  The only exchange
@@ -115,3 +121,40 @@ class RankExchange:
         self.lib_stream.wait_stream(self.torch.cuda.current_stream())
         ctx.import_async(dt, self.allc.data_ptr(), self.allm.data_ptr(), self.allp.data_ptr(), self.flags.data_ptr(), self.world)
         return settle_undecided(ctx, tree, dt, split, fill_seed) if split else []
+
+
+class PeerExchange:
+    """The exchange over peer memory (m2k_exchange_*): rank 0 opens it on its device tree and broadcasts
+    the handle once; the other ranks attach.  After that a pass is: every rank m2k_scan (attached ranks
+    reduce into rank 0's arrays from inside their kernels and raise a flag); rank 0 m2k_prepare,
+    m2k_exchange_collect (a device-side wait + the stitching of cut files), m2k_finalize.  Nothing on
+    the host of any rank waits for another rank."""
+
+    def __init__(self, dist, torch, ctx, dt, rank, world, device="cuda"):
+        self.rank, self.world = rank, world
+        buf = torch.zeros((192,), dtype=torch.uint8, device=device)
+        if rank == 0:
+            h = ctx.exchange_open(dt, world)
+            buf.copy_(torch.frombuffer(bytearray(h), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        self.error = None
+        if rank != 0:
+            try:
+                ctx.exchange_attach(dt, rank, bytes(buf.cpu().numpy().tobytes()))
+            except lib.M2KError as e:  # e.g. a sandbox that forbids CUDA IPC between processes
+                self.error = str(e)
+        # nobody scans before everybody is attached (pass numbers must stay in step), and everybody must
+        # know whether everybody could attach
+        ok = torch.tensor([0 if self.error else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        self.ok = bool(int(ok.item()))
+
+    def after_scan(self, ctx, dt, tree=None, split=(), fill_seed=None, wait=True):
+        """Rank 0: collect and settle (call between prepare and finalize).  Others: optionally block
+        until this rank's part has been delivered."""
+        if self.rank == 0:
+            ctx.exchange_collect(dt)
+            return settle_undecided(ctx, tree, dt, split, fill_seed) if split else []
+        if wait:
+            ctx.exchange_wait(dt)
+        return []
