@@ -150,7 +150,7 @@ typedef struct m2k_tree {
  * The arrays are pinned buffers the device copies into directly.  A result of m2k_detect stays valid
  * until m2k_result_free.  A result of m2k_finalize borrows the buffers of its device tree: it is valid
  * until the next m2k_scan / m2k_prepare / m2k_finalize on that tree or its m2k_devtree_free, and must
- * be released before or together with the tree. */
+ * be released before or together with the tree.  The two ignore lists live in such buffers too. */
 typedef struct m2k_result {
   uint32_t n_dirs, n_files, n_services, n_entries;
   uint32_t* dir_opts;      /* [n_dirs] built-in option bits (M2K_DF_*, M2K_S2I_*) for EVERY directory */
@@ -221,6 +221,12 @@ int m2k_synth_fill_host(const m2k_tree* tree, uint64_t seed, uint32_t file_begin
 /* -- whole path, host buffers in, host results out (H2D + kernels + D2H): the call a plugin makes -- */
 int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_params* params, m2k_result** out);
 void m2k_result_free(m2k_result* r);
+/* -- the same on SEVERAL devices from one process (the reference's caller is one process: any2kube.go:43-46):
+ * ctxs[0..n) are contexts on distinct devices (or, for testing, on the same one); one host thread per context
+ * uploads and scans a shard (ranges of 64 KiB chunks of near-equal cost, files of >= 64 MiB may be cut between
+ * devices), the shards' kernels reduce straight into ctxs[0]'s arrays over NVLink (m2k_exchange_* with peer access;
+ * no collective library), and the calling thread assembles the result on ctxs[0].  Same result as m2k_detect. -- */
+int m2k_detect_multi(m2k_ctx* const* ctxs, uint32_t n, const m2k_tree* tree, const m2k_detect_params* params, m2k_result** out);
 /* -- the same for a tree that is looked at once, straight from the file system: the walk and numbering
  * of m2k_pack_tree, but the file bytes are never gathered on the host -- host threads read them into
  * the context's two pinned blocks while the DMA engine drains the other one.  *tree_out is the packed

@@ -534,15 +534,25 @@ struct FileArgs {
 __device__ __forceinline__ RunAcc fold_records(const FileArgs& a, uint32_t c0, uint32_t k0, uint32_t k1, uint64_t byte0, uint64_t len,
                                                uint32_t* has_main, uint32_t* not_df) {
   RunAcc acc{0, 0, 0, 0};
-  for (uint32_t k = k0; k < k1; k++) {
-    ChunkRec rec = a.chunk_rec[c0 + k];
+  auto take = [&](uint32_t k, ChunkRec rec) {
     uint64_t bstart = byte0 + (uint64_t)k * kChunkBytes;
     uint64_t nb = len - bstart < kChunkBytes ? len - bstart : kChunkBytes;
     RunAcc b{nb, rec_lead(rec), rec_trail(rec), 0};
     *has_main |= rec_main(rec);
     *not_df |= rec_not_df(rec);
     acc = acc_merge(acc, b);
+  };
+  uint32_t k = k0;
+  // long runs (a multi-GiB file has thousands of records per lane): eight loads in flight before the
+  // merges, which depend on each other
+  for (; k + 8 <= k1; k += 8) {
+    ChunkRec r[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) r[j] = a.chunk_rec[c0 + k + j];
+#pragma unroll
+    for (int j = 0; j < 8; j++) take(k + j, r[j]);
   }
+  for (; k < k1; k++) take(k, a.chunk_rec[c0 + k]);
   return acc;
 }
 

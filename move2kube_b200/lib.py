@@ -31,7 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
-    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi",
 ]
 
 
@@ -103,6 +103,7 @@ def load():
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
     L.m2k_reupload.argtypes = [vp, vp, TP]
+    L.m2k_detect_multi.argtypes = [C.POINTER(vp), C.c_uint32, TP, PP, C.POINTER(RP)]
     L.m2k_exchange_open.argtypes = [vp, vp, C.c_uint32, vp]
     L.m2k_exchange_attach.argtypes = [vp, vp, C.c_uint32, vp]
     L.m2k_exchange_attach_local.argtypes = [vp, vp, C.c_uint32, vp, vp]
@@ -314,6 +315,16 @@ class Context:
 
     def stream(self):
         return self.L.m2k_stream(self.h)
+
+
+def detect_multi(ctxs, tree, flavor=_abi.SH_BASH, pre=(), skip_content=False):
+    """m2k_detect_multi: the whole path on several devices from this one process; ctxs[0] assembles the result."""
+    L = load()
+    p, keep = make_params(flavor, pre, skip_content)
+    arr = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    rp = C.POINTER(_abi.Result)()
+    _check(L.m2k_detect_multi(arr, len(ctxs), tree, C.byref(p), C.byref(rp)), ctxs[0].h)
+    return rp
 
 
 # -- calls that need no GPU (host logic of the boundary)

@@ -486,6 +486,37 @@ def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path, exch
         ctx.tree_free(tree)
 
 
+@pytest.mark.parametrize("n", [2, 3])
+def test_detect_multi_from_one_process(ctx, oracle, n):
+    """m2k_detect_multi: one host thread per context, shards reduced into the first context's arrays over
+    peer memory.  With fewer GPUs than contexts the extra contexts share device 0 (same protocol, local
+    memory); with enough GPUs every context gets its own device.  Files of 80 MiB are cut between shards."""
+    import torch
+    n_gpus = torch.cuda.device_count()
+    ctxs = [ctx] + [lib.Context(r if r < n_gpus else 0) for r in range(1, n)]
+    p = _abi.SynthParams(seed=44, n_files=1200, n_dirs=80, max_depth=5, n_ignore_files=3, total_bytes=40 << 20,
+                         n_huge=2, huge_bytes=80 << 20, n_large=2, large_bytes=3 << 20)
+    tree = ctx.synth_tree(p, host_bytes=True)
+    try:
+        from move2kube_b200 import multi
+        cuts = lib.plan_shards(tree, n, 64 << 20, None)
+        assert multi.split_files(tree, cuts), "the test tree should have a file cut between shards"
+        whole = ctx.detect(tree)
+        ores = oracle.detect(tree, n_threads=4)
+        compare_with_oracle(oracle, tree, whole, ores)
+        for _ in range(2):
+            res = lib.detect_multi(ctxs, tree)
+            assert_same_result(tree, res, whole)
+            compare_with_oracle(oracle, tree, res, ores)
+            ctx.result_free(res)
+        oracle.lib().m2ko_result_free(ores)
+        ctx.result_free(whole)
+    finally:
+        ctx.tree_free(tree)
+        for c in ctxs[1:]:
+            c.close()
+
+
 def test_pageable_tree_goes_through_the_staging_blocks(ctx, oracle):
     """A tree whose bytes sit in ordinary (pageable) host memory is streamed to the device through the
     context's two 32 MiB pinned blocks; 90 MB makes the blocks wrap around.  Same result as the oracle."""
