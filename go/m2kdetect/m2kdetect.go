@@ -135,6 +135,71 @@ func Detect(rootPath string, preContainerized []string, dashSh bool) (*Result, e
 	return copyOut(tree, res), nil
 }
 
+// DetectMulti is Detect on several GPUs of the box from this one process (the reference's caller is a single
+// process, any2kube.go:43-46): one context per device, the tree packed once into host memory, then
+// m2k_detect_multi -- a host thread per device uploads and scans a shard, the shards reduce into device 0's
+// arrays over NVLink, device 0 assembles the result.  devices == nil uses context() alone.
+func DetectMulti(rootPath string, preContainerized []string, dashSh bool, devices []int) (*Result, error) {
+	if len(devices) <= 1 {
+		return Detect(rootPath, preContainerized, dashSh)
+	}
+	mu.Lock()
+	defer mu.Unlock()
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	n := len(devices)
+	cctxs := (**C.m2k_ctx)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
+	defer C.free(unsafe.Pointer(cctxs))
+	slots := (*[1 << 20]*C.m2k_ctx)(unsafe.Pointer(cctxs))[:n:n]
+	for i, d := range devices {
+		var c *C.m2k_ctx
+		if rc := C.m2k_ctx_create(C.int(d), &c); rc != C.M2K_OK {
+			for j := 0; j < i; j++ {
+				C.m2k_ctx_destroy(slots[j])
+			}
+			return nil, fmt.Errorf("m2kdetect: device %d: %s", d, C.GoString(C.m2k_global_error()))
+		}
+		slots[i] = c
+	}
+	defer func() {
+		for _, c := range slots {
+			C.m2k_ctx_destroy(c)
+		}
+	}()
+	croot := C.CString(rootPath)
+	defer C.free(unsafe.Pointer(croot))
+	var tree *C.m2k_tree
+	// ordinary (pageable) host memory: page-locking a whole tree costs more than reading it; the uploads stage it
+	if rc := C.m2k_pack_tree(nil, croot, 1, &tree); rc != C.M2K_OK {
+		if rc == C.M2K_ERR_NOTDIR {
+			return nil, ErrNotDir
+		}
+		return nil, fmt.Errorf("m2kdetect: pack %q: %s", rootPath, C.GoString(C.m2k_global_error()))
+	}
+	defer C.m2k_tree_free(nil, tree)
+	var params C.m2k_detect_params
+	if dashSh {
+		params.sh_flavor = C.M2K_SH_DASH
+	}
+	np := len(preContainerized)
+	carr := (**C.char)(C.malloc(C.size_t(np+1) * C.size_t(unsafe.Sizeof(uintptr(0)))))
+	defer C.free(unsafe.Pointer(carr))
+	cslots := (*[1 << 28]*C.char)(unsafe.Pointer(carr))[: np+1 : np+1]
+	for i, p := range preContainerized {
+		cslots[i] = C.CString(p)
+		defer C.free(unsafe.Pointer(cslots[i]))
+	}
+	cslots[np] = nil
+	params.n_pre = C.uint32_t(np)
+	params.pre_paths = carr
+	var res *C.m2k_result
+	if rc := C.m2k_detect_multi(cctxs, C.uint32_t(n), tree, &params, &res); rc != C.M2K_OK {
+		return nil, fmt.Errorf("m2kdetect: detect %q on %d devices: %s", rootPath, n, C.GoString(C.m2k_last_error(slots[0])))
+	}
+	defer C.m2k_result_free(res)
+	return copyOut(tree, res), nil
+}
+
 // ErrNotDir: the root exists but is not a directory for Lstat (a file, or a symlink even to a directory).
 var ErrNotDir = fmt.Errorf("m2kdetect: root is not a directory")
 

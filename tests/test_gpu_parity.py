@@ -490,12 +490,12 @@ def test_every_cut_through_files_with_boundary_cases(ctx, oracle, tmp_path, exch
 def test_detect_multi_from_one_process(ctx, oracle, n):
     """m2k_detect_multi: one host thread per context, shards reduced into the first context's arrays over
     peer memory.  With fewer GPUs than contexts the extra contexts share device 0 (same protocol, local
-    memory); with enough GPUs every context gets its own device.  Files of 80 MiB are cut between shards."""
+    memory); with enough GPUs every context gets its own device.  Files of 70 MiB (nearly all of the bytes) are cut between shards."""
     import torch
     n_gpus = torch.cuda.device_count()
     ctxs = [ctx] + [lib.Context(r if r < n_gpus else 0) for r in range(1, n)]
-    p = _abi.SynthParams(seed=44, n_files=1200, n_dirs=80, max_depth=5, n_ignore_files=3, total_bytes=40 << 20,
-                         n_huge=2, huge_bytes=80 << 20, n_large=2, large_bytes=3 << 20)
+    p = _abi.SynthParams(seed=44, n_files=1200, n_dirs=80, max_depth=5, n_ignore_files=3, total_bytes=8 << 20,
+                         n_huge=4, huge_bytes=70 << 20, n_large=2, large_bytes=3 << 20)
     tree = ctx.synth_tree(p, host_bytes=True)
     try:
         from move2kube_b200 import multi
