@@ -146,6 +146,9 @@ void launch_name_features(Ctx* c, DevTree* t) {
 #ifndef M2K_SCAN_WAVES
 #define M2K_SCAN_WAVES 32
 #endif
+#ifndef M2K_SCAN_QUOTA_WAVES
+#define M2K_SCAN_QUOTA_WAVES 0  // ticket mode: 0 = one wave of blocks that never retire; W = W waves, warps retire after a quota
+#endif
 #ifndef M2K_SCAN_TICKET
 #define M2K_SCAN_TICKET 1  // one resident wave of blocks, further chunks drawn from a counter (13.60 vs 13.75 ms on config C, 0.163 vs 0.171 on B)
 #endif
@@ -238,7 +241,8 @@ struct ScanArgs {
   const uint8_t* bytes; uint64_t shard_byte0;
   uint32_t first_skip;
   ChunkRec* chunk_rec;
-  uint32_t* ticket;  // work items beyond the first wave are drawn from this counter (NULL: strided)
+  uint32_t* ticket;  // work items are drawn from this counter (NULL: strided over the grid)
+  uint32_t quota;    // ticket mode: a warp retires after this many chunks (0: never) -- see launch_scan_bytes
 };
 
 // where work item `item` (a 64 KiB chunk of one file) lies
@@ -342,7 +346,12 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t warps_per_block = kScanThreads / 32;
   const uint32_t n_warps = gridDim.x * warps_per_block;
-  uint32_t item = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  uint32_t item = blockIdx.x * warps_per_block + (threadIdx.x >> 5), taken = 0;
+  if (a.ticket) {
+    uint32_t nx = 0;
+    if (lane == 0) nx = atomicAdd(a.ticket, 1u);
+    item = __shfl_sync(FULL, nx, 0);
+  }
   while (item < a.n_chunks) {
     const ChunkCtx c = locate_chunk(a, item);
     ChunkAcc acc{M2K_NONE, M2K_NONE, 0, 0};
@@ -357,9 +366,10 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
     }
     const ChunkRec rec = chunk_record(c, acc, lane);
     if (lane == 0) a.chunk_rec[item] = rec;
-    if (a.ticket) {  // chunks differ in size (the last chunk of a file): hand the rest out as warps come free
+    if (a.ticket) {  // chunks differ in size (the last chunk of a file): handed out as warps come free
+      if (a.quota && ++taken >= a.quota) break;
       uint32_t nx = 0;
-      if (lane == 0) nx = n_warps + atomicAdd(a.ticket, 1u);
+      if (lane == 0) nx = atomicAdd(a.ticket, 1u);
       item = __shfl_sync(FULL, nx, 0);
     } else {
       item += n_warps;
@@ -456,7 +466,7 @@ __global__ void __launch_bounds__(kBulkWarps * 32, 1) k_scan_bytes_bulk(ScanArgs
 void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket) {
   if (!t->n_chunks) return;
   ScanArgs a{t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off, t->file_len, t->file_begin,
-             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket};
+             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket, 0};
 #if defined(M2K_SCAN_BULK) && M2K_SCAN_BULK
   static bool attr_set = false;
   if (!attr_set) { cudaFuncSetAttribute(k_scan_bytes_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBulkSmem); attr_set = true; }
@@ -469,7 +479,20 @@ void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket
   uint32_t want = (t->n_chunks + warps_per_block - 1) / warps_per_block;
   uint32_t cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS * M2K_SCAN_WAVES;  // resident blocks x waves
 #if M2K_SCAN_TICKET
-  if (a.ticket) cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS;  // one resident wave; the rest is drawn from the counter
+  if (a.ticket) {
+#if M2K_SCAN_QUOTA_WAVES
+    // Chunks come from a counter, but a warp retires after `quota` of them and the grid holds several
+    // waves of blocks: a block lives for a fraction of the scan, so the high-priority blocks of the
+    // directory-level kernels (side stream) find a free slot within that fraction instead of after the
+    // whole scan -- which is what a single wave of never-retiring blocks makes them do.  The quota is
+    // twice the even share: late blocks find the counter exhausted and leave at once.
+    cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS * M2K_SCAN_QUOTA_WAVES;
+    const uint32_t grid_warps = (want < cap ? want : cap) * warps_per_block;
+    a.quota = 2 * ((t->n_chunks + grid_warps - 1) / grid_warps);
+#else
+    cap = (uint32_t)c->sm_count * M2K_SCAN_MINBLOCKS;  // one resident wave, never retiring
+#endif
+  }
 #else
   a.ticket = nullptr;
 #endif
@@ -543,8 +566,8 @@ __device__ __forceinline__ RunAcc fold_records(const FileArgs& a, uint32_t c0, u
     acc = acc_merge(acc, b);
   };
   uint32_t k = k0;
-  // long runs (a multi-GiB file has thousands of records per lane): eight loads in flight before the
-  // merges, which depend on each other
+  // long runs (the share of a multi-GiB file's records one thread folds): eight loads in flight before
+  // the merges, which depend on each other
   for (; k + 8 <= k1; k += 8) {
     ChunkRec r[8];
 #pragma unroll
@@ -598,11 +621,15 @@ __device__ __forceinline__ void finish_file(const FileArgs& a, uint32_t i, uint3
 }
 
 __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
-  const uint32_t lane = threadIdx.x & 31;
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ uint32_t s_big[256], s_nbig, s_has[2];
+  __shared__ RunAcc s_part[8];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t i = blockIdx.x * blockDim.x + tid;
   const bool valid = i < a.n_shard_files;
   uint32_t f = 0, c0 = 0, nc = 0;
   uint64_t len = 0, byte0 = 0;
+  if (tid == 0) s_nbig = 0;
+  __syncthreads();
   if (valid) {
     f = a.file_begin + i;
     len = a.file_len[f];
@@ -614,30 +641,42 @@ __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
     uint32_t has_main = 0, not_df = 0;
     RunAcc tot = fold_records(a, c0, 0, nc, byte0, len, &has_main, &not_df);
     finish_file(a, i, f, tot, len, has_main, not_df);
+  } else if (valid) {
+    s_big[atomicAdd(&s_nbig, 1u)] = tid;
   }
-  // files with many chunks (config D's multi-GiB files): the warp folds them together, one at a time
-  uint32_t big = __ballot_sync(FULL, valid && nc > kCombineWarpChunks);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t bi = __shfl_sync(FULL, i, src), bf = __shfl_sync(FULL, f, src), bc0 = __shfl_sync(FULL, c0, src), bnc = __shfl_sync(FULL, nc, src);
-    const uint64_t blen = __shfl_sync(FULL, len, src), bbyte0 = __shfl_sync(FULL, byte0, src);
-    const uint32_t per = (bnc + 31) / 32;
-    const uint32_t k0 = lane * per < bnc ? lane * per : bnc, k1 = (lane + 1) * per < bnc ? (lane + 1) * per : bnc;
+  __syncthreads();
+  // files with many chunks (config D's multi-GiB files: 65 536 records each): the whole block folds them,
+  // one at a time -- 256 contiguous shares, merged in order through the warps
+  const uint32_t n_big = s_nbig;
+  for (uint32_t b = 0; b < n_big; b++) {
+    const uint32_t bi = blockIdx.x * blockDim.x + s_big[b], bf = a.file_begin + bi;
+    const uint64_t blen = a.file_len[bf], bbyte0 = bi == 0 ? (uint64_t)a.first_skip * kChunkBytes : 0;
+    const uint32_t bc0 = a.chunk_first[bi], bnc = a.chunk_first[bi + 1] - bc0;
+    const uint32_t per = (bnc + 255) / 256;
+    const uint32_t k0 = tid * per < bnc ? tid * per : bnc, k1 = (tid + 1) * per < bnc ? (tid + 1) * per : bnc;
     uint32_t has_main = 0, not_df = 0;
     RunAcc acc = fold_records(a, bc0, k0, k1, bbyte0, blen, &has_main, &not_df);
-    has_main = __any_sync(FULL, has_main);
-    not_df = __any_sync(FULL, not_df);
+    if (tid < 2) s_has[tid] = 0;
     RunAcc tot{0, 0, 0, 0};
-    for (int l = 0; l < 32; l++) {
-      RunAcc b;
-      b.bytes = __shfl_sync(FULL, acc.bytes, l);
-      b.lead = __shfl_sync(FULL, acc.lead, l);
-      b.trail = __shfl_sync(FULL, acc.trail, l);
-      b.longf = __shfl_sync(FULL, acc.longf, l);
-      if (lane == 0) tot = acc_merge(tot, b);
+    for (int l = 0; l < 32; l++) {  // the warp's 32 shares, in order, on lane 0
+      RunAcc x;
+      x.bytes = __shfl_sync(FULL, acc.bytes, l);
+      x.lead = __shfl_sync(FULL, acc.lead, l);
+      x.trail = __shfl_sync(FULL, acc.trail, l);
+      x.longf = __shfl_sync(FULL, acc.longf, l);
+      if (lane == 0) tot = acc_merge(tot, x);
     }
-    if (lane == 0) finish_file(a, bi, bf, tot, blen, has_main, not_df);
+    if (lane == 0) s_part[warp] = tot;
+    __syncthreads();
+    if (has_main) atomicOr(&s_has[0], 1u);
+    if (not_df) atomicOr(&s_has[1], 1u);
+    __syncthreads();
+    if (tid == 0) {
+      RunAcc all{0, 0, 0, 0};
+      for (int w = 0; w < 8; w++) all = acc_merge(all, s_part[w]);
+      finish_file(a, bi, bf, all, blen, s_has[0], s_has[1]);
+    }
+    __syncthreads();
   }
 }
 

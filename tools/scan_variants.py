@@ -18,6 +18,10 @@ VARIANTS = {
     "base": [],
     # round 2: work items drawn from a counter instead of strided; the bulk-copy engine (cp.async.bulk + mbarrier
     # rings in shared memory) feeding the same scan
+    "quota16": ["M2K_SCAN_QUOTA_WAVES=16"],
+    "quota32": ["M2K_SCAN_QUOTA_WAVES=32"],
+    "quota64": ["M2K_SCAN_QUOTA_WAVES=64"],
+    "mb3": ["M2K_SCAN_MINBLOCKS=3"],
     "strided": ["M2K_SCAN_TICKET=0"],  # round 1's distribution: item += number of warps, 32 waves of blocks
     "bulk_w16_s3": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=3"],
     "bulk_w24_s2": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=24", "M2K_BULK_STAGES=2"],
