@@ -122,6 +122,45 @@ func (c *Containerizers) InitContainerizersGPU(path string, res *m2kdetect.Resul
 	cnb := new(CNBContainerizer)
 	reuse := new(ReuseContainerizer)
 	c.containerizers = []Containerizer{df, s2i, cnb, reuse}
+	c.rememberOutputs(res)
+}
+
+// planTimeOutputs: stdout of the accepting built-in detect scripts, keyed by option directory and service
+// directory, as computed by the detection pass (m2kdetect.Result.OptionJSON).  GetContainer re-runs the detect
+// script only to read this JSON (dockerfilecontainerizer.go:105-129, s2icontainerizer.go:97-115); with the two-line
+// change to detect() shown in INTEGRATION.md it takes it from here instead: no fork/exec, no second grep -R.
+var planTimeOutputs = map[[2]string]string{}
+
+// CachedDetectOutput returns the plan-time stdout of scriptDir's detect script for directory, if the GPU pass has it.
+func CachedDetectOutput(scriptDir, directory string) (string, bool) {
+	out, ok := planTimeOutputs[[2]string{scriptDir, directory}]
+	return out, ok
+}
+
+func (c *Containerizers) rememberOutputs(res *m2kdetect.Result) {
+	for _, cz := range c.containerizers {
+		var g *gpuScriptContainerizer
+		var dirs []string
+		switch v := cz.(type) {
+		case *DockerfileGPUContainerizer:
+			g, dirs = &v.gpu, v.dfcontainerizers
+		case *S2IGPUContainerizer:
+			g, dirs = &v.gpu, v.s2icontainerizers
+		default:
+			continue
+		}
+		for _, optionDir := range dirs {
+			i := g.builtinIndex(optionDir)
+			if i < 0 {
+				continue
+			}
+			for d, byBit := range res.OptionJSON {
+				if out, ok := byBit[int(g.shift)+i]; ok {
+					planTimeOutputs[[2]string{optionDir, res.DirPath[d]}] = out
+				}
+			}
+		}
+	}
 }
 
 // NeedsHostOptions reports whether any option must be evaluated on the host per visited directory

@@ -86,6 +86,10 @@ type Result struct {
 	IgnoreDirs   []string
 	IgnoreConts  []string
 	KernelMillis float32
+	// OptionJSON[d][bit]: what the accepting built-in detect script `bit` (DirOpts bit number) prints on stdout for
+	// service directory d -- the JSON GetContainer re-runs the script for at translate time
+	// (dockerfilecontainerizer.go:105-129, s2icontainerizer.go:97-115); from m2k_option_json, nothing executed
+	OptionJSON map[uint32]map[int]string
 }
 
 // Detect walks rootPath once and runs the whole path on the GPU.  It uses m2k_pack_detect: the file bytes
@@ -288,6 +292,21 @@ func copyOut(t *C.m2k_tree, r *C.m2k_result) *Result {
 		out.IgnoreConts = append(out.IgnoreConts, C.GoString(p))
 	}
 	out.KernelMillis = float32(r.ms_kernels)
+	out.OptionJSON = map[uint32]map[int]string{}
+	buf := (*C.char)(C.malloc(8192))
+	defer C.free(unsafe.Pointer(buf))
+	for _, d := range out.ServiceDirs {
+		m := map[int]string{}
+		for bit := 0; bit < int(C.M2K_N_OPTS); bit++ {
+			if out.DirOpts[d]>>uint(bit)&1 == 0 {
+				continue
+			}
+			if n := C.m2k_option_json(t, r, C.uint32_t(d), C.uint32_t(bit), buf, 8192); n >= 0 {
+				m[bit] = C.GoStringN(buf, n)
+			}
+		}
+		out.OptionJSON[d] = m
+	}
 	return out
 }
 

@@ -354,6 +354,17 @@ int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d_bytes, con
                            const uint64_t* d_file_len, const uint32_t* d_chunk_first, uint32_t n_files,
                            uint32_t n_chunks, uint8_t* d_file_flags);
 
+/* -- translate-time re-detection without re-running anything: the bytes the accepting
+ * detect script of built-in option `option` (M2K_DF_* / M2K_S2I_*) prints on stdout for directory `dir` -- the JSON
+ * DockerfileContainerizer.GetContainer / S2IContainerizer.GetContainer re-run the script for
+ * (dockerfilecontainerizer.go:105-129, s2icontainerizer.go:97-115): constants, the directory's first *.war entry, or
+ * the main script the byte scan found (`main_script_rel_path` / `app_file`: the lowest file id under the directory;
+ * the reference's answer is the first path `grep -R` prints, which depends on readdir order).  Returns the number
+ * of bytes written (without the terminating NUL; buf == NULL only asks for the size), M2K_ERR_ARG when the option
+ * does not accept the directory (its script prints nothing and exits 1), M2K_ERR_LIMIT when cap is too small.
+ * Host code, no device needed; `res` must come from a pass with content (skip_content = 0) for the python options. -- */
+int m2k_option_json(const m2k_tree* tree, const m2k_result* res, uint32_t dir, uint32_t option, char* buf, size_t cap);
+
 /* -- host-side path helpers the mirror needs (Go stdlib semantics) -- */
 int m2k_path_clean(const char* path, char* out, size_t cap);              /* filepath.Clean */
 int m2k_equal_fold(const char* a, size_t na, const char* b, size_t nb);   /* strings.EqualFold */

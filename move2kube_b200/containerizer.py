@@ -75,8 +75,21 @@ class _ScriptContainerizer:
         for f in _find_scripts(path, self.script):
             self.options.append(os.path.dirname(f))
 
-    def detect(self, scriptDir: str, directory: str):
-        """dockerfilecontainerizer.go:76-83 -- only reached for user-supplied option directories."""
+    def detect(self, scriptDir: str, directory: str, det: "detection.Detection" = None):
+        """dockerfilecontainerizer.go:76-83: (stdout, err) of the option's detect script for `directory`.
+        For a built-in option the answer comes from the detection pass (m2k_option_json: the script's stdout
+        byte for byte, nothing executed) -- this is the call GetContainer makes again at translate time
+        (dockerfilecontainerizer.go:105-129, s2icontainerizer.go:97-115).  User-supplied option directories
+        are arbitrary shell and are executed exactly as the reference executes them."""
+        det = det or self._det
+        idx = _builtin_index(scriptDir, self.kind)
+        if idx is not None and det is not None:
+            d = det.dir_id(directory)
+            if d >= 0:
+                out = det.option_json(d, self.opt_shift + idx)
+                if out is None:
+                    return "", RuntimeError("exit status 1")
+                return out.decode("utf-8", "replace"), None
         try:
             p = subprocess.run(["/bin/sh", self.script, directory], cwd=scriptDir, stdout=subprocess.PIPE)
         except OSError as e:

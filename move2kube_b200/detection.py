@@ -138,6 +138,12 @@ class Detection:
             return []
         return [self.entry_path(e) for e in lib.list_entries(self.tree, 0, feat)]
 
+    def option_json(self, d: int, option: int):
+        """What the accepting built-in detect script `option` (a DirOpts bit number: 0-11 Dockerfile options,
+        12-17 S2I) prints for directory d, from this pass's arrays -- nothing is executed (m2k_option_json).
+        None = the option does not accept the directory."""
+        return lib.option_json(self.tree, self.res, d, option)
+
     def main_script_rel_path(self, d: int) -> str:
         """What the python detect scripts print as main_script_rel_path / app_file (a11)."""
         f = self.dir_main_file[d]

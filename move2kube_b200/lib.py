@@ -31,7 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
-    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi", "m2k_option_json",
 ]
 
 
@@ -103,6 +103,7 @@ def load():
     L.m2k_import_async.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint32]
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
     L.m2k_reupload.argtypes = [vp, vp, TP]
+    L.m2k_option_json.argtypes = [TP, RP, C.c_uint32, C.c_uint32, C.c_char_p, C.c_size_t]
     L.m2k_detect_multi.argtypes = [C.POINTER(vp), C.c_uint32, TP, PP, C.POINTER(RP)]
     L.m2k_exchange_open.argtypes = [vp, vp, C.c_uint32, vp]
     L.m2k_exchange_attach.argtypes = [vp, vp, C.c_uint32, vp]
@@ -367,6 +368,22 @@ def chunk_locate(tree, chunk):
     f, k = C.c_uint32(), C.c_uint32()
     _check(load().m2k_chunk_locate(tree, chunk, C.byref(f), C.byref(k)))
     return f.value, k.value
+
+
+def option_json(tree, res, d: int, option: int):
+    """Stdout of the accepting built-in detect script `option` for directory d (bytes), or None when the
+    option does not accept the directory."""
+    L = load()
+    n = L.m2k_option_json(tree, res, d, option, None, 0)
+    if n == _abi.ERR_ARG:
+        return None
+    if n < 0:
+        raise M2KError(n, (L.m2k_global_error() or b"").decode("utf-8", "replace"))
+    buf = C.create_string_buffer(n + 1)
+    n = L.m2k_option_json(tree, res, d, option, buf, n + 1)
+    if n < 0:
+        raise M2KError(n, (L.m2k_global_error() or b"").decode("utf-8", "replace"))
+    return buf.raw[:n]
 
 
 def path_clean(p: bytes) -> bytes:

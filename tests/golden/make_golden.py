@@ -91,11 +91,21 @@ def run_oracle(root: str, pre=()):
                           s["containerBuildType"], [opt_name(t, broot) for t in s["targetOptions"]]]
                          for s in services],
             "main_script": {},
+            # what every accepting detect script printed on stdout, per service directory and option: the JSON that
+            # GetContainer re-runs the script for at translate time (dockerfilecontainerizer.go:105-129, s2icontainerizer.go:97-115)
+            "outputs": {},
         }
         dir_links = os.path.isdir(root) and has_dir_symlink(broot)
         for p, action, cops in trace:
             if action != "service":
                 continue
+            outs = {}
+            for c in cs.list:
+                if isinstance(c, so.ScriptContainerizer):
+                    for (od, d), stdout in c.outputs.items():
+                        if d == p:
+                            outs[opt_name(od, broot)] = stdout.decode("latin-1")  # bytes kept one to one
+            exp["outputs"][rel(p, broot)] = outs
             ms = so.main_script_rel_path(cs, p)
             if ms:
                 exp["main_script"][rel(p, broot)] = {

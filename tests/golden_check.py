@@ -111,6 +111,44 @@ def check(spec, flavor, view, res, root: bytes):
             assert all(v in cands for v in ms["script_said"].values())
 
 
+def check_outputs(spec, flavor, view, tree, res):
+    """f3: m2k_option_json against what the reference's own scripts printed (expect[flavor]["outputs"], recorded by
+    make_golden.py): byte for byte for every option that prints a constant or the war file; for the python options
+    the path must be one the reference's grep could have printed (same rule as the main_script check above).
+    Returns the number of (directory, option) outputs compared."""
+    import json
+    from move2kube_b200 import lib
+    exp = spec["expect"][flavor]
+    rel_to_dir = {view.dir_rel[d]: d for d in range(view.n_dirs)}
+    names = ["m2kassets/dockerfiles/" + n for n in _abi.DF_NAMES] + ["m2kassets/s2i/" + n for n in _abi.S2I_NAMES]
+    n = 0
+    for rel, outs in exp.get("outputs", {}).items():
+        d = rel_to_dir[os.fsencode(rel)]
+        cands = (exp["main_script"].get(rel) or {}).get("candidates")
+        for opt, name in enumerate(names):
+            got = lib.option_json(tree, res, d, opt)
+            if name not in outs:
+                assert got is None, "dir %r option %s: the script did not accept, m2k_option_json answers %r" % (rel, name, got)
+                continue
+            want = outs[name].encode("latin-1")
+            assert got is not None, "dir %r option %s" % (rel, name)
+            n += 1
+            if name.endswith("/python"):
+                key = "main_script_rel_path" if "dockerfiles" in name else "app_file"
+                gj, wj = json.loads(got), json.loads(want)
+                if cands is None:      # symlinked directories in the tree: the packed tree does not follow them
+                    gj.pop(key), wj.pop(key)
+                elif cands:
+                    assert gj.pop(key) in cands and wj.pop(key) in cands
+                assert gj == wj, "dir %r option %s: %r vs %r" % (rel, name, got, want)
+                # and the same bytes around the path: key order, spacing, no trailing newline (printf)
+                tail = b'", "app_name": "app", "port": 8080}'
+                assert got.endswith(tail) and want.endswith(tail) and got.split(b'"')[0:3] == want.split(b'"')[0:3]
+            else:
+                assert got == want, "dir %r option %s: %r vs %r" % (rel, name, got, want)
+    return n
+
+
 def reference_plans():
     with open(os.path.join(GOLDEN_DIR, "_reference_plans.json")) as f:
         return json.load(f)

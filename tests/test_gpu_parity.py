@@ -55,6 +55,8 @@ def test_golden_fixture(ctx, oracle, tmp_path, spec, flavor):
             assert res.contents.n_kernel_launches >= 3
             if not gc.has_user_scripts(spec):
                 gc.check(spec, flavor, gc.TreeView(tree), res, root)
+                n_out = gc.check_outputs(spec, flavor, gc.TreeView(tree), tree, res)
+                assert n_out >= sum(len(v) for v in spec["expect"][flavor]["outputs"].values())
             ores = oracle.detect(tree, fl, pre)
             compare_with_oracle(oracle, tree, res, ores)
             oracle.lib().m2ko_result_free(ores)

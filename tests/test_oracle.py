@@ -78,3 +78,32 @@ def test_c_oracle_agrees_with_the_reference_scripts_on_generator_trees(oracle, t
     _, tree, res = sb.c_oracle_pass(root)
     bad, lists_ok = sb.compare(root, trace, services, ign_d, ign_c, tree, res)
     assert bad == [] and lists_ok
+
+
+@pytest.mark.parametrize("spec", [g for g in gc.load_goldens() if not g.get("nonexistent") and not gc.has_user_scripts(g)], ids=lambda g: g["name"])
+@pytest.mark.parametrize("flavor", ["bash", "dash"])
+def test_option_json_matches_what_the_scripts_print(oracle, tmp_path, spec, flavor):
+    """f3 without a GPU: m2k_option_json (host code of the product library) over the ORACLE's per-directory arrays
+    must reproduce the stdout the reference's scripts printed for every accepted (directory, option) of every
+    golden tree.  The -m gpu tier runs the same check over the device's arrays (test_gpu_parity.test_golden_fixture)."""
+    import ctypes as C
+    from move2kube_b200 import _abi, lib
+    root = os.fsencode(treespec.materialize(spec, str(tmp_path / spec["name"])))
+    fl = _abi.SH_BASH if flavor == "bash" else _abi.SH_DASH
+    pre = [oracle.join(root, os.fsencode(p)) if p != "." else root for p in spec.get("pre", [])]
+    tree = lib.pack_tree_host(root)
+    try:
+        ores = oracle.detect(tree, fl, pre)
+        o, t = ores.contents, tree.contents
+        view = gc.TreeView(tree)
+        direct = (C.c_uint32 * max(1, t.n_dirs))()
+        for e in range(t.n_entries):  # the one name feature m2k_option_json looks at: [ -f D/pom.xml ]
+            if view.entry_name[e] == b"pom.xml" and (t.entry_type[e] >> 4) == _abi.T_REG:
+                direct[t.entry_dir[e]] |= 1 << 3
+        res = _abi.Result(n_dirs=t.n_dirs, n_files=t.n_files, n_entries=t.n_entries, dir_opts=o.dir_opts,
+                          dir_direct=C.cast(direct, _abi.u32p), dir_main_file=o.dir_main_file)
+        n = gc.check_outputs(spec, flavor, view, tree, C.pointer(res))
+        assert n == sum(len(v) for v in spec["expect"][flavor]["outputs"].values())
+        oracle.lib().m2ko_result_free(ores)
+    finally:
+        lib.tree_free_host(tree)
