@@ -215,6 +215,7 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   if (C->copy_stream) cudaStreamSynchronize(C->copy_stream);
   if (C->side_stream) cudaStreamSynchronize(C->side_stream);
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
+  for (auto& A : C->arena) if (A.p) cudaFree(A.p);
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
   for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
   if (C->ev_idle) cudaEventDestroy(C->ev_idle);
@@ -233,6 +234,14 @@ extern "C" int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes,
   if (sm_count) *sm_count = p.multiProcessorCount;
   if (hbm_bytes) *hbm_bytes = p.totalGlobalMem;
   if (name && name_cap) { strncpy(name, p.name, name_cap - 1); name[name_cap - 1] = 0; }
+  return M2K_OK;
+}
+
+extern "C" int m2k_ctx_trim(m2k_ctx* ctx) {
+  if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  for (auto& A : C->arena) if (A.p && !A.in_use) { cudaFree(A.p); A.p = nullptr; A.cap = 0; }
   return M2K_OK;
 }
 
@@ -307,6 +316,11 @@ static void devtree_release(DevTree* t) {
   if (t->link.ipc_base) { cudaIpcCloseMemHandle(t->link.ipc_base); t->link.ipc_base = nullptr; }
   // (dir_direct, dir_content, dir_subtree, file_flags, df_counters, special, dir_first_war, dir_main and
   // dir_main_sub live inside the slab)
+  if (t->arena_ctx) {  // hand the big buffers back to the context instead of freeing them
+    if (t->from_arena & 1u) { t->arena_ctx->arena[0].in_use = false; t->bytes = nullptr; }
+    if (t->from_arena & 2u) { t->arena_ctx->arena[1].in_use = false; t->stripe_state = nullptr; }
+    t->from_arena = 0;
+  }
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->slab, t->early,
@@ -334,6 +348,25 @@ extern "C" void m2k_devtree_free(m2k_ctx* ctx, m2k_devtree* dt) {
 }
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// `bytes` bytes from the context's arena k when it is free (growing it when too small), else a plain allocation
+static cudaError_t arena_alloc(Ctx* C, DevTree* t, int k, void** out, size_t bytes) {
+  Ctx::Arena& A = C->arena[k];
+  if (!bytes) bytes = 1;
+  if (A.in_use) return cudaMalloc(out, bytes);
+  if (A.cap < bytes) {
+    if (A.p) cudaFree(A.p);
+    A.p = nullptr; A.cap = 0;
+    cudaError_t e = cudaMalloc(&A.p, bytes);
+    if (e != cudaSuccess) return e;
+    A.cap = bytes;
+  }
+  A.in_use = true;
+  t->arena_ctx = C;
+  t->from_arena |= 1u << k;
+  *out = A.p;
+  return cudaSuccess;
+}
 
 template <typename T>
 static cudaError_t dev_alloc(T** p, size_t n) { return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)); }
@@ -425,7 +458,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(dev_alloc(&t->entry_type, ne)); CU(dev_alloc(&t->names, (size_t)tree->n_name_bytes));
   CU(dev_alloc(&t->file_entry, nf)); CU(dev_alloc(&t->file_off, nf)); CU(dev_alloc(&t->file_len, nf));
   CU(dev_alloc(&t->chunk_first, (size_t)ns + 1));
-  CU(dev_alloc(&t->bytes, (size_t)t->shard_bytes));
+  CU(arena_alloc(C, t, 0, (void**)&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne)); CU(dev_alloc(&t->pieces, 2));
   {
     // isDockerFile scratch (DevTree): sized for the worst case, every file a candidate
@@ -436,7 +469,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
     t->tile_cap = (uint32_t)cap;
     CU(dev_alloc(&t->head_list, ns)); CU(dev_alloc(&t->cand_file, ns)); CU(dev_alloc(&t->cand_stripe0, ns)); CU(dev_alloc(&t->cand_done, ns));
     CU(dev_alloc(&t->cand_err, ns)); CU(dev_alloc(&t->cand_body, ns)); CU(dev_alloc(&t->cand_esc, ns));
-    CU(dev_alloc(&t->stripe_state, scap)); CU(dev_alloc(&t->tile_state, cap));
+    CU(arena_alloc(C, t, 1, (void**)&t->stripe_state, scap)); CU(dev_alloc(&t->tile_state, cap));
     CU(cudaMemsetAsync(t->tile_state, 0, 4ull * cap, C->stream));  // once: pass numbers start at 1
   }
   {

@@ -114,6 +114,8 @@ struct DevTree {
   uint64_t *file_off = nullptr, *file_len = nullptr;  // [n_files] (all files; offsets are tree-global)
   uint32_t* chunk_first = nullptr;        // [shard files + 1] prefix of ceil(len / kChunkBytes) over the shard
   uint8_t* bytes = nullptr;               // shard bytes; byte 0 is tree offset shard_byte0
+  struct Ctx* arena_ctx = nullptr;        // the context whose arena `bytes` / `stripe_state` came from (bit 0 / 1 of from_arena)
+  uint32_t from_arena = 0;
   // synthetic content description (device copies), only for m2k_synth_fill_device
   uint8_t* synth_class = nullptr;
   uint64_t* synth_inject = nullptr;
@@ -178,6 +180,10 @@ struct Ctx {
   // two pinned blocks through which bytes held in pageable host memory are streamed to the device
   void* stage[2] = {nullptr, nullptr};
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
+  // the two allocations that grow with the shard -- its bytes and the Dockerfile stripe states -- are kept by the
+  // context when a device tree is released and handed to the next one that fits (grow-only): a plugin that
+  // detects tree after tree does not pay cudaMalloc / cudaFree of tens of GB per call (m2k_ctx_trim drops them)
+  struct Arena { void* p = nullptr; size_t cap = 0; bool in_use = false; } arena[2];
   float phase_ms[8] = {};  // names, scan, combine, dockerfile, finalize kernels, host ignore, host verify, d2h
   int sm_count = 0;
   uint64_t launches = 0;
