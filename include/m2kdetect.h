@@ -189,9 +189,11 @@ const char* m2k_global_error(void);
 int m2k_ctx_create(int device, m2k_ctx** out);
 void m2k_ctx_destroy(m2k_ctx* ctx);
 const char* m2k_last_error(const m2k_ctx* ctx);
-/* a context keeps the two device buffers that grow with a shard (its bytes, the Dockerfile stripe states) when a
- * device tree is released and hands them to the next one that fits, so that repeated m2k_detect calls do not pay
- * cudaMalloc / cudaFree of the whole tree each time; m2k_ctx_trim gives the idle ones back to the driver */
+/* a context keeps the two device buffers that grow with a shard (its bytes, the Dockerfile stripe states) and the
+ * page-locked host blocks of its results when they are released, and hands them to the next call that fits, so
+ * that repeated m2k_detect calls pay neither cudaMalloc / cudaFree of the whole tree nor page-locking each time;
+ * m2k_ctx_trim gives the idle ones back to the driver.  Release every result and device tree of a context
+ * before destroying it. */
 int m2k_ctx_trim(m2k_ctx* ctx);
 int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes, char* name, size_t name_cap);
 

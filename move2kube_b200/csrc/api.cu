@@ -27,18 +27,41 @@ constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2k
 // what m2k_prepare / m2k_finalize derive from the .m2kignore files (host side of a2 / a4)
 struct Folded { uint64_t key; uint32_t off, len, flag; };  // one ignore entry: hash of its folded runes, where they are
 
+// pinned host blocks from the context's pool (Ctx::pinned_pool); a NULL context means plain cudaHostAlloc
+static void* pinned_take(Ctx* C, size_t bytes) {
+  if (!bytes) bytes = 16;
+  if (C) {
+    Ctx::PinnedBlock* best = nullptr;
+    for (auto& b : C->pinned_pool)
+      if (!b.in_use && b.cap >= bytes && (!best || b.cap < best->cap)) best = &b;
+    if (best && best->cap <= 4 * bytes + (1u << 20)) { best->in_use = true; return best->p; }
+  }
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (C) C->pinned_pool.push_back({p, bytes, true});
+  return p;
+}
+static void pinned_give(Ctx* C, void* p) {
+  if (!p) return;
+  if (C)
+    for (auto& b : C->pinned_pool)
+      if (b.p == p) { b.in_use = false; return; }
+  cudaFreeHost(p);
+}
+
 // grow-only host buffer the ignore table is built in.  Pinned in the product: a copy from pageable
 // memory would make m2k_prepare wait for the byte scan queued ahead of it.
 struct Staging {
   void* p = nullptr;
   size_t cap = 0;
   bool pinned = true;
+  Ctx* pool = nullptr;  // pinned blocks come from / go back to this context's pool
   // room for `bytes`; the first `keep` bytes survive a reallocation
   bool reserve(size_t bytes, size_t keep) {
     if (bytes <= cap) return true;
     const size_t want = bytes * 2;
     void* q = nullptr;
-    if (pinned) { if (cudaHostAlloc(&q, want, cudaHostAllocDefault) != cudaSuccess) return false; }
+    if (pinned) { if (!(q = pinned_take(pool, want))) return false; }
     else if (!(q = malloc(want))) return false;
     if (keep) memcpy(q, p, keep);
     release();
@@ -46,7 +69,7 @@ struct Staging {
     return true;
   }
   void release() {
-    if (p) { if (pinned) cudaFreeHost(p); else free(p); }
+    if (p) { if (pinned) pinned_give(pool, p); else free(p); }
     p = nullptr; cap = 0;
   }
 };
@@ -84,6 +107,7 @@ struct m2k_devtree {
   uint32_t* h_entry_feat = nullptr;  // pinned
   uint32_t* h_special = nullptr;     // pinned: [0] count, then entry ids
   Staging stage;                     // pinned staging of the ignore table (grow-only)
+  Ctx* ctx = nullptr;                // the context whose pinned pool the host buffers below belong to
   m2k_result* pending = nullptr;     // result shell made by m2k_prepare
   uint8_t* h_results = nullptr;      // pinned: every per-directory / per-file result array (see result_layout)
   bool content = true;
@@ -216,6 +240,7 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   if (C->side_stream) cudaStreamSynchronize(C->side_stream);
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
   for (auto& A : C->arena) if (A.p) cudaFree(A.p);
+  for (auto& b : C->pinned_pool) cudaFreeHost(b.p);  // results must have been released before their context
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
   for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
   if (C->ev_idle) cudaEventDestroy(C->ev_idle);
@@ -242,6 +267,10 @@ extern "C" int m2k_ctx_trim(m2k_ctx* ctx) {
   Ctx* C = &ctx->c;
   CU(cudaSetDevice(C->device));
   for (auto& A : C->arena) if (A.p && !A.in_use) { cudaFree(A.p); A.p = nullptr; A.cap = 0; }
+  for (size_t i = 0; i < C->pinned_pool.size();) {
+    if (!C->pinned_pool[i].in_use) { cudaFreeHost(C->pinned_pool[i].p); C->pinned_pool.erase(C->pinned_pool.begin() + i); }
+    else i++;
+  }
   return M2K_OK;
 }
 
@@ -331,11 +360,11 @@ static void devtree_release(DevTree* t) {
 
 // pinned host buffers and the object itself (device memory is released separately)
 static void free_devtree_shell(m2k_devtree* dt) {
-  if (dt->h_entry_feat) cudaFreeHost(dt->h_entry_feat);
-  if (dt->h_special) cudaFreeHost(dt->h_special);
+  pinned_give(dt->ctx, dt->h_entry_feat);
+  pinned_give(dt->ctx, dt->h_special);
   dt->stage.release();
   free(dt->lists[0].p); free(dt->lists[1].p);
-  if (dt->h_results) cudaFreeHost(dt->h_results);
+  pinned_give(dt->ctx, dt->h_results);
   if (dt->pending) { m2k_result* p = dt->pending; dt->pending = nullptr; p->owner = nullptr; m2k_result_free(p); }
   delete dt;
 }
@@ -416,6 +445,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
                        m2k_devtree** out) {
   Ctx* C = &ctx->c;
   *out = nullptr;
+  const double t_setup = now_ms();
   CU(cudaSetDevice(C->device));
   m2k_devtree* dt = new m2k_devtree();
   DevTree* t = &dt->t;
@@ -511,12 +541,16 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   }
   CU(dev_alloc(&t->dir_descend, nd));
 
-  CU(cudaHostAlloc((void**)&dt->h_entry_feat, 4ull * (ne ? ne : 1), cudaHostAllocDefault));
-  CU(cudaHostAlloc((void**)&dt->h_special, 4ull * (kSpecialCap + 1), cudaHostAllocDefault));
-  CU(cudaHostAlloc((void**)&dt->h_results, 5 * align256(4ull * (nd ? nd : 1)) + 2 * align256(nd ? nd : 1) + nf + 256, cudaHostAllocDefault));
+  dt->ctx = C;
+  dt->stage.pool = C;
+  dt->h_entry_feat = (uint32_t*)pinned_take(C, 4ull * (ne ? ne : 1));
+  dt->h_special = (uint32_t*)pinned_take(C, 4ull * (kSpecialCap + 1));
+  dt->h_results = (uint8_t*)pinned_take(C, 5 * align256(4ull * (nd ? nd : 1)) + 2 * align256(nd ? nd : 1) + nf + 256);
+  if (!dt->h_entry_feat || !dt->h_special || !dt->h_results) return fail(C, M2K_ERR_NOMEM, "out of pinned host memory for the result buffers");
   t->special_cap = kSpecialCap;
   CU(cudaMemcpyAsync(t->chunk_first, chunk_first.data(), 4ull * ((size_t)ns + 1), cudaMemcpyHostToDevice, C->stream));
   CU(cudaStreamSynchronize(C->stream));  // chunk_first is a stack-owned host vector
+  if (getenv("M2K_DEBUG_TIMING")) fprintf(stderr, "[m2k] upload: set-up (layout, allocations, pinned result buffers) %.2f ms\n", now_ms() - t_setup);
   if (int rc = copy_shard(C, dt, tree)) return rc;
   guard.keep = true;
   *out = dt;
@@ -1472,15 +1506,19 @@ extern "C" int m2k_detect(m2k_ctx* ctx, const m2k_tree* tree, const m2k_detect_p
   m2k_devtree* dt = nullptr;
   int rc = m2k_upload(ctx, tree, 0, content ? tree->n_files : 0, &dt);
   if (rc != M2K_OK) return rc;
+  const double t1 = now_ms();
   rc = m2k_scan(ctx, dt, params);
   if (rc == M2K_OK) rc = m2k_finalize(ctx, dt, params, out);
   if (rc != M2K_OK) { m2k_devtree_free(ctx, dt); return rc; }
+  const double t2 = now_ms();
   // the result's arrays live in the device tree's pinned buffers: free the device memory now, hand the
   // rest to the result
   cudaStreamSynchronize(ctx->c.stream);
   devtree_release(&dt->t);
   dt->t = DevTree();
   (*out)->owner = dt;
+  if (getenv("M2K_DEBUG_TIMING"))
+    fprintf(stderr, "[m2k] detect: upload %.2f ms (H2D %.2f), scan + finalize %.2f, release %.2f\n", t1 - t0, dt->ms_h2d, t2 - t1, now_ms() - t2);
   if (rc == M2K_OK) {
     (*out)->ms_total = (float)(now_ms() - t0);
     (*out)->n_kernel_launches = (uint32_t)(ctx->c.launches - l0);
