@@ -337,6 +337,12 @@ int m2k_phase_ms(m2k_ctx* ctx, float* out, int cap);
 uint64_t m2k_launch_count(const m2k_ctx* ctx);
 void* m2k_stream(m2k_ctx* ctx); /* cudaStream_t the library launches on */
 
+/* diagnostic, no counterpart in the reference: a library built with -DM2K_CHECKED=1 counts, instead of making it,
+ * every kernel access that falls outside the buffer it belongs to (scan loads outside the shard, record / list /
+ * stripe indices past their tables).  out[0..8) receives the counters and clears them; returns 1 for a checked
+ * build, 0 for the product build (whose counters stay zero), or a negative m2k_status. */
+int m2k_debug_violations(m2k_ctx* ctx, uint64_t* out);
+
 /* -- the byte scan without any GPU allocation (no counterpart in the reference) --
  * For hosts that cannot call cudaMalloc where they call this library: inside work they are
  * capturing or replaying, under a device-memory arena that is handed out once and then locked, or

@@ -262,6 +262,19 @@ extern "C" int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes,
   return M2K_OK;
 }
 
+// diagnostic: the counters of a checked build (kernels.cu M2K_CHECKED): out[0..8), cleared by the call.
+// Returns 1 when the library was built with the checks, 0 when not (the counters then stay zero).
+extern "C" int m2k_debug_violations(m2k_ctx* ctx, uint64_t* out) {
+  if (!ctx || !out) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  CU(cudaSetDevice(C->device));
+  CU(cudaDeviceSynchronize());
+  unsigned long long v[8];
+  if (int e = read_violations(v)) return fail(C, M2K_ERR_CUDA, "reading the check counters: %s", cudaGetErrorString((cudaError_t)e));
+  for (int i = 0; i < 8; i++) out[i] = v[i];
+  return checked_build();
+}
+
 extern "C" int m2k_ctx_trim(m2k_ctx* ctx) {
   if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
   Ctx* C = &ctx->c;

@@ -16,6 +16,27 @@ static_assert(df::kStripe == kDfStripe, "stripe size");
 
 #define FULL 0xFFFFFFFFu
 
+// A checked build (-DM2K_CHECKED=1, tools/scan_variants.py "checked") counts every access that falls outside
+// the buffer it belongs to instead of making it: our own bounds checks, run over the adversarial parity tests,
+// where a memory checker cannot be used.  Slots: 0 scan load outside the shard's bytes, 1 chunk record index,
+// 2 head list / candidate index, 3 stripe or tile index, 4 a Dockerfile stripe outside its file.
+#ifndef M2K_CHECKED
+#define M2K_CHECKED 0
+#endif
+__device__ unsigned long long g_violations[8];
+#if M2K_CHECKED
+#define M2K_CHECK(cond, slot) ((cond) ? true : (atomicAdd(&g_violations[slot], 1ull), false))
+#else
+#define M2K_CHECK(cond, slot) true
+#endif
+int read_violations(unsigned long long* out) {  // host: 0 or a cudaError_t; zeroes the counters
+  unsigned long long zero[8] = {};
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_violations, sizeof zero);
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_violations, zero, sizeof zero);
+  return (int)e;
+}
+int checked_build() { return M2K_CHECKED; }
+
 // ---------------------------------------------------------------------------------------------
 // small helpers
 // ---------------------------------------------------------------------------------------------
@@ -243,7 +264,12 @@ struct ScanArgs {
   ChunkRec* chunk_rec;
   uint32_t* ticket;  // work items are drawn from this counter (NULL: strided over the grid)
   uint32_t quota;    // ticket mode: a warp retires after this many chunks (0: never) -- see launch_scan_bytes
+  uint64_t shard_bytes;  // resident bytes (checked builds)
 };
+__device__ __forceinline__ bool in_shard(const ScanArgs& a, const void* p, size_t n) {
+  const uint64_t off = (uint64_t)((const uint8_t*)p - a.bytes);  // wraps to a huge value below the buffer
+  return off <= a.shard_bytes && n <= a.shard_bytes - off;
+}
 
 // where work item `item` (a 64 KiB chunk of one file) lies
 struct ChunkCtx {
@@ -360,12 +386,12 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
 #pragma unroll
       for (int r = 0; r < kScanRows; r++) {
         uint32_t u = u0 + r * 32 + lane;
-        v[r] = u < c.n_units ? ldg_stream(c.src + u) : make_uint4(0, 0, 0, 0);
+        v[r] = (u < c.n_units && M2K_CHECK(in_shard(a, c.src + u, 16), 0)) ? ldg_stream(c.src + u) : make_uint4(0, 0, 0, 0);
       }
       scan_batch(v, u0, lane, c, acc);
     }
     const ChunkRec rec = chunk_record(c, acc, lane);
-    if (lane == 0) a.chunk_rec[item] = rec;
+    if (lane == 0 && M2K_CHECK(item < a.n_chunks, 1)) a.chunk_rec[item] = rec;
     if (a.ticket) {  // chunks differ in size (the last chunk of a file): handed out as warps come free
       if (a.quota && ++taken >= a.quota) break;
       uint32_t nx = 0;
@@ -466,7 +492,7 @@ __global__ void __launch_bounds__(kBulkWarps * 32, 1) k_scan_bytes_bulk(ScanArgs
 void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket) {
   if (!t->n_chunks) return;
   ScanArgs a{t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off, t->file_len, t->file_begin,
-             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket, 0};
+             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket, 0, t->shard_bytes};
 #if defined(M2K_SCAN_BULK) && M2K_SCAN_BULK
   static bool attr_set = false;
   if (!attr_set) { cudaFuncSetAttribute(k_scan_bytes_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBulkSmem); attr_set = true; }
@@ -550,6 +576,7 @@ struct FileArgs {
   uint8_t* stripe_state; // per 256-byte stripe of candidate body: the line state at its first line start
   uint32_t* tile_state;  // per tile of 256 stripes: (pass number << 3) | 4: end state known | map (2 bits) or end state (bit 0)
   uint32_t epoch;
+  uint32_t stripe_cap, tile_cap;  // sizes of the two tables (checked builds)
 };
 
 // fold records [k0, k1) (indices into the file's records present in this shard, the first of which
@@ -611,13 +638,13 @@ __device__ __forceinline__ void finish_file(const FileArgs& a, uint32_t i, uint3
     ps.bytes = tot.bytes; ps.lead = tot.lead; ps.trail = tot.trail;
     a.pieces[i == 0 ? 0 : 1] = ps;
     a.file_flags[f] = 0;
-    if (!cut_front && !not_df) a.head_list[atomicAdd(&a.ctr->n_heads, 1u)] = i;  // this part starts the file: its head can be looked at
+    if (!cut_front && !not_df) { const uint32_t h = atomicAdd(&a.ctr->n_heads, 1u); if (M2K_CHECK(h < a.n_shard_files, 2)) a.head_list[h] = i; }  // this part starts the file: its head can be looked at
     return;
   }
   const uint32_t longf = acc_long(tot.bytes, tot.lead, tot.trail, tot.longf);
   a.file_flags[f] = (uint8_t)((has_main ? M2K_FILE_HAS_MAIN : 0u) | (longf ? M2K_FILE_LONG_LINE : 0u));
   if (has_main) note_main_file(f, a.file_entry, a.entry_dir, a.entry_name_off, a.names, a.dir_content, a.dir_main);
-  if (!not_df && !longf && len) a.head_list[atomicAdd(&a.ctr->n_heads, 1u)] = i;  // a long line fails the parse anyway
+  if (!not_df && !longf && len) { const uint32_t h = atomicAdd(&a.ctr->n_heads, 1u); if (M2K_CHECK(h < a.n_shard_files, 2)) a.head_list[h] = i; }  // a long line fails the parse anyway
 }
 
 __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
@@ -729,6 +756,7 @@ __global__ void __launch_bounds__(128) k_df_head(FileArgs a) {
     } else {
       const unsigned long long old = atomicAdd(&a.ctr->cand_stripes, (1ull << 32) | n_stripes);
       const uint32_t c = (uint32_t)(old >> 32);
+      if (!M2K_CHECK(c < a.n_shard_files && (uint32_t)old + n_stripes <= a.stripe_cap, 2)) continue;
       a.cand_file[c] = f; a.cand_body[c] = body; a.cand_esc[c] = (uint8_t)esc;
       a.cand_stripe0[c] = (uint32_t)old; a.cand_err[c] = 0; a.cand_done[c] = 0;
     }
@@ -840,7 +868,7 @@ __global__ void __launch_bounds__(kDfTileStripes) k_df_states(FileArgs a) {
     }
     __syncthreads();
     // this stripe's own start state: from the start of its body when that lies in the tile, else from the tile's
-    if (live) a.stripe_state[s] = (el & 4u) ? (uint8_t)0 : (uint8_t)df::map_apply(exc & 3u, (exc & 4u) ? 0u : s_in);
+    if (live && M2K_CHECK(s < a.stripe_cap && t < a.tile_cap, 3)) a.stripe_state[s] = (el & 4u) ? (uint8_t)0 : (uint8_t)df::map_apply(exc & 3u, (exc & 4u) ? 0u : s_in);
   }
 }
 
@@ -855,6 +883,7 @@ __global__ void __launch_bounds__(128) k_df_validate(FileArgs a) {
     if (live) {
       const StripeRef r = df_stripe(a, n_cand, s);
       c = r.c;
+      (void)M2K_CHECK(r.lo >= r.body && r.lo < r.hi && r.hi <= a.file_len[a.cand_file[c]], 4);
       if (!df::stripe_validate(df_file(a, c), r.body, r.lo, r.hi, a.stripe_state[s])) atomicExch(&a.cand_err[c], 1u);
     }
     // count finished stripes per candidate, one atomic per (warp, candidate); whoever completes a
@@ -882,7 +911,7 @@ static FileArgs file_args(DevTree* t, const ChunkRec* chunk_rec) {
   return FileArgs{t->file_end - t->file_begin, t->file_begin, t->first_skip, t->last_end, t->chunk_first, chunk_rec,
                   t->file_off, t->file_len, t->bytes, t->shard_byte0, t->file_entry, t->entry_dir, t->entry_name_off, t->names,
                   t->file_flags, remote ? t->link.dir_content : t->dir_content, remote ? t->link.dir_main : t->dir_main, t->pieces, t->df_counters, t->head_list, t->cand_file, t->cand_body,
-                  t->cand_esc, t->cand_stripe0, t->cand_err, t->cand_done, t->stripe_state, t->tile_state, t->epoch};
+                  t->cand_esc, t->cand_stripe0, t->cand_err, t->cand_done, t->stripe_state, t->tile_state, t->epoch, t->stripe_cap, t->tile_cap};
 }
 
 // per-file combine, then isDockerFile: heads, stripe states, validation

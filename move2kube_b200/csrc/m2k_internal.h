@@ -218,6 +218,8 @@ void launch_signal(Ctx* c, uint32_t* flag, uint32_t value, cudaStream_t st);
 void launch_wait_ge(Ctx* c, const uint32_t* flags, uint32_t n_flags, uint32_t value, uint32_t* abort, cudaStream_t st);
 void launch_contribute(Ctx* c, DevTree* t, cudaStream_t st);
 int preload_kernels();  // 0 or a cudaError_t
+int read_violations(unsigned long long* out);  // checked builds: the bounds-check counters (and clears them)
+int checked_build();
 void launch_fill_u32(Ctx* c, uint32_t* p, uint32_t v, size_t n);
 
 void set_global_error(const char* msg);  // api.cu: what m2k_global_error() returns on this thread

@@ -144,6 +144,7 @@ extern "C" int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d
   t.file_len = const_cast<uint64_t*>(d_file_len);
   t.bytes = const_cast<uint8_t*>(d_bytes);
   t.shard_byte0 = 0;
+  t.shard_bytes = ~0ull >> 1;  // the caller's buffer: its size is not known here (checked builds compare against this)
   e = cudaMemsetAsync(g_ticket_ptr[device], 0, sizeof(uint32_t), c.stream);  // a memset node, not an allocation
   if (e != cudaSuccess) return noalloc_fail(M2K_ERR_CUDA, "m2k_scan_flags_noalloc: clearing the chunk counter: %s", cudaGetErrorString(e));
   launch_scan_bytes(&c, &t, g_records_ptr[device], g_ticket_ptr[device]);

@@ -31,7 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
-    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi", "m2k_option_json", "m2k_ctx_trim",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi", "m2k_option_json", "m2k_ctx_trim", "m2k_debug_violations",
 ]
 
 
@@ -104,6 +104,7 @@ def load():
     L.m2k_pack_detect.argtypes = [vp, C.c_char_p, PP, C.POINTER(TP), C.POINTER(RP)]
     L.m2k_reupload.argtypes = [vp, vp, TP]
     L.m2k_ctx_trim.argtypes = [vp]
+    L.m2k_debug_violations.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.m2k_option_json.argtypes = [TP, RP, C.c_uint32, C.c_uint32, C.c_char_p, C.c_size_t]
     L.m2k_detect_multi.argtypes = [C.POINTER(vp), C.c_uint32, TP, PP, C.POINTER(RP)]
     L.m2k_exchange_open.argtypes = [vp, vp, C.c_uint32, vp]
@@ -155,6 +156,14 @@ class Context:
 
     def __exit__(self, *a):
         self.close()
+
+    def debug_violations(self):
+        """(checked build?, [8 counters]) -- see m2k_debug_violations."""
+        out = (C.c_uint64 * 8)()
+        rc = self.L.m2k_debug_violations(self.h, out)
+        if rc < 0:
+            _check(rc, self.h)
+        return bool(rc), list(out)
 
     def trim(self):
         """Give the device buffers the context keeps between calls back to the driver."""

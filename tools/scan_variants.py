@@ -22,6 +22,7 @@ VARIANTS = {
     "quota32": ["M2K_SCAN_QUOTA_WAVES=32"],
     "quota64": ["M2K_SCAN_QUOTA_WAVES=64"],
     "mb3": ["M2K_SCAN_MINBLOCKS=3"],
+    "checked": ["M2K_CHECKED=1"],  # own bounds checks (m2k_debug_violations), run under the parity tests
     "strided": ["M2K_SCAN_TICKET=0"],  # round 1's distribution: item += number of warps, 32 waves of blocks
     "bulk_w16_s3": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=3"],
     "bulk_w24_s2": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=24", "M2K_BULK_STAGES=2"],
