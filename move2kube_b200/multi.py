@@ -20,17 +20,21 @@ from itertools import accumulate
 from . import _abi, lib
 
 
-def shard_ranges(file_len, world):
-    """Contiguous [begin, end) file-id ranges, one per rank, covering all files, near-equal in bytes.
-    `file_len` is any sequence of file sizes."""
+def shard_ranges(file_len, world, weights=None):
+    """Contiguous [begin, end) file-id ranges, one per rank, covering all files, near-equal in bytes --
+    or, with `weights`, in proportion to them (e.g. the host-to-device rate each rank was measured at: on
+    a box whose GPUs do not all reach the host equally fast, equal shards make everybody wait for the
+    slowest link).  `file_len` is any sequence of file sizes."""
     n = len(file_len)
     if world <= 1:
         return [(0, n)]
     prefix = list(accumulate(file_len))
     total = prefix[-1] if prefix else 0
+    w = [1.0] * world if not weights else [max(float(x), 1e-9) for x in weights]
+    wsum = sum(w)
     cuts = [0]
     for r in range(1, world):
-        target = total * r / world
+        target = total * sum(w[:r]) / wsum
         c = bisect_left(prefix, target) + 1 if total else n * r // world
         cuts.append(min(max(c, cuts[-1]), n))
     cuts.append(n)
