@@ -96,3 +96,14 @@ KATS = [
     ("continuation_inside_env", b"FROM a\nEN\\\nV A\n", False),
     ("backslash_not_last_in_word", b"FR\\OM a\n", False),
 ]
+
+
+def reference_corpus():
+    """(path, bytes, is_dockerfile) for the files of the reference tree recorded by tests/golden/make_dockerfile_corpus.py:
+    its 16 real Dockerfiles (true) and 31 other files (false), expectations by inspection."""
+    import base64
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "_reference_dockerfile_corpus.json")) as f:
+        j = json.load(f)
+    return [(x["path"], base64.b64decode(x["bytes_b64"]), x["is_dockerfile"]) for x in j["files"]]

@@ -143,6 +143,30 @@ def test_dockerfile_translator_finds_dockerfiles(tmp_path, assets):
     assert [os.path.relpath(f, str(d)) for f in files] == ["build.Dockerfile", "svc/Dockerfile", "zz.Dockerfile"]
 
 
+def test_translate_time_detect_is_answered_from_the_pass(tmp_path, assets):
+    """GetContainer re-runs the option's detect script to read its JSON (dockerfilecontainerizer.go:105-129,
+    s2icontainerizer.go:97-115): the mirror's detect() answers from the detection pass instead, with the
+    bytes the reference's script prints (internal/assets/dockerfiles/python/m2kdfdetect.sh:21-24)."""
+    import json
+    app = tmp_path / "svc"
+    (app / "pkg").mkdir(parents=True)
+    (app / "requirements.txt").write_text("flask\n")
+    (app / "pkg" / "run.py").write_text("import x\nif __name__ == '__main__':\n    x.go()\n")
+    (app / "lib.war").write_text("not really a war")
+    cs = containerizer.Containerizers()
+    cs.InitContainerizers(str(app))
+    df, s2i = cs.containerizers[0], cs.containerizers[1]
+    out, err = df.detect(os.path.join(assets, "dockerfiles", "python"), str(app))
+    assert err is None and out == '{"main_script_rel_path": "pkg/run.py", "app_name": "app", "port": 8080}'
+    out, err = s2i.detect(os.path.join(assets, "s2i", "python"), str(app))
+    assert err is None and json.loads(out)["app_file"] == "pkg/run.py" and json.loads(out)["builder"].endswith("python-36-rhel7:latest")
+    out, err = df.detect(os.path.join(assets, "dockerfiles", "java-war-liberty"), str(app))
+    assert err is None and out == '{"port":9080, "war_path":"lib.war"}'
+    out, err = df.detect(os.path.join(assets, "dockerfiles", "nodejs"), str(app))
+    assert err is not None and out == ""          # the script would print nothing and exit 1
+    cs.close()
+
+
 def test_a_root_that_is_not_a_directory(tmp_path, assets):
     """filepath.Walk Lstats its root: a symlink to a directory, or a file, is visited alone.  Any2Kube
     returns no services (any2kube.go:63-65); getDockerfileServices asks isDockerFile about the root

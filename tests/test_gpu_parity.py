@@ -7,7 +7,7 @@ import pytest
 
 import golden_check as gc
 import treespec
-from dockerfile_kats import KATS
+from dockerfile_kats import KATS, reference_corpus
 from move2kube_b200 import _abi, lib
 
 pytestmark = pytest.mark.gpu
@@ -70,6 +70,25 @@ def test_nonexistent_root_is_an_io_error(ctx, tmp_path):
     with pytest.raises(lib.M2KError) as ei:
         ctx.pack_tree(os.fsencode(str(tmp_path / "missing")))
     assert ei.value.code == _abi.ERR_IO
+
+
+def test_dockerfiles_that_ship_in_the_reference_tree(ctx, oracle, tmp_path):
+    """The reference tree's own 16 Dockerfiles and 31 of its other files, laid out as in the reference, through
+    the GPU path: flags equal the oracle's and the expectation made by inspection (make_dockerfile_corpus.py)."""
+    root = tmp_path / "ref"
+    corpus = reference_corpus()
+    for path, data, want in corpus:
+        (root / path).parent.mkdir(parents=True, exist_ok=True)
+        (root / path).write_bytes(data)
+    tree = ctx.pack_tree(os.fsencode(str(root)))
+    res = ctx.detect(tree)
+    view = gc.TreeView(tree)
+    got = {os.fsdecode(view.file_rel[f]): res.contents.file_flags[f] for f in range(view.n_files)}
+    for path, data, want in corpus:
+        assert got[path] == oracle.file_flags(data), path
+        assert bool(got[path] & _abi.FILE_DOCKERFILE) == want, path
+    ctx.result_free(res)
+    ctx.tree_free(tree)
 
 
 def test_dockerfile_known_answers(ctx, oracle, tmp_path):

@@ -2,7 +2,7 @@
 import pytest
 
 import gopath
-from dockerfile_kats import KATS
+from dockerfile_kats import KATS, reference_corpus
 from move2kube_b200 import _abi
 
 CLEAN = [(b"", b"."), (b"/", b"/"), (b"a//b", b"a/b"), (b"a/./b/", b"a/b"), (b"a/b/..", b"a"), (b"../a", b"../a"),
@@ -50,3 +50,14 @@ def test_dockerfile_kat(oracle, name, data, want):
     flags = oracle.file_flags(data)
     assert bool(flags & _abi.FILE_DOCKERFILE) == want, "flags=%#x" % flags
     assert bool(flags & _abi.FILE_HAS_MAIN) == (b"__main__" in data)
+
+
+CORPUS = reference_corpus()
+
+
+@pytest.mark.parametrize("path,data,want", CORPUS, ids=[c[0] for c in CORPUS])
+def test_dockerfiles_that_ship_in_the_reference_tree(oracle, path, data, want):
+    """Every real Dockerfile of the reference tree must be accepted, a spread of its other files rejected
+    (expectations by inspection: tests/golden/make_dockerfile_corpus.py)."""
+    flags = oracle.file_flags(data)
+    assert bool(flags & _abi.FILE_DOCKERFILE) == want, "%s flags=%#x" % (path, flags)
