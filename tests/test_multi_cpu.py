@@ -95,3 +95,27 @@ def test_two_rank_gather_on_gloo(tmp_path, oracle):
     for r, p in enumerate(procs):
         assert p.returncode == 0, outs[r][-2000:]
         assert "rank %d ok" % r in outs[r]
+
+
+def test_weighted_shard_ranges_follow_the_weights():
+    """bench.py's e2e leg deals files out in proportion to each rank's measured host-to-device rate."""
+    lens = [1000] * 10000
+    r = multi.shard_ranges(lens, 4, [23, 23, 34.5, 34.5])
+    sizes = [b - a for a, b in r]
+    assert r[0][0] == 0 and r[-1][1] == len(lens) and all(r[i][1] == r[i + 1][0] for i in range(3))
+    assert sizes[0] == sizes[1] and sizes[2] == sizes[3] and abs(sizes[2] / sizes[0] - 1.5) < 0.01
+    assert multi.shard_ranges(lens, 4, [1, 1, 1, 1]) == multi.shard_ranges(lens, 4)
+    assert multi.shard_ranges(lens, 2, [0, 1])[0] == (0, 1) or multi.shard_ranges(lens, 2, [0, 1])[0][1] <= 1
+
+
+def test_bench_snapshot_comparison_counts_differences():
+    import numpy as np
+    sys.path.insert(0, REPO)
+    import bench
+    a = {k: np.arange(10, dtype=np.uint32) for k in bench.RESULT_ARRAYS}
+    b = {k: v.copy() for k, v in a.items()}
+    assert bench.compare_snapshots(a, b) == {}
+    b["dir_opts"][3] = 99
+    b["service_dirs"] = b["service_dirs"][:8]
+    d = bench.compare_snapshots(a, b)
+    assert d == {"dir_opts": 1, "service_dirs": 2}
