@@ -167,6 +167,9 @@ void launch_name_features(Ctx* c, DevTree* t) {
 #ifndef M2K_SCAN_WAVES
 #define M2K_SCAN_WAVES 32
 #endif
+#ifndef M2K_SCAN_PREFETCH
+#define M2K_SCAN_PREFETCH 0
+#endif
 #ifndef M2K_SCAN_QUOTA_WAVES
 #define M2K_SCAN_QUOTA_WAVES 0  // ticket mode: 0 = one wave of blocks that never retire; W = W waves, warps retire after a quota
 #endif
@@ -388,6 +391,17 @@ __global__ void __launch_bounds__(kScanThreads, M2K_SCAN_MINBLOCKS) k_scan_bytes
         uint32_t u = u0 + r * 32 + lane;
         v[r] = (u < c.n_units && M2K_CHECK(in_shard(a, c.src + u, 16), 0)) ? ldg_stream(c.src + u) : make_uint4(0, 0, 0, 0);
       }
+#if M2K_SCAN_PREFETCH
+      // the next batch on its way into L2 while this one is looked at (costs no registers): one request per
+      // 128-byte line, from the lane that holds its first 16 bytes
+      if ((lane & 7u) == 0) {
+#pragma unroll
+        for (int r = 0; r < kScanRows; r++) {
+          uint32_t u = u0 + (kScanRows + r) * 32 + lane;
+          if (u < c.n_units) asm volatile("prefetch.global.L2 [%0];" ::"l"(c.src + u));
+        }
+      }
+#endif
       scan_batch(v, u0, lane, c, acc);
     }
     const ChunkRec rec = chunk_record(c, acc, lane);

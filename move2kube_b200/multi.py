@@ -14,6 +14,7 @@ two 32-byte piece summaries per rank, gathered with one all_gather (NCCL over NV
 no bitwise-OR reduction, so gather + merge kernels), and the per-file flag bytes (all_reduce).  The
 rank that consumes the result merges and runs the cheap directory-level phases.
 """
+import os
 from bisect import bisect_left
 from itertools import accumulate
 
@@ -144,6 +145,8 @@ class PeerExchange:
         self.error = None
         if rank != 0:
             try:
+                if os.environ.get("M2K_TEST_NO_IPC"):  # testing the fallback: behave as if the mapping had been refused
+                    raise lib.M2KError(_abi.ERR_CUDA, "M2K_TEST_NO_IPC is set")
                 ctx.exchange_attach(dt, rank, bytes(buf.cpu().numpy().tobytes()))
             except lib.M2KError as e:  # e.g. a sandbox that forbids CUDA IPC between processes
                 self.error = str(e)

@@ -22,6 +22,7 @@ VARIANTS = {
     "quota32": ["M2K_SCAN_QUOTA_WAVES=32"],
     "quota64": ["M2K_SCAN_QUOTA_WAVES=64"],
     "mb3": ["M2K_SCAN_MINBLOCKS=3"],
+    "prefetch": ["M2K_SCAN_PREFETCH=1"],  # L2 prefetch of the next batch while the current one is processed: C 14.10 vs 13.75 ms, B 0.159 vs 0.163, 32-512 MB trees unchanged
     "checked": ["M2K_CHECKED=1"],  # own bounds checks (m2k_debug_violations), run under the parity tests
     "strided": ["M2K_SCAN_TICKET=0"],  # round 1's distribution: item += number of warps, 32 waves of blocks
     "bulk_w16_s3": ["M2K_SCAN_BULK=1", "M2K_BULK_WARPS=16", "M2K_BULK_STAGES=3"],
