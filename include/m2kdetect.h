@@ -296,6 +296,10 @@ int m2k_exchange_attach_local(m2k_ctx* ctx, m2k_devtree* dt, uint32_t rank, m2k_
 int m2k_exchange_collect(m2k_ctx* ctx, m2k_devtree* root_dt);
 /* an attached rank: block (without spinning) until its part of the current pass has been delivered */
 int m2k_exchange_wait(m2k_ctx* ctx, m2k_devtree* dt);
+/* ... or only until the pass BEFORE the last m2k_scan has been delivered: a rank that serves pass after pass may
+ * queue the next one at once (its writes into the root's memory wait on the device for the root's flag), so its
+ * next byte scan starts the moment its GPU is free */
+int m2k_exchange_wait_previous(m2k_ctx* ctx, m2k_devtree* dt);
 /* which file holds global chunk `chunk`, and which of its chunks that is (a cut at chunk_in_file != 0 splits the file) */
 int m2k_chunk_locate(const m2k_tree* tree, uint64_t chunk, uint32_t* file, uint32_t* chunk_in_file);
 /* one file's flags on the device, read back (synchronises); and, before m2k_finalize, the flags a

@@ -244,6 +244,7 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
   for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
   if (C->ev_idle) cudaEventDestroy(C->ev_idle);
+  for (cudaEvent_t ev : C->ev_pass) if (ev) cudaEventDestroy(ev);
   if (C->side_stream) cudaStreamDestroy(C->side_stream);
   for (int k = 0; k < 2; k++) { if (C->stage[k]) cudaFreeHost(C->stage[k]); if (C->stage_ev[k]) cudaEventDestroy(C->stage_ev[k]); }
   if (C->stream) cudaStreamDestroy(C->stream);
@@ -646,12 +647,14 @@ static constexpr uint64_t kChunkFixedCost = 4096;
 static inline uint64_t file_cost(const m2k_tree* tree, uint32_t f) { return tree->file_len[f] + kChunkFixedCost * file_chunks(tree, f); }
 
 extern "C" uint64_t m2k_root_extra_bytes(const m2k_tree* tree) {
-  // what the rank that assembles the result does on its main stream before the exchange, besides
-  // scanning its shard -- the name kernel, queueing and the blocks its side-stream kernels take from the
-  // scan -- expressed as bytes of scanning.  From the measured gap between rank 0 and the other ranks
-  // reaching the exchange on B200 (2 and 8 GPUs): about 0.06 ms per million entries, at 7 TB/s.
+  // What the rank that assembles the result does besides scanning its shard, expressed as bytes of scanning
+  // (7 TB/s).  The other ranks stay one pass ahead of their hosts (m2k_exchange_wait_previous), so a pass takes
+  // max(root's scan + its tail, a rank's scan + its per-file kernels); the root's tail is the longer one by its
+  // stitching, k_content_up, result copies and host work, and its scan starts behind the name kernel and shares
+  // the SMs with its directory-level kernels.  Swept on 2 x B200 (0.1 / 0.25 / 0.4 ms: config E 7.42 / 7.46 /
+  // 7.56 ms, D 4.12 / 4.16 / 4.28, 2 x C 14.50 / 14.41 / 14.41): 0.1 ms plus 0.06 ms per million entries.
   if (!tree) return 0;
-  return (uint64_t)(7.0e9 * (0.06e-6 * (double)tree->n_entries));
+  return (uint64_t)(7.0e12 /* bytes per second */ * (0.10e-3 + 0.06e-9 * (double)tree->n_entries) /* seconds */);
 }
 
 extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t split_min_bytes, uint64_t root_extra_bytes,
@@ -758,6 +761,9 @@ extern "C" int m2k_scan(m2k_ctx* ctx, m2k_devtree* dt, const m2k_detect_params* 
   if (remote) {
     launch_contribute(C, t, s);
     launch_signal(C, &L.mailbox->done[L.rank], L.pass, s);
+    cudaEvent_t& ev = C->ev_pass[L.pass & 1u];
+    if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventBlockingSync | cudaEventDisableTiming));
+    CU(cudaEventRecord(ev, s));
   }
   CU(cudaGetLastError());
   // no synchronisation here: m2k_finalize overlaps its host work with these kernels
@@ -1017,6 +1023,22 @@ extern "C" int m2k_exchange_wait(m2k_ctx* ctx, m2k_devtree* dt) {
   CU(cudaEventRecord(C->ev_idle, C->stream));
   CU(cudaEventSynchronize(C->ev_idle));
   if (int rc = collect_scan_timings(C, dt)) return rc;
+  return M2K_OK;
+}
+
+// An attached rank may queue its next pass before the previous one has been delivered: everything it does is
+// ordered on its own stream, and what it writes into the root's memory waits (on the device) for the root's
+// "cleared for this pass" flag.  Its host then only has to stay one pass behind: this waits for the pass BEFORE
+// the last m2k_scan, so the rank's next byte scan starts the moment its GPU is free instead of after a host
+// wake-up (measured: 0.2-0.4 ms per pass at 2 and 8 GPUs).
+extern "C" int m2k_exchange_wait_previous(m2k_ctx* ctx, m2k_devtree* dt) {
+  if (!ctx || !dt) return fail(nullptr, M2K_ERR_ARG, "NULL argument");
+  Ctx* C = &ctx->c;
+  const PeerLink& L = dt->t.link;
+  if (!L.attached || L.is_root || L.pass < 2) return M2K_OK;
+  CU(cudaSetDevice(C->device));
+  cudaEvent_t ev = C->ev_pass[(L.pass - 1) & 1u];
+  if (ev) CU(cudaEventSynchronize(ev));
   return M2K_OK;
 }
 

@@ -177,6 +177,7 @@ struct Ctx {
   cudaEvent_t ev_side0 = nullptr, ev_side1 = nullptr;  // timing on: the span of those kernels
   cudaEvent_t ev_early = nullptr;                      // ... and their results are on the host
   cudaEvent_t ev_idle = nullptr;                       // blocking-sync event for ranks that only wait (m2k_exchange_wait)
+  cudaEvent_t ev_pass[2] = {nullptr, nullptr};         // blocking-sync: an attached rank's pass p has been delivered (p & 1)
   // two pinned blocks through which bytes held in pageable host memory are streamed to the device
   void* stage[2] = {nullptr, nullptr};
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};

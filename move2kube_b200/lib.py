@@ -31,7 +31,7 @@ EXPORTS = [
     "m2k_chunk_count", "m2k_plan_shards", "m2k_upload_chunks", "m2k_pieces", "m2k_merge_pieces",
     "m2k_chunk_locate", "m2k_file_flag", "m2k_settle_file", "m2k_devtree_content_bytes", "m2k_root_extra_bytes",
     "m2k_export_async", "m2k_import_async", "m2k_pack_detect", "m2k_is_dockerfile",
-    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_reupload", "m2k_detect_multi", "m2k_option_json", "m2k_ctx_trim", "m2k_debug_violations",
+    "m2k_exchange_open", "m2k_exchange_attach", "m2k_exchange_attach_local", "m2k_exchange_collect", "m2k_exchange_wait", "m2k_exchange_wait_previous", "m2k_reupload", "m2k_detect_multi", "m2k_option_json", "m2k_ctx_trim", "m2k_debug_violations",
 ]
 
 
@@ -112,6 +112,7 @@ def load():
     L.m2k_exchange_attach_local.argtypes = [vp, vp, C.c_uint32, vp, vp]
     L.m2k_exchange_collect.argtypes = [vp, vp]
     L.m2k_exchange_wait.argtypes = [vp, vp]
+    L.m2k_exchange_wait_previous.argtypes = [vp, vp]
     L.m2k_is_dockerfile.argtypes = [vp, C.c_char_p, C.c_uint64, _abi.u32p]
     L.m2k_host_prepare_probe.argtypes = [TP, PP, C.c_uint32, C.POINTER(C.c_double), _abi.u32p, _abi.u32p]
     for name in EXPORTS:
@@ -268,6 +269,9 @@ class Context:
 
     def exchange_wait(self, dt):
         _check(self.L.m2k_exchange_wait(self.h, dt), self.h)
+
+    def exchange_wait_previous(self, dt):
+        _check(self.L.m2k_exchange_wait_previous(self.h, dt), self.h)
 
     def shard_content_bytes(self, dt) -> int:
         return self.L.m2k_devtree_content_bytes(dt)

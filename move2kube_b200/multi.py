@@ -162,6 +162,8 @@ class PeerExchange:
         if self.rank == 0:
             ctx.exchange_collect(dt)
             return settle_undecided(ctx, tree, dt, split, fill_seed) if split else []
-        if wait:
+        if wait == "previous":   # stay one pass behind: the next scan can be queued at once
+            ctx.exchange_wait_previous(dt)
+        elif wait:
             ctx.exchange_wait(dt)
         return []
