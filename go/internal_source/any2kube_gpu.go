@@ -9,6 +9,8 @@ package source
 import (
 	"os"
 	"path/filepath"
+	"strconv"
+	"strings"
 
 	"github.com/konveyor/move2kube/internal/common"
 	"github.com/konveyor/move2kube/internal/containerizer"
@@ -43,7 +45,14 @@ func (t *Any2KubeGPUTranslator) GetServiceOptions(inputPath string, plan plantyp
 		// `!info.IsDir()` returns nil (any2kube.go:63-65)
 		return services, nil
 	}
-	res, err := m2kdetect.Detect(inputPath, preContainerizedSourcePaths, os.Getenv("M2K_SH") == "dash")
+	// M2K_DEVICES="0,1,2,3": use several GPUs of the box from this one process (m2k_detect_multi); default: device 0
+	var res *m2kdetect.Result
+	var err error
+	if devs := parseDevices(os.Getenv("M2K_DEVICES")); len(devs) > 1 {
+		res, err = m2kdetect.DetectMulti(inputPath, preContainerizedSourcePaths, os.Getenv("M2K_SH") == "dash", devs)
+	} else {
+		res, err = m2kdetect.Detect(inputPath, preContainerizedSourcePaths, os.Getenv("M2K_SH") == "dash")
+	}
 	if err != nil {
 		// no CPU fallback: a GPU failure is an error of this translator, never silently empty results
 		log.Errorf("GPU source detection failed for %q Error: %q", inputPath, err)
@@ -106,3 +115,14 @@ func (t *Any2KubeGPUTranslator) GetServiceOptions(inputPath string, plan plantyp
 
 var _ Translator = (*Any2KubeGPUTranslator)(nil)
 var _ = irtypes.IR{}
+
+// parseDevices reads a comma-separated list of CUDA device numbers.
+func parseDevices(v string) []int {
+	devs := []int{}
+	for _, f := range strings.Split(v, ",") {
+		if n, err := strconv.Atoi(strings.TrimSpace(f)); err == nil && n >= 0 {
+			devs = append(devs, n)
+		}
+	}
+	return devs
+}
