@@ -365,7 +365,7 @@ static void devtree_release(DevTree* t) {
     t->from_arena = 0;
   }
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
-                  t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->bytes,
+                  t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->chunk_file, t->bytes,
                   t->synth_class, t->synth_inject, t->chunk_rec, t->entry_feat, t->slab, t->early,
                   t->dir_descend, t->head_list, t->cand_file, t->cand_stripe0, t->cand_err, t->cand_done, t->cand_body,
                   t->cand_esc, t->stripe_state, t->tile_state, t->ign_blob, t->pieces};
@@ -501,7 +501,7 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   CU(dev_alloc(&t->entry_dir, ne)); CU(dev_alloc(&t->entry_name_off, (size_t)ne + 1)); CU(dev_alloc(&t->entry_child, ne));
   CU(dev_alloc(&t->entry_type, ne)); CU(dev_alloc(&t->names, (size_t)tree->n_name_bytes));
   CU(dev_alloc(&t->file_entry, nf)); CU(dev_alloc(&t->file_off, nf)); CU(dev_alloc(&t->file_len, nf));
-  CU(dev_alloc(&t->chunk_first, (size_t)ns + 1));
+  CU(dev_alloc(&t->chunk_first, (size_t)ns + 1)); CU(dev_alloc(&t->chunk_file, t->n_chunks));
   CU(arena_alloc(C, t, 0, (void**)&t->bytes, (size_t)t->shard_bytes));
   CU(dev_alloc(&t->chunk_rec, t->n_chunks)); CU(dev_alloc(&t->entry_feat, ne)); CU(dev_alloc(&t->pieces, 2));
   {
@@ -562,8 +562,11 @@ static int upload_impl(m2k_ctx* ctx, const m2k_tree* tree, uint32_t file_begin, 
   dt->h_results = (uint8_t*)pinned_take(C, 5 * align256(4ull * (nd ? nd : 1)) + 2 * align256(nd ? nd : 1) + nf + 256);
   if (!dt->h_entry_feat || !dt->h_special || !dt->h_results) return fail(C, M2K_ERR_NOMEM, "out of pinned host memory for the result buffers");
   t->special_cap = kSpecialCap;
+  std::vector<uint32_t> chunk_file(t->n_chunks ? t->n_chunks : 1);
+  for (uint32_t i = 0; i < ns; i++) std::fill(chunk_file.begin() + chunk_first[i], chunk_file.begin() + chunk_first[i + 1], i);
   CU(cudaMemcpyAsync(t->chunk_first, chunk_first.data(), 4ull * ((size_t)ns + 1), cudaMemcpyHostToDevice, C->stream));
-  CU(cudaStreamSynchronize(C->stream));  // chunk_first is a stack-owned host vector
+  CU(cudaMemcpyAsync(t->chunk_file, chunk_file.data(), 4ull * t->n_chunks, cudaMemcpyHostToDevice, C->stream));
+  CU(cudaStreamSynchronize(C->stream));  // chunk_first / chunk_file are stack-owned host vectors
   if (getenv("M2K_DEBUG_TIMING")) fprintf(stderr, "[m2k] upload: set-up (layout, allocations, pinned result buffers) %.2f ms\n", now_ms() - t_setup);
   if (int rc = copy_shard(C, dt, tree)) return rc;
   guard.keep = true;
@@ -662,6 +665,8 @@ extern "C" int m2k_plan_shards(const m2k_tree* tree, uint32_t n_ranks, uint64_t 
   if (!tree || !n_ranks || !chunk_cuts) return fail(nullptr, M2K_ERR_ARG, "m2k_plan_shards: bad argument");
   uint64_t total_cost = 0, total_chunks = 0;
   for (uint32_t f = 0; f < tree->n_files; f++) { total_cost += file_cost(tree, f); total_chunks += file_chunks(tree, f); }
+  // the discount is meant for shards that take milliseconds to scan: never more than half of an even share
+  root_extra_bytes = std::min<uint64_t>(root_extra_bytes, total_cost / n_ranks / 2);
   chunk_cuts[0] = 0;
   uint32_t f = 0;
   uint64_t at_cost = 0, at_chunk = 0;  // cost / chunks of the files before f

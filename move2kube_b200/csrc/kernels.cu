@@ -268,6 +268,7 @@ struct ScanArgs {
   uint32_t* ticket;  // work items are drawn from this counter (NULL: strided over the grid)
   uint32_t quota;    // ticket mode: a warp retires after this many chunks (0: never) -- see launch_scan_bytes
   uint64_t shard_bytes;  // resident bytes (checked builds)
+  const uint32_t* chunk_file;  // [n_chunks] shard-local index of the file each chunk belongs to (NULL: bisect chunk_first)
 };
 __device__ __forceinline__ bool in_shard(const ScanArgs& a, const void* p, size_t n) {
   const uint64_t off = (uint64_t)((const uint8_t*)p - a.bytes);  // wraps to a huge value below the buffer
@@ -282,9 +283,16 @@ struct ChunkCtx {
   const uint4* src;
 };
 __device__ __forceinline__ ChunkCtx locate_chunk(const ScanArgs& a, uint32_t item) {
-  // which file: last f with chunk_first[f] <= item (empty files share their successor's value)
-  uint32_t lo = 0, hi = a.n_shard_files;
-  while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (a.chunk_first[mid] <= item) lo = mid; else hi = mid; }
+  // which file: last f with chunk_first[f] <= item (empty files share their successor's value).  A table made
+  // at upload answers in one load; without it (the no-allocation entry point) twenty dependent loads bisect
+  // chunk_first -- for a tree of tiny files that search cost more than the bytes.
+  uint32_t lo = 0;
+  if (a.chunk_file) {
+    lo = a.chunk_file[item];
+  } else {
+    uint32_t hi = a.n_shard_files;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (a.chunk_first[mid] <= item) lo = mid; else hi = mid; }
+  }
   const uint32_t f = a.file_begin + lo;
   ChunkCtx c;
   c.flen = a.file_len[f];
@@ -506,7 +514,7 @@ __global__ void __launch_bounds__(kBulkWarps * 32, 1) k_scan_bytes_bulk(ScanArgs
 void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket) {
   if (!t->n_chunks) return;
   ScanArgs a{t->n_chunks, t->file_end - t->file_begin, t->chunk_first, t->file_off, t->file_len, t->file_begin,
-             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket, 0, t->shard_bytes};
+             t->bytes, t->shard_byte0, t->first_skip, chunk_rec, ticket, 0, t->shard_bytes, t->chunk_file};
 #if defined(M2K_SCAN_BULK) && M2K_SCAN_BULK
   static bool attr_set = false;
   if (!attr_set) { cudaFuncSetAttribute(k_scan_bytes_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBulkSmem); attr_set = true; }

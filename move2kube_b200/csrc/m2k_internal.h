@@ -113,6 +113,7 @@ struct DevTree {
   uint32_t* file_entry = nullptr;
   uint64_t *file_off = nullptr, *file_len = nullptr;  // [n_files] (all files; offsets are tree-global)
   uint32_t* chunk_first = nullptr;        // [shard files + 1] prefix of ceil(len / kChunkBytes) over the shard
+  uint32_t* chunk_file = nullptr;         // [n_chunks] its inverse: the shard-local file index of every chunk
   uint8_t* bytes = nullptr;               // shard bytes; byte 0 is tree offset shard_byte0
   struct Ctx* arena_ctx = nullptr;        // the context whose arena `bytes` / `stripe_state` came from (bit 0 / 1 of from_arena)
   uint32_t from_arena = 0;
