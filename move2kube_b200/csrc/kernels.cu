@@ -906,7 +906,10 @@ __global__ void __launch_bounds__(128) k_df_validate(FileArgs a) {
       const StripeRef r = df_stripe(a, n_cand, s);
       c = r.c;
       (void)M2K_CHECK(r.lo >= r.body && r.lo < r.hi && r.hi <= a.file_len[a.cand_file[c]], 4);
-      if (!df::stripe_validate(df_file(a, c), r.body, r.lo, r.hi, a.stripe_state[s])) atomicExch(&a.cand_err[c], 1u);
+      if (!df::stripe_validate(df_file(a, c), r.body, r.lo, r.hi, a.stripe_state[s])) {
+        atomicExch(&a.cand_err[c], 1u);
+        __threadfence();  // visible before this warp's leader counts the stripe as finished (the vote below orders the two)
+      }
     }
     // count finished stripes per candidate, one atomic per (warp, candidate); whoever completes a
     // candidate publishes its verdict
