@@ -61,3 +61,49 @@ def test_dockerfiles_that_ship_in_the_reference_tree(oracle, path, data, want):
     (expectations by inspection: tests/golden/make_dockerfile_corpus.py)."""
     flags = oracle.file_flags(data)
     assert bool(flags & _abi.FILE_DOCKERFILE) == want, "%s flags=%#x" % (path, flags)
+
+
+def test_fold_table_agrees_with_a_second_derivation(oracle):
+    """strings.EqualFold beyond ASCII rests on one generated table (tools/gen_casefold.py, from str.casefold()), which
+    the oracle and the product both compile in.  This derives the classes a SECOND way -- the closure of the Unicode
+    database's single-character upper / lower / title mappings, which is what Go's unicode.SimpleFold walks -- and
+    checks both compiled tables against it for every cased code point.  The only differences allowed are the ones
+    Go itself makes: dotless / dotted i (U+0131, U+0130) fold to themselves, and pairs that entered Unicode after
+    12.0 (Go 1.15's tables) are not folded."""
+    from move2kube_b200 import lib
+    parent = {}
+
+    def find(x):
+        while parent.get(x, x) != x:
+            parent[x] = parent.get(parent[x], parent[x])
+            x = parent[x]
+        return x
+
+    for cp in range(0x41, 0x110000):
+        if 0xD800 <= cp <= 0xDFFF:
+            continue
+        ch = chr(cp)
+        for m in (ch.upper(), ch.lower(), ch.title()):
+            if len(m) == 1 and ord(m) != cp:
+                ra, rb = find(cp), find(ord(m))
+                if ra != rb:
+                    parent[max(ra, rb)] = min(ra, rb)
+    groups = {}
+    for cp in set(parent) | set(parent.values()):
+        groups.setdefault(find(cp), set()).add(cp)
+    post_u12 = gopath._POST_U12
+    checked = 0
+    for g in groups.values():
+        members = sorted(g)
+        for a in members[1:]:
+            b = members[0]
+            sa, sb = chr(a).encode("utf-8"), chr(b).encode("utf-8")
+            want = not ({a, b} & {0x130, 0x131}) and not ({a, b} & post_u12)
+            assert oracle.equal_fold(sa, sb) == want, "oracle: U+%04X vs U+%04X" % (a, b)
+            assert lib.equal_fold(sa, sb) == want, "product: U+%04X vs U+%04X" % (a, b)
+            checked += 1
+    assert checked > 1300
+    # and nothing outside those classes is folded together: neighbours in code point order that the closure keeps apart
+    for a in range(0x80, 0x3000):
+        if find(a) != find(a + 1):
+            assert not lib.equal_fold(chr(a).encode("utf-8"), chr(a + 1).encode("utf-8")), "U+%04X / U+%04X" % (a, a + 1)
