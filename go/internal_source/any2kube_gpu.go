@@ -77,7 +77,7 @@ func (t *Any2KubeGPUTranslator) GetServiceOptions(inputPath string, plan plantyp
 		}
 	}
 	if !containerizers.NeedsHostOptions() {
-		// the walk ran on the device (k_walk_level): directories in state SERVICE, in walk order
+		// the walk ran on the device (k_walk_local + k_walk_reach): directories in state SERVICE, in walk order
 		for _, d := range res.ServiceDirs {
 			emit(d)
 		}

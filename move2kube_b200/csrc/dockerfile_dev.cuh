@@ -435,8 +435,8 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 // Whether a physical line starts a logical line depends on one bit of state carried from the line
 // before it: OUT (0) or inside a continuation (1).  Each line maps that state to the next, so the
 // state at any offset is a prefix composition of 2-bit maps: bit0 = next state from OUT, bit1 = next
-// state from IN.  Stripes of the body compute their composed map (k_df_maps), a per-file scan turns
-// the maps into the state at each stripe start (k_df_scan), and every stripe then checks the logical
+// state from IN.  Stripes of the body compute their composed map, a segmented scan with a look-back across
+// tiles turns the maps into the state at each stripe start (k_df_states), and every stripe then checks the logical
 // lines that start inside it (k_df_validate).
 #ifndef M2K_DF_STRIPE
 #define M2K_DF_STRIPE 128

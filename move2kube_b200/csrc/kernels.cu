@@ -595,7 +595,7 @@ struct FileArgs {
   DfCounters* ctr;
   uint32_t* head_list;   // shard-local indices of the files whose head must be parsed
   uint32_t* cand_file; uint64_t* cand_body; uint8_t* cand_esc; uint32_t* cand_stripe0; uint32_t* cand_err; uint32_t* cand_done;
-  uint8_t* stripe_state; // per 256-byte stripe of candidate body: the line state at its first line start
+  uint8_t* stripe_state; // per stripe (kDfStripe bytes) of candidate body: the line state at its first line start
   uint32_t* tile_state;  // per tile of 256 stripes: (pass number << 3) | 4: end state known | map (2 bits) or end state (bit 0)
   uint32_t epoch;
   uint32_t stripe_cap, tile_cap;  // sizes of the two tables (checked builds)
@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
 // their sizes from device memory, so the host never waits for a count):
 //   k_df_head     one thread per listed file: directives, comments, ARGs, first instruction.
 //                 FROM-first files become candidates; a candidate's number and the number of its
-//                 first 256-byte body stripe come from ONE 64-bit counter (high / low half), so the
+//                 first body stripe (kDfStripe = 128 bytes) come from ONE 64-bit counter (high / low half), so the
 //                 stripe offsets grow with the candidate number and a stripe finds its candidate
 //                 by bisection -- no prefix-sum launch.
 //   k_df_states   one thread per stripe, in tiles of 256 consecutive stripes (whatever candidates

@@ -123,7 +123,7 @@ struct DevTree {
   // work buffers
   ChunkRec* chunk_rec = nullptr;          // [n_chunks] scratch
   // isDockerFile scratch: the files whose head must be parsed and the FROM-first candidates among
-  // them (worst case: every file), one byte per 256-byte stripe of candidate body (worst case: every
+  // them (worst case: every file), one byte per stripe (kDfStripe bytes) of candidate body (worst case: every
   // byte of the shard), one word per tile of 256 stripes (tagged with `epoch`, so never cleared)
   DfCounters* df_counters = nullptr;      // in the slab's zero region
   uint32_t *head_list = nullptr, *cand_file = nullptr, *cand_stripe0 = nullptr, *cand_err = nullptr, *cand_done = nullptr;

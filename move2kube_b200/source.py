@@ -67,7 +67,7 @@ class Any2KubeTranslator:
             containerizers.InitContainerizers(inputPath, det)
             builtin_only = not containerizers.has_user_options() and self._assets_complete(containerizers)
             if builtin_only:
-                # the walk's decisions were made on the device (k_walk_level): emit in walk order
+                # the walk's decisions were made on the device (k_walk_local + k_walk_reach): emit in walk order
                 for d in det.service_dirs:
                     self._emit(services, containerizers, plan, det, d)
             else:
