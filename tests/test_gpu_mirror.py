@@ -197,7 +197,7 @@ def test_a_root_that_is_not_a_directory(tmp_path, assets):
 
 @pytest.mark.parametrize("key", ["planfornodejsapp", "servicesfornodejsapp", "servicesfornodejsappwithm2kignorecase1",
                                  "servicesforjavamavenappwithm2kignorecase2"])
-def test_against_the_reference_golden_plans(tmp_path, assets, monkeypatch, key):
+def test_against_the_reference_golden_plans(tmp_path, tmp_path_factory, assets, monkeypatch, key):
     """The reference's OWN golden YAML files for this path (planner_test.go:99-128, any2kube_test.go:97-286),
     field by field in the plan's wire format.  They were recorded with Docker available, so the CNB
     provider hook stands in for the builders' detector; the three any2kube goldens were recorded without the
@@ -205,7 +205,9 @@ def test_against_the_reference_golden_plans(tmp_path, assets, monkeypatch, key):
     ref = gc.reference_plans()[key]
     spec = GOLDENS[ref["tree"]]
     # the service is named after the directory: samples/nodejs in the reference
-    root = treespec.materialize(spec, str(tmp_path / ("nodejs" if ref["tree"] == "samples_nodejs" else ref["tree"])))
+    # (the sources live outside the directory that holds the assets: common.TempPath never contains the input tree)
+    src_base = tmp_path_factory.mktemp("sources")
+    root = treespec.materialize(spec, str(src_base / ("nodejs" if ref["tree"] == "samples_nodejs" else ref["tree"])))
     if key != "planfornodejsapp":
         monkeypatch.setattr(containerizer, "AssetsPath", str(tmp_path / "no-assets"))
     # stand-in for the builder images' detector: what the goldens pin is that both builders accept a
@@ -219,4 +221,16 @@ def test_against_the_reference_golden_plans(tmp_path, assets, monkeypatch, key):
     for s in services:
         got.setdefault(s.ServiceName, []).append(plantypes.service_to_plan_dict(s, root, containerizer.AssetsPath))
     assert got == ref["services"]
+    if key == "planfornodejsapp":
+        # and as a FILE: the plan these services make, written by planio.WritePlan's encoder from the package
+        # directory the reference's test runs in, is the reference's golden file byte for byte
+        from move2kube_b200 import planio
+        p = plantypes.NewPlan()
+        p.Name = "nodejs-app"
+        p.Spec.Inputs.RootDir = root
+        p.AddServicesToPlan(services)
+        cwd = os.path.join(os.path.dirname(os.path.dirname(root)), "internal", "move2kube")  # rootDir: ../../samples/nodejs
+        text = planio.dumps(p, cwd=cwd)
+        want = ref["text"].replace("rootDir: ../../samples/nodejs", "rootDir: " + os.path.relpath(root, cwd))
+        assert text == want
     containerizer.CNBContainerizer._cache.clear()
