@@ -364,7 +364,9 @@ int m2k_debug_violations(m2k_ctx* ctx, uint64_t* out);
  * current device is the same after the call as before it.  The first
  * call on a device looks up the table's device address: make it before any stream capture.  Calls
  * share the table; run them one after the other (overlapping calls race on it).  Nothing in the
- * table needs clearing between calls: each call writes every record it later reads.
+ * table needs clearing between calls: each call writes every record it later reads; the one word that
+ * must start at zero (the counter the scan draws its chunks from, next to the table) is cleared on
+ * `stream` by every call.
  * Error text: m2k_global_error(). */
 int m2k_scan_flags_noalloc(int device, void* stream, const uint8_t* d_bytes, const uint64_t* d_file_off,
                            const uint64_t* d_file_len, const uint32_t* d_chunk_first, uint32_t n_files,
