@@ -192,8 +192,9 @@ const char* m2k_last_error(const m2k_ctx* ctx);
 /* a context keeps the two device buffers that grow with a shard (its bytes, the Dockerfile stripe states) and the
  * page-locked host blocks of its results when they are released, and hands them to the next call that fits, so
  * that repeated m2k_detect calls pay neither cudaMalloc / cudaFree of the whole tree nor page-locking each time;
- * m2k_ctx_trim gives the idle ones back to the driver.  Release every result and device tree of a context
- * before destroying it. */
+ * m2k_ctx_trim gives the idle ones back to the driver.  A result that is released after its context was
+ * destroyed frees what it holds itself (hosts with a garbage collector release in any order); a device tree
+ * still needs a live context for m2k_devtree_free. */
 int m2k_ctx_trim(m2k_ctx* ctx);
 int m2k_device_info(m2k_ctx* ctx, int* sm_count, uint64_t* hbm_bytes, char* name, size_t name_cap);
 

@@ -27,6 +27,15 @@ constexpr uint32_t kSpecialCap = 1u << 16;  // entries with a special name (.m2k
 // what m2k_prepare / m2k_finalize derive from the .m2kignore files (host side of a2 / a4)
 struct Folded { uint64_t key; uint32_t off, len, flag; };  // one ignore entry: hash of its folded runes, where they are
 
+// Results and device trees may outlive their context (a garbage-collected host language releases in any order):
+// what they hold from a context's pools goes back to the pool only while that context is alive, and is
+// freed directly otherwise.
+static std::mutex g_live_mu;
+static std::vector<Ctx*> g_live_ctx;
+static bool ctx_alive(Ctx* C) {  // caller holds g_live_mu
+  return C && std::find(g_live_ctx.begin(), g_live_ctx.end(), C) != g_live_ctx.end();
+}
+
 // pinned host blocks from the context's pool (Ctx::pinned_pool); a NULL context means plain cudaHostAlloc
 static void* pinned_take(Ctx* C, size_t bytes) {
   if (!bytes) bytes = 16;
@@ -43,10 +52,13 @@ static void* pinned_take(Ctx* C, size_t bytes) {
 }
 static void pinned_give(Ctx* C, void* p) {
   if (!p) return;
-  if (C)
-    for (auto& b : C->pinned_pool)
-      if (b.p == p) { b.in_use = false; return; }
-  cudaFreeHost(p);
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    if (ctx_alive(C))
+      for (auto& b : C->pinned_pool)
+        if (b.p == p) { b.in_use = false; return; }
+  }
+  cudaFreeHost(p);  // not pooled, or the pool's context is gone (it left its lent blocks to their holders)
 }
 
 // grow-only host buffer the ignore table is built in.  Pinned in the product: a copy from pageable
@@ -227,6 +239,10 @@ extern "C" int m2k_ctx_create(int device, m2k_ctx** out) {
   CUX(cudaMalloc(&C->d_sigs, sizeof(NameSig) * sigs.size()));
   CUX(cudaMemcpy(C->d_sigs, sigs.data(), sizeof(NameSig) * sigs.size(), cudaMemcpyHostToDevice));
 #undef CUX
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live_ctx.push_back(C);
+  }
   *out = ctx;
   return M2K_OK;
 }
@@ -239,8 +255,13 @@ extern "C" void m2k_ctx_destroy(m2k_ctx* ctx) {
   if (C->copy_stream) cudaStreamSynchronize(C->copy_stream);
   if (C->side_stream) cudaStreamSynchronize(C->side_stream);
   cudaFree(C->d_fold_from); cudaFree(C->d_fold_to); cudaFree(C->d_sigs);
-  for (auto& A : C->arena) if (A.p) cudaFree(A.p);
-  for (auto& b : C->pinned_pool) cudaFreeHost(b.p);  // results must have been released before their context
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live_ctx.erase(std::remove(g_live_ctx.begin(), g_live_ctx.end(), C), g_live_ctx.end());
+  }
+  // what is lent out stays with its holder (a result or device tree released later frees it itself)
+  for (auto& A : C->arena) if (A.p && !A.in_use) cudaFree(A.p);
+  for (auto& b : C->pinned_pool) if (!b.in_use) cudaFreeHost(b.p);
   for (auto& ev : C->ev) if (ev) cudaEventDestroy(ev);
   for (cudaEvent_t ev : {C->ev_names, C->ev_feat, C->ev_blob, C->ev_fork, C->ev_join, C->ev_early, C->ev_side0, C->ev_side1}) if (ev) cudaEventDestroy(ev);
   if (C->ev_idle) cudaEventDestroy(C->ev_idle);
@@ -359,10 +380,14 @@ static void devtree_release(DevTree* t) {
   if (t->link.ipc_base) { cudaIpcCloseMemHandle(t->link.ipc_base); t->link.ipc_base = nullptr; }
   // (dir_direct, dir_content, dir_subtree, file_flags, df_counters, special, dir_first_war, dir_main and
   // dir_main_sub live inside the slab)
-  if (t->arena_ctx) {  // hand the big buffers back to the context instead of freeing them
-    if (t->from_arena & 1u) { t->arena_ctx->arena[0].in_use = false; t->bytes = nullptr; }
-    if (t->from_arena & 2u) { t->arena_ctx->arena[1].in_use = false; t->stripe_state = nullptr; }
+  if (t->arena_ctx) {  // hand the big buffers back to the context instead of freeing them -- if it is still there
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    if (ctx_alive(t->arena_ctx)) {
+      if (t->from_arena & 1u) { t->arena_ctx->arena[0].in_use = false; t->bytes = nullptr; }
+      if (t->from_arena & 2u) { t->arena_ctx->arena[1].in_use = false; t->stripe_state = nullptr; }
+    }
     t->from_arena = 0;
+    t->arena_ctx = nullptr;
   }
   void* ptrs[] = {t->dir_parent, t->dir_entry, t->dir_depth, t->dir_flags, t->entry_dir, t->entry_name_off,
                   t->entry_child, t->entry_type, t->names, t->file_entry, t->file_off, t->file_len, t->chunk_first, t->chunk_file, t->bytes,

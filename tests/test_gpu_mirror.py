@@ -234,3 +234,26 @@ def test_against_the_reference_golden_plans(tmp_path, tmp_path_factory, assets, 
         want = ref["text"].replace("rootDir: ../../samples/nodejs", "rootDir: " + os.path.relpath(root, cwd))
         assert text == want
     containerizer.CNBContainerizer._cache.clear()
+
+
+def test_a_result_may_outlive_its_context(tmp_path):
+    """A host with a garbage collector releases in any order: a result freed after m2k_ctx_destroy gives nothing
+    back to the (gone) context's pools and frees its buffers itself."""
+    from move2kube_b200 import _abi, lib
+    c = lib.Context(0)
+    p = _abi.SynthParams(seed=3, n_files=300, n_dirs=30, max_depth=4, n_ignore_files=2, total_bytes=4 << 20)
+    tree = c.synth_tree(p, host_bytes=True)
+    res = c.detect(tree)
+    n = res.contents.n_services
+    L = c.L
+    c.close()                      # the context goes first
+    assert res.contents.n_services == n and res.contents.dir_opts[0] is not None   # the result's arrays are still there
+    L.m2k_result_free(res)         # ... and can be released now
+    L.m2k_tree_free(None, tree)
+    c2 = lib.Context(0)            # a new context works as usual
+    t2 = c2.synth_tree(p, host_bytes=True)
+    r2 = c2.detect(t2)
+    assert r2.contents.n_services == n
+    c2.result_free(r2)
+    c2.tree_free(t2)
+    c2.close()
