@@ -133,6 +133,32 @@ __device__ __forceinline__ uint32_t kw_final(uint32_t alive, uint32_t len) {
   return out;
 }
 
+// The byte scan's pre-filter (kernels.cu first_word_rules_out_dockerfile): w = the first 16 bytes of a file, little
+// endian, zero padded.  true = the first instruction cannot be FROM, whatever follows.
+__device__ inline bool first_word_rules_out(const uint32_t (&w)[4]) {
+  int start = ((w[0] & 0xFFFFFFu) == 0xBFBBEFu) ? 3 : 0;  // UTF-8 byte order mark
+  uint32_t alive = 0x1F, idx = 0;
+  bool in_word = false;
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    if (i < start) continue;
+    uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xFF;
+    bool ws = c == ' ' || (c >= 0x09 && c <= 0x0D);
+    if (!in_word) {
+      if (ws) continue;
+      if (c == 0 || c == '#' || c == '\\' || c >= 0x80) return false;
+      in_word = true;
+    } else {
+      if (ws) return kw_final(alive, idx) == 0;
+      if (c == 0 || c == '\\' || c >= 0x80) return false;
+    }
+    alive = kw_step(alive, idx, c);
+    idx++;
+    if (alive == 0) return true;
+  }
+  return false;
+}
+
 // extractBuilderFlags: advances c to the start of the remaining part.  Byte-wise, with
 // unicode.IsSpace applied to byte values (0x85 and 0xA0 count as space).
 __device__ inline void skip_builder_flags(const File& f, LCur& c) {
@@ -398,6 +424,7 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
           uint32_t c0 = p[t];
           if (c0 == '\n' || ascii_ws(c0)) break;
           if (c0 == f.esc) { alive = 0x1F; break; }  // may be a line continuation inside the word: exact path
+          if (c0 >= 0x80 && n - t < 4) { alive = 0x1F; break; }  // a rune that [0, n) may hold only in part (n can be a cut): exact path
           uint32_t w, r = decode_rune(p + t, n - t, &w);
           if (is_space_rune(r)) break;  // unicode space: leave it to the exact path
           alive = kw_step(alive, idx, r);

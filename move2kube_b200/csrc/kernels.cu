@@ -234,28 +234,8 @@ __device__ __noinline__ bool confirm_main(const uint8_t* file, uint64_t len, uin
 // false without ever touching the file again.  Anything unusual (comment or directive, non-ASCII
 // byte, escape character, NUL, no verdict within 16 bytes) is left to k_df_head.
 __device__ __noinline__ bool first_word_rules_out_dockerfile(uint4 v) {
-  uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  int start = ((v.x & 0xFFFFFFu) == 0xBFBBEFu) ? 3 : 0;  // UTF-8 byte order mark
-  uint32_t alive = 0x1F, idx = 0;
-  bool in_word = false;
-#pragma unroll
-  for (int i = 0; i < 16; i++) {
-    if (i < start) continue;
-    uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xFF;
-    bool ws = c == ' ' || (c >= 0x09 && c <= 0x0D);
-    if (!in_word) {
-      if (ws) continue;
-      if (c == 0 || c == '#' || c == '\\' || c >= 0x80) return false;
-      in_word = true;
-    } else {
-      if (ws) return df::kw_final(alive, idx) == 0;
-      if (c == 0 || c == '\\' || c >= 0x80) return false;
-    }
-    alive = df::kw_step(alive, idx, c);
-    idx++;
-    if (alive == 0) return true;
-  }
-  return false;
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  return df::first_word_rules_out(w);  // dockerfile_dev.cuh, where the host-side fuzz of the parsing code reaches it
 }
 
 struct ScanArgs {
