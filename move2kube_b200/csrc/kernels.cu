@@ -8,6 +8,7 @@
 #include "dockerfile_dev.cuh"
 #include "gostr.h"
 #include "m2k_internal.h"
+#include "runacc.h"
 #include "synth.h"
 
 namespace m2k {
@@ -535,30 +536,10 @@ void launch_scan_bytes(Ctx* c, DevTree* t, ChunkRec* chunk_rec, uint32_t* ticket
 // more than 128 chunks).  Produces HAS_MAIN and
 // LONG_LINE, and the per-directory content partials for "__main__" in a file named *py.
 // ---------------------------------------------------------------------------------------------
-struct RunAcc {            // monoid over a span of bytes of one file
-  uint64_t bytes;          // bytes in the span
-  uint64_t lead, trail;    // bytes before the first / after the last newline (== bytes when there is none)
-  uint32_t longf;          // a line closed inside the span has >= 64 KiB
-};
-
-__device__ __forceinline__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b) {
-  if (a.bytes == 0) return b;
-  if (b.bytes == 0) return a;
-  RunAcc r;
-  r.bytes = a.bytes + b.bytes;
-  r.longf = a.longf | b.longf;
-  const bool a_free = a.lead == a.bytes, b_free = b.lead == b.bytes;
-  r.lead = a_free ? a.bytes + b.lead : a.lead;
-  r.trail = b_free ? b.bytes + a.trail : b.trail;
-  if (!a_free && !b_free && a.trail + b.lead >= kLongLine) r.longf = 1;  // a line closed on both sides
-  return r;
-}
-
-// LONG_LINE of a whole file: a closed line, or the open runs at the file's start / end
+// RunAcc, acc_merge, acc_long: runacc.h (shared with the host-side property test of the fold)
+__device__ __forceinline__ RunAcc acc_merge(const RunAcc& a, const RunAcc& b) { return acc_merge_at(a, b, (uint64_t)kLongLine); }
 __host__ __device__ __forceinline__ uint32_t acc_long(uint64_t bytes, uint64_t lead, uint64_t trail, uint32_t longf) {
-  if (longf) return 1;
-  if (lead >= kLongLine) return 1;  // also the file without any newline (lead == bytes)
-  return (lead != bytes && trail >= kLongLine) ? 1u : 0u;
+  return acc_long_at(bytes, lead, trail, longf, (uint64_t)kLongLine);
 }
 
 constexpr uint32_t kCombineWarpChunks = 128;  // files with more chunks are folded by the whole warp
@@ -732,9 +713,24 @@ __global__ void __launch_bounds__(256) k_file_combine(FileArgs a) {
 //                 start in it; the thread that completes a candidate's last stripe sets its
 //                 DOCKERFILE bit and the directory's content bit.
 // ---------------------------------------------------------------------------------------------
+// Work items of the two parsing kernels below are handed out so that as few of them as possible share a warp:
+// threads of one warp that parse different files or stripes diverge, and a diverged warp runs its lanes' paths one
+// after the other -- on a small tree (config B: 128 heads, 1551 stripes) that serial run IS the kernel's duration.
+// With n items and W warps in the grid, each warp takes k = the power of two >= n / W (at most 32) consecutive
+// items per round on its first k lanes; k = 32 is the plain one-item-per-thread order large trees get.
+struct Spread { uint32_t k, item0, per_round; bool lane_on; };
+__device__ __forceinline__ Spread spread_items(uint32_t n) {
+  const uint32_t W = gridDim.x * (blockDim.x >> 5), gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  uint32_t k = 1;
+  while (k < 32 && (uint64_t)k * W < n) k <<= 1;
+  return Spread{k, gw * k + lane, W * k, lane < k};
+}
+
 __global__ void __launch_bounds__(128) k_df_head(FileArgs a) {
   const uint32_t n = a.ctr->n_heads;
-  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+  const Spread sp = spread_items(n);
+  if (!sp.lane_on) return;
+  for (uint32_t j = sp.item0; j < n; j += sp.per_round) {
     const uint32_t i = a.head_list[j], f = a.file_begin + i;
     const uint8_t* fbytes = a.bytes + (a.file_off[f] - a.shard_byte0);
     const uint64_t len = a.file_len[f];
@@ -799,12 +795,25 @@ __device__ __forceinline__ uint32_t seg_join(uint32_t first, uint32_t then) {  /
   return (first & 4u) | df::map_compose(first & 3u, then & 3u);
 }
 
+// line-state map of every stripe (bits 0-1) and "a body starts here" (bit 2), left in stripe_state for the scan below:
+// the parsing half of the state computation, apart from the scan so that its items can be spread over the warps
+__global__ void __launch_bounds__(128) k_df_maps(FileArgs a) {
+  const unsigned long long cs = a.ctr->cand_stripes;  // final: k_df_head has finished
+  const uint32_t n_cand = (uint32_t)(cs >> 32), n_stripes = (uint32_t)cs;
+  const Spread sp = spread_items(n_stripes);
+  if (!sp.lane_on) return;
+  for (uint32_t s = sp.item0; s < n_stripes; s += sp.per_round) {
+    const StripeRef r = df_stripe(a, n_cand, s);
+    const uint32_t el = df::stripe_map(df_file(a, r.c), r.body, r.lo, r.hi) | (r.k == 0 ? 4u : 0u);
+    if (M2K_CHECK(s < a.stripe_cap, 3)) a.stripe_state[s] = (uint8_t)el;
+  }
+}
+
 __global__ void __launch_bounds__(kDfTileStripes) k_df_states(FileArgs a) {
   __shared__ uint32_t s_ticket, s_in;
   __shared__ uint32_t s_warp[kDfTileStripes / 32];
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned long long cs = a.ctr->cand_stripes;  // final: k_df_head has finished
-  const uint32_t n_cand = (uint32_t)(cs >> 32), n_stripes = (uint32_t)cs;
+  const uint32_t n_stripes = (uint32_t)a.ctr->cand_stripes;  // low half; final: k_df_head has finished
   const uint32_t n_tiles = (n_stripes + kDfTileStripes - 1) / kDfTileStripes;
   const uint32_t tag = a.epoch << 3;
   for (;;) {
@@ -815,10 +824,7 @@ __global__ void __launch_bounds__(kDfTileStripes) k_df_states(FileArgs a) {
     const uint32_t s = t * kDfTileStripes + tid;
     const bool live = s < n_stripes;
     uint32_t el = 0x2u;  // identity map, no segment start
-    if (live) {
-      const StripeRef r = df_stripe(a, n_cand, s);
-      el = df::stripe_map(df_file(a, r.c), r.body, r.lo, r.hi) | (r.k == 0 ? 4u : 0u);
-    }
+    if (live && M2K_CHECK(s < a.stripe_cap, 3)) el = a.stripe_state[s];  // k_df_maps left it there
     uint32_t inc = el;  // inclusive segmented scan over the warp (earlier stripe first)
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -878,9 +884,10 @@ __global__ void __launch_bounds__(128) k_df_validate(FileArgs a) {
   const unsigned long long cs = a.ctr->cand_stripes;
   const uint32_t n_cand = (uint32_t)(cs >> 32), n_stripes = (uint32_t)cs;
   const uint32_t lane = threadIdx.x & 31;
-  const uint32_t n_round = (n_stripes + 31) & ~31u;  // whole warps stay together for the vote below
-  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
-    const bool live = s < n_stripes;
+  const Spread sp = spread_items(n_stripes);
+  for (uint32_t base = 0; base < n_stripes; base += sp.per_round) {  // whole warps stay together for the vote below
+    const uint32_t s = base + sp.item0;
+    const bool live = sp.lane_on && s < n_stripes;
     uint32_t c = M2K_NONE;
     if (live) {
       const StripeRef r = df_stripe(a, n_cand, s);
@@ -932,9 +939,10 @@ void launch_dockerfile(Ctx* c, DevTree* t) {
   if (t->file_end == t->file_begin) return;
   FileArgs a = file_args(t, nullptr);
   k_df_head<<<c->sm_count * 8, 128, 0, c->stream>>>(a);
+  k_df_maps<<<c->sm_count * 8, 128, 0, c->stream>>>(a);
   k_df_states<<<c->sm_count * 4, kDfTileStripes, 0, c->stream>>>(a);
   k_df_validate<<<c->sm_count * 8, 128, 0, c->stream>>>(a);
-  c->launches += 3;
+  c->launches += 4;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1174,7 +1182,7 @@ __global__ void __launch_bounds__(256) k_contribute(const uint8_t* __restrict__ 
 // Every kernel a pass can launch is therefore loaded when an exchange is set up.
 int preload_kernels() {
   const void* fns[] = {(const void*)k_fill_u32, (const void*)k_name_features, (const void*)k_scan_bytes, (const void*)k_scan_bytes_bulk,
-                       (const void*)k_file_combine, (const void*)k_df_head, (const void*)k_df_states, (const void*)k_df_validate,
+                       (const void*)k_file_combine, (const void*)k_df_head, (const void*)k_df_maps, (const void*)k_df_states, (const void*)k_df_validate,
                        (const void*)k_content_up, (const void*)k_walk_local, (const void*)k_walk_reach, (const void*)k_signal,
                        (const void*)k_wait_ge, (const void*)k_contribute, (const void*)k_merge_partials_fn(), (const void*)k_merge_pieces_fn(),
                        (const void*)k_settle_file_fn(), (const void*)k_synth_fill_fn()};

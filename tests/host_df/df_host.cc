@@ -98,3 +98,45 @@ extern "C" uint32_t dfhost_head_prefix(const uint8_t* data, uint64_t n_here) {
 }
 
 extern "C" uint32_t dfhost_default_stripe(void) { return m2k::df::kStripe; }
+
+// ---- the newline-run monoid (move2kube_b200/csrc/runacc.h) --------------------------------------------------------
+#include "../../move2kube_b200/csrc/runacc.h"
+
+namespace {
+m2k::RunAcc span_summary(const uint8_t* d, uint64_t n, uint64_t limit) {  // straight from the bytes
+  m2k::RunAcc r{n, n, n, 0};
+  uint64_t first = n, last = n;
+  for (uint64_t i = 0; i < n; i++) if (d[i] == '\n') { if (first == n) first = i; last = i; }
+  if (first == n) return r;
+  r.lead = first;
+  r.trail = n - 1 - last;
+  uint64_t run = 0;
+  bool open = true;  // the run before the first newline is open on the left
+  for (uint64_t i = 0; i < n; i++) {
+    if (d[i] == '\n') { if (!open && run >= limit) r.longf = 1; run = 0; open = false; }
+    else run++;
+  }
+  return r;
+}
+m2k::RunAcc fold_tree(const uint8_t* d, const uint64_t* cut, uint32_t lo, uint32_t hi, uint64_t limit, uint32_t* seed) {
+  if (hi - lo == 1) return span_summary(d + cut[lo], cut[hi] - cut[lo], limit);
+  *seed = *seed * 1664525u + 1013904223u;
+  const uint32_t mid = lo + 1 + (*seed >> 8) % (hi - lo - 1);
+  const m2k::RunAcc a = fold_tree(d, cut, lo, mid, limit, seed), b = fold_tree(d, cut, mid, hi, limit, seed);
+  return m2k::acc_merge_at(a, b, limit);
+}
+}  // namespace
+
+// data[0, n) cut at cut[0] = 0 < ... <= cut[n_cut] = n into spans; the spans' summaries merged in a random tree
+// shape must equal the summary of the whole, and LONG_LINE must be "some line has >= limit bytes".
+// Returns 0 when everything agrees, else a code saying what did not.
+extern "C" uint32_t dfhost_runacc_check(const uint8_t* data, uint64_t n, const uint64_t* cut, uint32_t n_cut, uint64_t limit, uint32_t seed) {
+  const m2k::RunAcc whole = span_summary(data, n, limit);
+  const m2k::RunAcc got = n_cut ? fold_tree(data, cut, 0, n_cut, limit, &seed) : m2k::RunAcc{0, 0, 0, 0};
+  if (n && (got.bytes != whole.bytes || got.lead != whole.lead || got.trail != whole.trail || got.longf != whole.longf)) return 1;
+  uint64_t run = 0;
+  uint32_t want = 0;
+  for (uint64_t i = 0; i < n; i++) { if (data[i] == '\n') run = 0; else if (++run >= limit) want = 1; }
+  if (m2k::acc_long_at(got.bytes, got.lead, got.trail, got.longf, limit) != want) return 2;
+  return 0;
+}

@@ -30,7 +30,7 @@ def dfhost():
     os.makedirs(out_dir, exist_ok=True)
     so = os.path.join(out_dir, "libdfhost.so")
     srcs = [os.path.join(HERE, "host_df", "df_host.cc"), os.path.join(ROOT, "move2kube_b200", "csrc", "dockerfile_dev.cuh"),
-            os.path.join(ROOT, "move2kube_b200", "csrc", "gostr.h")]
+            os.path.join(ROOT, "move2kube_b200", "csrc", "gostr.h"), os.path.join(ROOT, "move2kube_b200", "csrc", "runacc.h")]
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wall", "-Wno-unknown-pragmas", "-Wno-sign-compare",
                                "-I", os.path.join(ROOT, "move2kube_b200", "csrc"), "-I", os.path.join(ROOT, "include"), srcs[0], "-o", so])
@@ -40,6 +40,8 @@ def dfhost():
     L.dfhost_head_prefix.restype = C.c_uint32
     L.dfhost_head_prefix.argtypes = [C.c_char_p, C.c_uint64]
     L.dfhost_default_stripe.restype = C.c_uint32
+    L.dfhost_runacc_check.restype = C.c_uint32
+    L.dfhost_runacc_check.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_uint32, C.c_uint64, C.c_uint32]
     return L
 
 
@@ -184,3 +186,22 @@ def test_a_head_settled_on_a_prefix_stays_settled(dfhost, seed):
             settled += 1
             assert (v == 1) == whole, (data, cut, v)
     assert settled > 10000
+
+
+def test_newline_runs_fold_the_same_in_any_grouping(dfhost):
+    """LONG_LINE comes from per-chunk (lead, trail) records merged per thread, per block share of a big file and per
+    piece of a file cut between GPUs (runacc.h): any grouping of any cutting of a span must give the summary of the
+    whole, and the flag must say "some line has >= limit bytes".  Short limits, so that every boundary case is common."""
+    r = random.Random(5)
+    for case in range(40000):
+        limit = r.choice((1, 2, 3, 5, 8, 13))
+        n = r.randrange(0, 48)
+        p_nl = r.choice((0.0, 0.05, 0.2, 0.5, 0.9))
+        data = bytes(10 if r.random() < p_nl else 120 for _ in range(n))
+        cuts = sorted({0, n} | {r.randrange(0, n + 1) for _ in range(r.randrange(0, 9))}) if n else [0]
+        if r.random() < 0.2 and n:  # chunk-like: equal spans
+            step = r.randrange(1, 9)
+            cuts = list(range(0, n, step)) + [n]
+        arr = (C.c_uint64 * len(cuts))(*cuts)
+        rc = dfhost.dfhost_runacc_check(data, n, arr, len(cuts) - 1, limit, case)
+        assert rc == 0, (rc, data, cuts, limit)
