@@ -5,7 +5,8 @@
 // [external] buildkit's source is not in the reference tree (go.mod:22 pins v0.7.2) and the
 // reference has no test for this function: parity for this kernel is unpinned.  What
 // Parse can fail on, and therefore what this code checks for the whole file: the escape parser
-// directive (invalid or repeated), ENV/LABEL name-value syntax (also under ONBUILD), "file with no
+// directive (invalid or repeated), ENV/LABEL name-value syntax and a JSON-form argument that is a well-formed array with a
+// non-string element (both also under ONBUILD), "file with no
 // instructions", and lines of 64 KiB or more (checked by the byte-scan kernel, passed in here).
 //
 // One thread parses one file.  A logical line (continuation lines joined, comment and blank
@@ -59,15 +60,6 @@ __device__ inline bool trim_continuation(const File& f, uint64_t lb, uint64_t* l
   return false;
 }
 
-__device__ inline bool all_space(const File& f, uint64_t lb, uint64_t le) {
-  while (lb < le) {
-    uint32_t w, r = decode_rune(f.p + lb, le - lb, &w);
-    if (!is_space_rune(r)) return false;
-    lb += w;
-  }
-  return true;
-}
-
 // cursor over a logical line
 struct LCur {
   uint64_t pos, seg_end, next_line;
@@ -81,8 +73,10 @@ __device__ inline int lc_get(const File& f, LCur& c) {
     if (c.next_line >= f.n) { c.more = false; return -1; }
     uint64_t lb = c.next_line, le;
     c.next_line = phys_line(f, lb, &le);
-    if (lb < le && f.p[lb] == '#') continue;  // isComment(raw continuation line)
-    if (all_space(f, lb, le)) continue;       // isEmptyContinuationLine
+    // isComment(trimWhitespace(raw continuation line)) -- an indented comment is dropped too -- and isEmptyContinuationLine
+    uint64_t t = lb;
+    while (t < le) { uint32_t w, r = decode_rune(f.p + t, le - t, &w); if (!is_space_rune(r)) break; t += w; }
+    if (t == le || f.p[t] == '#') continue;
     c.more = trim_continuation(f, lb, &le);
     c.pos = lb;
     c.seg_end = le;
@@ -112,24 +106,41 @@ __device__ inline bool lc_rest_all_space(const File& f, LCur c) {
   return true;
 }
 
-// keywords: bit0 from, bit1 arg, bit2 env, bit3 label, bit4 onbuild (packed little-endian)
+// keywords: bit0 from, bit1 arg, bit2 env, bit3 label, bit4 onbuild -- the five the head of a file is about -- then
+// the commands whose arguments may be a JSON array (parseMaybeJSON: cmd, entrypoint, run, shell; parseMaybeJSONToList:
+// add, copy, volume; parseHealthConfig: healthcheck).  Two little-endian words of eight characters per keyword.
+enum : uint32_t {
+  KW_FROM = 1u << 0, KW_ARG = 1u << 1, KW_ENV = 1u << 2, KW_LABEL = 1u << 3, KW_ONBUILD = 1u << 4,
+  KW_ADD = 1u << 5, KW_CMD = 1u << 6, KW_COPY = 1u << 7, KW_ENTRYPOINT = 1u << 8, KW_RUN = 1u << 9, KW_SHELL = 1u << 10,
+  KW_VOLUME = 1u << 11, KW_HEALTHCHECK = 1u << 12,
+  KW_HEAD = 0x1Fu,                                  // what first_word_rules_out and the head's quick reject follow
+  KW_JSON = 0x1FE0u,                                // the eight JSON-form commands
+  KW_CAN_FAIL = KW_ENV | KW_LABEL | KW_ONBUILD | KW_JSON  // newNodeFromLine can return an error for these only
+};
+constexpr int kNKeywords = 13;
 __device__ __forceinline__ uint32_t kw_step(uint32_t alive, uint32_t idx, uint32_t r) {
   // strings.ToLower: the only non-ASCII runes lower-casing into ASCII letters are U+0130 and U+212A
   if (r - 'A' < 26u) r += 32; else if (r == 0x130) r = 'i'; else if (r == 0x212A) r = 'k';
-  constexpr uint64_t KW[5] = {0x6D6F7266ull /*from*/, 0x677261ull /*arg*/, 0x766E65ull /*env*/,
-                              0x6C6562616Cull /*label*/, 0x646C6975626E6Full /*onbuild*/};
-  if (idx >= 8) return 0;
+  constexpr uint64_t LO[kNKeywords] = {0x6D6F7266ull /*from*/, 0x677261ull /*arg*/, 0x766E65ull /*env*/, 0x6C6562616Cull /*label*/,
+                                       0x646C6975626E6Full /*onbuild*/, 0x646461ull /*add*/, 0x646D63ull /*cmd*/, 0x79706F63ull /*copy*/,
+                                       0x696F707972746E65ull /*entrypoi*/, 0x6E7572ull /*run*/, 0x6C6C656873ull /*shell*/,
+                                       0x656D756C6F76ull /*volume*/, 0x686368746C616568ull /*healthch*/};
+  constexpr uint32_t HI[kNKeywords] = {0, 0, 0, 0, 0, 0, 0, 0, 0x746Eu /*nt*/, 0, 0, 0, 0x6B6365u /*eck*/};
+  if (idx >= 12) return 0;
   uint32_t out = 0;
 #pragma unroll
-  for (int k = 0; k < 5; k++)
-    if ((alive >> k & 1) && (uint32_t)((KW[k] >> (8 * idx)) & 0xFF) == r) out |= 1u << k;
+  for (int k = 0; k < kNKeywords; k++) {
+    if (!(alive >> k & 1)) continue;
+    const uint32_t ch = idx < 8 ? (uint32_t)((LO[k] >> (8 * idx)) & 0xFF) : ((HI[k] >> (8 * (idx - 8))) & 0xFF);
+    if (ch == r) out |= 1u << k;
+  }
   return out;
 }
 __device__ __forceinline__ uint32_t kw_final(uint32_t alive, uint32_t len) {
-  constexpr uint32_t LEN[5] = {4, 3, 3, 5, 7};
+  constexpr uint32_t LEN[kNKeywords] = {4, 3, 3, 5, 7, 3, 3, 4, 10, 3, 5, 6, 11};
   uint32_t out = 0;
 #pragma unroll
-  for (int k = 0; k < 5; k++) if ((alive >> k & 1) && len == LEN[k]) out |= 1u << k;
+  for (int k = 0; k < kNKeywords; k++) if ((alive >> k & 1) && len == LEN[k]) out |= 1u << k;
   return out;
 }
 
@@ -328,13 +339,178 @@ __device__ inline bool from_regex(const File& f, LCur c) {
   }
 }
 
+// ---- arguments in JSON form ---------------------------------------------------------------------------------------
+// parseMaybeJSON / parseMaybeJSONToList (line_parsers.go) hand an argument that starts with '[' to
+// json.NewDecoder(..).Decode(&[]interface{}) and fail -- errDockerfileNotStringArray, which fails Parse -- only when
+// that succeeds AND some element of the array is not a string; any Decode error makes them take the argument as a
+// plain string instead.  So the exact question is: is the FIRST JSON value of the stream a well-formed array (by
+// encoding/json's scanner: nesting at most 10000, Go >= 1.15), with every number at any depth inside float64 range
+// (d.convertNumber: strconv.ParseFloat fails on overflow only), and with a top-level element that is not a string?
+
+// |value| >= 2^1024 - 2^970 rounds to infinity.  The literal is followed digit by digit: `nd` significant digits so
+// far, `cmp` how their first 309 compare with the limit's, `point` where the decimal point sits relative to the first
+// significant digit.
+struct F64Range {
+  uint32_t nd; int32_t cmp; int64_t point; bool seen_point;
+  __device__ void start() { nd = 0; cmp = 0; point = 0; seen_point = false; }
+  __device__ void digit(uint32_t d) {
+    const char* const LIMIT =
+        "1797693134862315807937289714053034150799341327100378269361737789804449682927647509466490179775872070963302864166928879109465555478519404026306574886715058206819089020007083836762738548458177115317644757302700698555713669596228429148198608349364752927190741684443655107043427115596995080930428801779041744977"
+        "92";
+    if (nd == 0 && d == 0) { if (seen_point) point--; return; }  // a leading zero: only moves the point
+    if (nd < 309 && cmp == 0) { const uint32_t l = (uint32_t)(LIMIT[nd] - '0'); cmp = d < l ? -1 : (d > l ? 1 : 0); }
+    nd++;
+    if (!seen_point) point++;
+  }
+  __device__ void decimal_point() { seen_point = true; }
+  // exp: the exponent's value (clamped by the caller), already signed
+  __device__ bool overflows(int64_t exp) const {
+    if (nd == 0) return false;  // zero
+    const int64_t p = point + exp;  // value = 0.d1d2d3... x 10^p
+    if (p != 309) return p > 309;
+    return nd >= 309 ? cmp >= 0 : cmp > 0;  // fewer digits than the limit and equal so far: the limit's next digit is not 0
+  }
+};
+
+#ifndef M2K_JSON_KEEP
+#define M2K_JSON_KEEP 64  // innermost levels whose kind (array / object) is kept in a register; tests build with 2
+#endif
+
+// c: cursor at the '[' .  true = errDockerfileNotStringArray.
+__device__ inline bool json_array_not_all_strings(const File& f, LCur c) {
+  enum { BEGIN_VALUE, BEGIN_VALUE_OR_EMPTY, BEGIN_STRING_OR_EMPTY, BEGIN_STRING, IN_STRING, IN_ESC, NEG, N1, N0, DOT, DOT0, EXP, ESIGN, E0, END_VALUE };
+  const LCur origin = c;
+  uint64_t kinds = 0;        // bit i: the container i levels above the innermost is an object
+  uint32_t depth = 0, known = 0, consumed = 0;
+  bool top_key = false;      // the innermost container is an object waiting for ':' after a key
+  bool non_string = false, out_of_range = false, exp_neg = false;
+  int step = BEGIN_VALUE;
+  int64_t exp = 0;
+  F64Range num;
+  num.start();
+  int b = lc_get(f, c);
+  consumed++;
+  for (;;) {
+    if (b < 0) return false;  // the array never closed
+    const uint32_t ch = (uint32_t)b;
+    const bool sp = ch == ' ' || ch == '\t' || ch == '\r' || ch == '\n';
+    bool redo = false;  // the state hands this byte on to another one
+    switch (step) {
+      case BEGIN_VALUE: case BEGIN_VALUE_OR_EMPTY: case BEGIN_STRING_OR_EMPTY: case BEGIN_STRING:
+        if (sp) break;
+        if (step == BEGIN_VALUE_OR_EMPTY && ch == ']') { step = END_VALUE; redo = true; break; }
+        if (step == BEGIN_STRING_OR_EMPTY && ch == '}') { top_key = false; step = END_VALUE; redo = true; break; }
+        if (step == BEGIN_STRING_OR_EMPTY || step == BEGIN_STRING) { if (ch != '"') return false; step = IN_STRING; break; }
+        if (depth == 1 && ch != '"') non_string = true;
+        if (ch == '{' || ch == '[') {
+          if (++depth > 10000) return false;  // "exceeded max depth"
+          kinds = (kinds << 1) | (ch == '{' ? 1u : 0u);
+          if (known < M2K_JSON_KEEP) known++;
+          top_key = ch == '{';
+          step = ch == '{' ? BEGIN_STRING_OR_EMPTY : BEGIN_VALUE_OR_EMPTY;
+        } else if (ch == '"') step = IN_STRING;
+        else if (ch == '-') { step = NEG; num.start(); }
+        else if (ch == '0') { step = N0; num.start(); num.digit(0); }
+        else if (ch - '1' < 9u) { step = N1; num.start(); num.digit(ch - '0'); }
+        else if (ch == 't' || ch == 'f' || ch == 'n') {
+          const char* w = ch == 't' ? "true" : ch == 'f' ? "false" : "null";
+          for (int k = 1; w[k]; k++) { b = lc_get(f, c); consumed++; if (b != w[k]) return false; }
+          step = END_VALUE;
+        } else return false;
+        break;
+      case IN_STRING:
+        if (ch == '"') step = END_VALUE; else if (ch == '\\') step = IN_ESC; else if (ch < 0x20) return false;
+        break;
+      case IN_ESC:
+        if (ch == 'b' || ch == 'f' || ch == 'n' || ch == 'r' || ch == 't' || ch == '\\' || ch == '/' || ch == '"') step = IN_STRING;
+        else if (ch == 'u') {
+          for (int k = 0; k < 4; k++) {
+            b = lc_get(f, c); consumed++;
+            if (b < 0) return false;
+            const uint32_t h = (uint32_t)b;
+            if (!(h - '0' < 10u || (h | 0x20) - 'a' < 6u)) return false;
+          }
+          step = IN_STRING;
+        } else return false;
+        break;
+      case NEG: if (ch == '0') { step = N0; num.digit(0); } else if (ch - '1' < 9u) { step = N1; num.digit(ch - '0'); } else return false; break;
+      case N1: if (ch - '0' < 10u) num.digit(ch - '0'); else { step = N0; redo = true; } break;
+      case N0:
+        if (ch == '.') { step = DOT; num.decimal_point(); }
+        else if (ch == 'e' || ch == 'E') { step = EXP; exp = 0; exp_neg = false; }
+        else { if (num.overflows(0)) out_of_range = true; step = END_VALUE; redo = true; }
+        break;
+      case DOT: if (ch - '0' >= 10u) return false; num.digit(ch - '0'); step = DOT0; break;
+      case DOT0:
+        if (ch - '0' < 10u) num.digit(ch - '0');
+        else if (ch == 'e' || ch == 'E') { step = EXP; exp = 0; exp_neg = false; }
+        else { if (num.overflows(0)) out_of_range = true; step = END_VALUE; redo = true; }
+        break;
+      case EXP: if (ch == '+' || ch == '-') { exp_neg = ch == '-'; step = ESIGN; } else { step = ESIGN; redo = true; } break;
+      case ESIGN: if (ch - '0' >= 10u) return false; exp = ch - '0'; step = E0; break;
+      case E0:
+        if (ch - '0' < 10u) { if (exp < 100000000) exp = exp * 10 + (ch - '0'); }
+        else { if (num.overflows(exp_neg ? -exp : exp)) out_of_range = true; step = END_VALUE; redo = true; }
+        break;
+      case END_VALUE: {
+        if (sp) break;
+        const bool in_object = (kinds & 1u) != 0;
+        if (in_object && top_key) { if (ch != ':') return false; top_key = false; step = BEGIN_VALUE; break; }
+        if (ch == ',') { if (in_object) { top_key = true; step = BEGIN_STRING; } else step = BEGIN_VALUE; break; }
+        if (ch != (in_object ? '}' : ']')) return false;
+        if (--depth == 0) return non_string && !out_of_range;  // the top-level array closed: the value is complete
+        kinds >>= 1; known--;
+        top_key = false;  // an enclosing object is inside one of its values
+        if (known == 0) {
+          // the kinds of the enclosing levels fell out of the register: one more pass over what has been read,
+          // noting the last container opened at each of the innermost levels <= depth (those are the open ones)
+          LCur r = origin;
+          uint32_t d = 0;
+          bool in_str = false;
+          uint64_t k2 = 0;
+          for (uint32_t i = 0; i < consumed; i++) {
+            const int x = lc_get(f, r);
+            if (in_str) { if (x == '\\') { lc_get(f, r); i++; } else if (x == '"') in_str = false; continue; }
+            if (x == '"') in_str = true;
+            else if (x == '[' || x == '{') {
+              d++;
+              if (d <= depth && depth - d < M2K_JSON_KEEP) { const uint64_t bit = 1ull << (depth - d); k2 = x == '{' ? (k2 | bit) : (k2 & ~bit); }
+            } else if (x == ']' || x == '}') d--;
+          }
+          kinds = k2;
+          known = depth < M2K_JSON_KEEP ? depth : M2K_JSON_KEEP;
+        }
+        break;
+      }
+    }
+    if (!redo) { b = lc_get(f, c); consumed++; }
+  }
+}
+
+// parseMaybeJSON* on the rest of the line at c (already past the flags): false = they fail
+__device__ inline bool maybe_json_ok(const File& f, LCur c) {
+  for (;;) { LCur t = c; uint32_t r; if (!lc_get_rune(f, t, &r)) return true; if (!is_space_rune(r)) break; c = t; }  // TrimSpace / parseJSON's TrimLeftFunc
+  if (lc_peek(f, c) != '[') return true;
+  return !json_array_not_all_strings(f, c);
+}
+
+// parseHealthConfig: the first word byte by byte (unicode.IsSpace of the byte's value), then parseMaybeJSON
+__device__ inline bool health_config_ok(const File& f, LCur c) {
+  for (;;) { LCur t = c; uint32_t r; if (!lc_get_rune(f, t, &r)) return true; if (!is_space_rune(r)) break; c = t; }  // TrimSpace(args)
+  uint32_t sep = 0;
+  for (;; sep++) { LCur t = c; const int b = lc_get(f, t); if (b < 0 || is_space_rune((uint32_t)b)) break; c = t; }
+  if (sep == 0) return true;
+  for (;;) { LCur t = c; const int b = lc_get(f, t); if (b < 0 || !is_space_rune((uint32_t)b)) break; c = t; }
+  return maybe_json_ok(f, c);
+}
+
 // newNodeFromLine at c.  Returns false on a parse error; *kind: 0 other, 1 from, 2 arg.
 __device__ inline bool node_from_line(const File& f, LCur c, int* kind) {
   *kind = 0;
   for (int depth = 0;; depth++) {
     // strings.TrimSpace (left)
     for (;;) { LCur t = c; uint32_t r; if (!lc_get_rune(f, t, &r)) { return true; } if (!is_space_rune(r)) break; c = t; }
-    uint32_t alive = 0x1F, idx = 0;
+    uint32_t alive = (1u << kNKeywords) - 1, idx = 0;
     bool has_rest = false;
     for (;;) {
       LCur t = c;
@@ -347,12 +523,14 @@ __device__ inline bool node_from_line(const File& f, LCur c, int* kind) {
       c = t;
     }
     uint32_t kw = kw_final(alive, idx);
-    if (depth == 0) *kind = (kw & 1) ? 1 : (kw & 2) ? 2 : 0;
-    if (!(kw & (4 | 8 | 16))) return true;  // only ENV, LABEL and ONBUILD can fail
-    if (!has_rest) return true;             // no arguments: parseNameVal / parseSubCommand accept ""
+    if (depth == 0) *kind = (kw & KW_FROM) ? 1 : (kw & KW_ARG) ? 2 : 0;
+    if (!(kw & KW_CAN_FAIL)) return true;   // the other parsers cannot fail (parseIgnore, parseString, parseStringsWhitespaceDelimited, parseNameOrNameVal)
+    if (!has_rest) return true;             // no arguments: every one of them accepts ""
     for (;;) { LCur t = c; int b = lc_get(f, t); if (b < 0 || !ascii_ws((uint32_t)b)) break; c = t; }
     skip_builder_flags(f, c);
-    if (kw & (4 | 8)) return name_val_ok(f, c);
+    if (kw & (KW_ENV | KW_LABEL)) return name_val_ok(f, c);
+    if (kw & KW_HEALTHCHECK) return health_config_ok(f, c);
+    if (kw & KW_JSON) return maybe_json_ok(f, c);
     // onbuild: parseSubCommand -> newNodeFromLine(rest)
   }
 }
@@ -471,16 +649,14 @@ __device__ inline bool head(const uint8_t* p, uint64_t n, bool long_line, uint64
 constexpr uint32_t kStripe = M2K_DF_STRIPE;   // == kDfStripe (m2k_internal.h)
 
 __device__ inline uint32_t line_map(const File& f, uint64_t lb, uint64_t le) {
-  // from IN: comment and blank lines are dropped and the continuation goes on
   bool cont = false;
   { uint64_t e = le; cont = trim_continuation(f, lb, &e); }
-  bool raw_comment = lb < le && f.p[lb] == '#';
-  bool blank_line = all_space(f, lb, le);
-  uint32_t from_in = (raw_comment || blank_line) ? 1u : (cont ? 1u : 0u);
-  // from OUT: the line is left-trimmed first; comments and empty lines are skipped
-  uint64_t t = lb;
+  uint64_t t = lb;  // the line is left-trimmed before it is looked at, inside a continuation as well as outside
   while (t < le) { uint32_t w, r = decode_rune(f.p + t, le - t, &w); if (!is_space_rune(r)) break; t += w; }
-  uint32_t from_out = (t == le || f.p[t] == '#') ? 0u : (cont ? 1u : 0u);
+  const bool dropped = t == le || f.p[t] == '#';  // blank or comment
+  // from IN: dropped lines leave the continuation open; from OUT: they are skipped
+  const uint32_t from_in = dropped ? 1u : (cont ? 1u : 0u);
+  const uint32_t from_out = dropped ? 0u : (cont ? 1u : 0u);
   return from_out | (from_in << 1);
 }
 __device__ __forceinline__ uint32_t map_apply(uint32_t m, uint32_t state) { return (m >> state) & 1u; }
@@ -531,9 +707,9 @@ __device__ inline bool stripe_validate(const File& f, uint64_t body, uint64_t a,
       while (lb < le) { uint32_t w, r = decode_rune(f.p + lb, le - lb, &w); if (!is_space_rune(r)) break; lb += w; }
       bool check = lb < le && f.p[lb] != '#';
       if (check) {
-        // only ENV, LABEL and ONBUILD can fail: skip the line when its first word, ended by a blank
-        // inside this physical line, cannot be one of them
-        uint32_t alive = 4 | 8 | 16, idx = 0;
+        // only ENV, LABEL, ONBUILD and the JSON-form commands can fail: skip the line when its first word, ended by
+        // a blank inside this physical line, cannot be one of them
+        uint32_t alive = KW_CAN_FAIL, idx = 0;
         for (uint64_t t = lb; t < le && alive; idx++) {
           uint32_t c0 = f.p[t];
           if (ascii_ws(c0)) break;

@@ -15,9 +15,11 @@
  * Each function cites the reference lines it follows (paths under /root/reference).
  */
 #define _GNU_SOURCE
+#include <ctype.h>
 #include <dirent.h>
 #include <errno.h>
 #include <fcntl.h>
+#include <math.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -659,6 +661,95 @@ static int cmd_is(const char* w, size_t n, const char* kw) {
   return k == kn;
 }
 
+/* parseJSON's json.NewDecoder(...).Decode(&[]interface{}) on s[0..n), s[0] == '[': the FIRST JSON value of the
+ * stream by encoding/json's scanner (what follows the closing bracket is not looked at).  Returns 1 when the array is
+ * well formed, every number in it (at any depth) is in float64 range (d.convertNumber -> strconv.ParseFloat fails on
+ * overflow only) and some top-level element is not a string: errDockerfileNotStringArray, the one JSON outcome that
+ * makes parseMaybeJSON / parseMaybeJSONToList -- and with them Parse -- fail.  Anything else (syntax error, unclosed
+ * array, nesting beyond Go's 10000, number out of range, all strings) returns 0: the argument is then taken as a plain
+ * string.  [external] Go 1.15 encoding/json scanner.go, decode.go; buildkit v0.7.2 line_parsers.go. */
+static int json_array_not_all_strings(const uint8_t* s, size_t n) {
+  enum { OBJ_KEY, OBJ_VALUE, ARR_VALUE };
+  enum { BEGIN_VALUE, BEGIN_VALUE_OR_EMPTY, BEGIN_STRING_OR_EMPTY, BEGIN_STRING, IN_STRING, IN_ESC, NEG, N1, N0, DOT, DOT0, E, ESIGN, E0, END_VALUE };
+  size_t cap = 64, depth = 0, i = 0, num_start = 0;
+  uint8_t* st = (uint8_t*)malloc(cap);
+  int step = BEGIN_VALUE, non_string = 0, out_of_range = 0, result = 0;
+#define JFAIL() do { free(st); return 0; } while (0)
+#define JPUSH(kind) do { if (depth == cap) { cap *= 2; st = (uint8_t*)realloc(st, cap); } st[depth++] = (uint8_t)(kind); if (depth > 10000) JFAIL(); } while (0)
+#define JNUM_END() do { char tmp[64]; char* lit = (i - num_start < sizeof tmp) ? tmp : (char*)malloc(i - num_start + 1); \
+    memcpy(lit, s + num_start, i - num_start); lit[i - num_start] = 0; errno = 0; double v = strtod(lit, NULL); \
+    if (v == HUGE_VAL || v == -HUGE_VAL) out_of_range = 1; \
+    if (lit != tmp) free(lit); } while (0)
+  for (;;) {
+    if (i >= n) JFAIL(); /* io.ErrUnexpectedEOF */
+    const uint8_t c = s[i];
+    const int sp = c == ' ' || c == '\t' || c == '\r' || c == '\n';
+    int redo = 0;
+    switch (step) {
+      case BEGIN_VALUE: case BEGIN_VALUE_OR_EMPTY: case BEGIN_STRING_OR_EMPTY: case BEGIN_STRING:
+        if (sp) break;
+        if (step == BEGIN_VALUE_OR_EMPTY && c == ']') { step = END_VALUE; redo = 1; break; }
+        if (step == BEGIN_STRING_OR_EMPTY && c == '}') { st[depth - 1] = OBJ_VALUE; step = END_VALUE; redo = 1; break; }
+        if (step == BEGIN_STRING_OR_EMPTY || step == BEGIN_STRING) { if (c != '"') JFAIL(); step = IN_STRING; break; }
+        if (depth == 1 && c != '"') non_string = 1;
+        if (c == '{') { JPUSH(OBJ_KEY); step = BEGIN_STRING_OR_EMPTY; }
+        else if (c == '[') { JPUSH(ARR_VALUE); step = BEGIN_VALUE_OR_EMPTY; }
+        else if (c == '"') step = IN_STRING;
+        else if (c == '-') { step = NEG; num_start = i; }
+        else if (c == '0') { step = N0; num_start = i; }
+        else if (c >= '1' && c <= '9') { step = N1; num_start = i; }
+        else if (c == 't' || c == 'f' || c == 'n') {
+          const char* w = c == 't' ? "true" : c == 'f' ? "false" : "null";
+          const size_t wn = strlen(w);
+          if (n - i < wn || memcmp(s + i, w, wn) != 0) JFAIL();
+          i += wn - 1; step = END_VALUE;
+        } else JFAIL();
+        break;
+      case IN_STRING:
+        if (c == '"') step = END_VALUE; else if (c == '\\') step = IN_ESC; else if (c < 0x20) JFAIL();
+        break;
+      case IN_ESC:
+        if (c == 'b' || c == 'f' || c == 'n' || c == 'r' || c == 't' || c == '\\' || c == '/' || c == '"') step = IN_STRING;
+        else if (c == 'u') {
+          if (n - i < 5) JFAIL();
+          for (int k = 1; k <= 4; k++) if (!isxdigit(s[i + k])) JFAIL();
+          i += 4; step = IN_STRING;
+        } else JFAIL();
+        break;
+      case NEG: if (c == '0') step = N0; else if (c >= '1' && c <= '9') step = N1; else JFAIL(); break;
+      case N1: if (!(c >= '0' && c <= '9')) { step = N0; redo = 1; } break;
+      case N0: if (c == '.') step = DOT; else if (c == 'e' || c == 'E') step = E; else { JNUM_END(); step = END_VALUE; redo = 1; } break;
+      case DOT: if (!(c >= '0' && c <= '9')) JFAIL(); step = DOT0; break;
+      case DOT0: if (c >= '0' && c <= '9') break; if (c == 'e' || c == 'E') step = E; else { JNUM_END(); step = END_VALUE; redo = 1; } break;
+      case E: if (c == '+' || c == '-') step = ESIGN; else { step = ESIGN; redo = 1; } break;
+      case ESIGN: if (!(c >= '0' && c <= '9')) JFAIL(); step = E0; break;
+      case E0: if (!(c >= '0' && c <= '9')) { JNUM_END(); step = END_VALUE; redo = 1; } break;
+      case END_VALUE:
+        if (sp) break;
+        if (st[depth - 1] == OBJ_KEY) { if (c != ':') JFAIL(); st[depth - 1] = OBJ_VALUE; step = BEGIN_VALUE; }
+        else if (st[depth - 1] == OBJ_VALUE) {
+          if (c == ',') { st[depth - 1] = OBJ_KEY; step = BEGIN_STRING; } else if (c == '}') depth--; else JFAIL();
+        } else {
+          if (c == ',') step = BEGIN_VALUE;
+          else if (c == ']') { if (--depth == 0) { result = non_string && !out_of_range; free(st); return result; } }
+          else JFAIL();
+        }
+        break;
+    }
+    if (!redo) i++;
+  }
+#undef JFAIL
+#undef JPUSH
+#undef JNUM_END
+}
+
+/* parseMaybeJSON / parseMaybeJSONToList on [b, e): -1 when they fail */
+static int maybe_json(const uint8_t* b, const uint8_t* e) {
+  while (b < e) { size_t w; uint32_t r = decode_rune(b, (size_t)(e - b), &w); if (!is_space_rune(r)) break; b += w; } /* parseJSON: TrimLeftFunc */
+  if (b == e || *b != '[') return 0;
+  return json_array_not_all_strings(b, (size_t)(e - b)) ? -1 : 0;
+}
+
 /* newNodeFromLine: returns -1 on parse error; otherwise sets *kind: 0 other, 1 from, 2 arg */
 static int node_from_line(const char* line, size_t n, const directive* d, int* kind) {
   const uint8_t* b = (const uint8_t*)line; const uint8_t* e = b + n;
@@ -690,6 +781,17 @@ static int node_from_line(const char* line, size_t n, const directive* d, int* k
     if (rn == 0) return 0;
     int k2;
     return node_from_line((const char*)rest_b, rn, d, &k2);
+  }
+  /* the JSON-form commands: parseMaybeJSON (cmd, entrypoint, run, shell), parseMaybeJSONToList (add, copy, volume) */
+  if (cmd_is(cmd, cn, "add") || cmd_is(cmd, cn, "cmd") || cmd_is(cmd, cn, "copy") || cmd_is(cmd, cn, "entrypoint") || cmd_is(cmd, cn, "run") ||
+      cmd_is(cmd, cn, "shell") || cmd_is(cmd, cn, "volume"))
+    return maybe_json(rest_b, rest_e);
+  if (cmd_is(cmd, cn, "healthcheck")) { /* parseHealthConfig: the first word (bytes up to a byte that IsSpace), then parseMaybeJSON */
+    const uint8_t* q = rest_b;
+    while (q < rest_e && !is_space_rune(*q)) q++;
+    if (q == rest_b) return 0;
+    while (q < rest_e && is_space_rune(*q)) q++;
+    return maybe_json(q, rest_e);
   }
   return 0;
 }
@@ -773,9 +875,11 @@ uint32_t m2ko_dockerfile_flags(const uint8_t* data, uint64_t len) {
       if (rc == 0) break;
       if (possible_directive(&d, (const char*)lb, (size_t)(le - lb)) < 0) { parse_error = 1; break; }
       current_line++;
-      if (lb < le && *lb == '#') continue; /* isComment(raw line) */
+      /* isComment(scanner.Bytes()) = tokenComment.Match(trimWhitespace(line)): the raw line, left-trimmed first -- an
+       * INDENTED comment inside a continuation is dropped too (buildkit's TestParseWarnsOnEmptyContinutationLine has
+       * "RUN indented \\ / <4 blanks># this is an indented comment / comment"); then isEmptyContinuationLine */
       { const uint8_t* q = lb; while (q < le) { size_t w; uint32_t r = decode_rune(q, (size_t)(le - q), &w); if (!is_space_rune(r)) break; q += w; }
-        if (q == le) continue; } /* isEmptyContinuationLine */
+        if (q == le || *q == '#') continue; }
       cont.n = 0; sb_add(&cont, (const char*)lb, (size_t)(le - lb));
       eol = trim_continuation(&d, &cont);
       sb_add(&line, cont.p, cont.n);

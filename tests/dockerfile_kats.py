@@ -42,6 +42,13 @@ KATS = [
     ("continuation_comment_inside", b"FROM \\\n# comment\n  ubuntu\n", True),
     ("continuation_empty_inside", b"FROM \\\n\n  ubuntu\n", True),
     ("continuation_eof", b"FROM ubuntu \\", True),
+    # isComment() left-trims the raw continuation line first (tokenComment.Match(trimWhitespace(line))): an INDENTED
+    # comment inside a continuation is dropped, it does not become part of the instruction
+    ("continuation_indented_comment_dropped", b"FROM a \\\n  # c\n  b\n", False),       # "FROM a   b": two arguments
+    ("continuation_indented_comment_run", b"FROM a\nRUN x \\\n    # indented\n    && y\n", True),
+    ("continuation_indented_comment_env", b"FROM a\nENV A \\\n  # c\n", False),        # "ENV A": one argument
+    ("continuation_nbsp_indented_comment", b"FROM a \\\n\xc2\xa0# c\n b\n", False),
+    ("continuation_indented_comment_keeps_open", b"FROM \\\n \t# c \\\n  a\n", True),   # the comment's own backslash is not looked at
     ("escape_backtick", b"# escape=`\nFROM `\n  ubuntu\n", True),
     ("escape_backtick_backslash_literal", b"# escape=`\nFROM ubuntu\\\n", True),
     ("escape_invalid", b"# escape=x\nFROM a\n", False),
@@ -107,3 +114,38 @@ def reference_corpus():
     with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "_reference_dockerfile_corpus.json")) as f:
         j = json.load(f)
     return [(x["path"], base64.b64decode(x["bytes_b64"]), x["is_dockerfile"]) for x in j["files"]]
+
+# Arguments in JSON form (parseMaybeJSON / parseMaybeJSONToList / parseHealthConfig): a well-formed array with a non-string
+# element fails Parse (errDockerfileNotStringArray); whatever json.Decoder.Decode rejects is taken as a plain string.
+JSON_KATS = [
+    (b'FROM a\nCMD ["x"]\n', True),
+    (b'FROM a\nCMD [1]\n', False),                      # errDockerfileNotStringArray
+    (b'FROM a\nCMD ["a", 1] tail\n', False),            # Decode reads the first value only
+    (b'FROM a\nRUN [1e999]\n', True),                   # number out of range: Decode fails, plain string
+    (b'FROM a\nRUN [1,]\n', True),                      # syntax error: plain string
+    (b'FROM a\nCOPY [null]\n', False),
+    (b'FROM a\nADD [ "a" , "b" ]\n', True),
+    (b'FROM a\nHEALTHCHECK CMD [true]\n', False),
+    (b'FROM a\nHEALTHCHECK --interval=3s CMD ["x"]\n', True),
+    (b'FROM a\nHEALTHCHECK NONE\n', True),
+    (b'FROM a\nONBUILD RUN [{}]\n', False),
+    (b'FROM a\nRUN []\n', True),
+    (b'FROM a\nEXPOSE [1]\n', True),                    # parseStringsWhitespaceDelimited: no JSON
+    (b'FROM a\nVOLUME [ "a" , [ ] ]\n', False),
+    (b'FROM a\nRUN [1 2]\n', True),
+    (b'FROM a\nrun\t[0.5e-3 ]x\n', False),
+    (b'FROM a\nRUN ["\\u12g4", 1]\n', True),
+    (b'FROM a\nRUN [01]\n', True),
+    (b'FROM a\nRUN \\\n  [1]\n', False),                # the array on a continuation line
+    (b'FROM a\nRUN [1 \\\n  # c\n ]\n', False),         # ... with a dropped comment inside
+    (b'FROM a\nRUN --mount=type=cache [1]\n', False),   # after the flags
+    (b'FROM a\nENTRYPOINT [1.7976931348623157e308]\n', False),
+    (b'FROM a\nENTRYPOINT [1.7976931348623158e308]\n', False),   # still rounds to MaxFloat64
+    (b'FROM a\nENTRYPOINT [1.7976931348623159e308]\n', True),    # rounds to +Inf
+    (b'FROM a\nSHELL [{"a":[1e400]}, 2]\n', True),      # the out-of-range number sits two levels down
+    (b'FROM a\nSHELL ["a"\x0b]\n', True),               # \v is not JSON white space
+    (b'FROM a\nCMD\xc2\xa0[1]\n', True),                # NBSP does not end the command word: the command is unknown
+    (b'FROM a\nCMD \xc2\xa0[1]\n', False),              # ... after a blank it is trimmed off the arguments
+]
+
+KATS += [("json_%02d" % i, data, want) for i, (data, want) in enumerate(JSON_KATS)]
