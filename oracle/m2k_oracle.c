@@ -10,7 +10,9 @@
  * by running the reference's own detect scripts (oracle/script_oracle.py) on the reference's
  * fixtures.  The Dockerfile half (m2ko_is_dockerfile) restates moby/buildkit v0.7.2
  * frontend/dockerfile/parser (go.mod:22), whose source is NOT under /root/reference and which
- * no reference test exercises: that half is "parity unpinned".
+ * no reference test exercises: that half is "parity unpinned".  oracle/dockerfile_re.py derives the
+ * same function a third time by another method (a regex engine, literal string building); the CPU
+ * tests hold the three against each other.
  *
  * Each function cites the reference lines it follows (paths under /root/reference).
  */
