@@ -23,6 +23,5 @@ keys = [k for k in rows[-1]]
 rows = rows[2:] or rows
 med = {k: sorted(r[k] for r in rows)[len(rows) // 2] for k in keys}
 print("config B phases (median ms): " + ", ".join("%s %.3f" % (k, med[k]) for k in keys), flush=True)
-flags = ctx.file_flags(dt) if hasattr(ctx, "file_flags") else None
 ctx.devtree_free(dt)
 ctx.tree_free(tree)

@@ -16,11 +16,9 @@ answers back and run `compare`: zero differences pins a12 / f2; any difference n
 No GPU is involved: the kernel source is compiled by g++ (tests/host_df/df_host.cc).
 """
 import argparse
-import ctypes as C
 import json
 import os
 import random
-import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
