@@ -16,6 +16,7 @@ Fixtures and where the reference pins them (paths under /root/reference):
   multiignores                  any2kube_test.go:334-391 + testdata/testmultiplem2kignores.tar
   emptydir / nonexistent        any2kube_test.go:38-70
   nasty, userscript, randomNNN  ours: edge cases of SURVEY.md App. A and random small trees
+  pairwise                      ours: every single marker and every pair of markers, each in its own directory
 """
 import json
 import os
@@ -189,6 +190,38 @@ def nasty_spec():
     return {"name": "nasty", "entries": e}
 
 
+def pairwise_spec():
+    """The 18 detect scripts' truth table, pinned beyond the fixtures above: one first-level directory for every single
+    marker and every PAIR of markers the scripts look at (own files, files anywhere below, a *.war, a python main), and
+    every subset of the four that s2i/java weighs against each other.  The root is ignored but descended (an empty
+    .m2kignore line, as in `nasty`), so each directory meets the scripts on its own."""
+    markers = {
+        "pipfile": [("Pipfile", {})], "buildxml": [("build.xml", {})], "gradle": [("build.gradle", {})], "pom": [("pom.xml", {})],
+        "pkgjson": [("package.json", {})], "reqs": [("requirements.txt", {})], "setuppy": [("setup.py", {})], "envyml": [("environment.yml", {})],
+        "gemfile": [("Gemfile", {})], "gomod": [("go.mod", {})],
+        "go": [("x.go", {})], "godeep": [("sub/deeper/y.go", {})], "php": [("index.php", {})], "phpdeep": [("sub/z.php", {})],
+        "java": [("A.java", {})], "javadeep": [("src/main/B.java", {})], "war": [("app.war", {})],
+        "mainpy": [("tool/run.py", {"size": 60, "main": True})],
+    }
+    names = sorted(markers)
+    combos = [()] + [(a,) for a in names] + [(a, b) for i, a in enumerate(names) for b in names[i + 1:]]
+    four = ("gradle", "buildxml", "pom", "javadeep")
+    for mask in range(16):
+        c = tuple(sorted(four[k] for k in range(4) if mask >> k & 1))
+        if len(c) > 2:
+            combos.append(c)
+    e = [treespec.lit(".m2kignore", b"\n")]
+    for c in combos:
+        d = "_".join(c) if c else "none"
+        e.append({"p": d, "t": "d"})
+        for m in c:
+            for rel_path, extra in markers[m]:
+                ent = {"p": d + "/" + rel_path, "t": "f", "size": 7}
+                ent.update(extra)
+                e.append(ent)
+    return {"name": "pairwise", "entries": e}
+
+
 def userscript_spec():
     L = treespec.lit
     script = (b"#!/bin/sh\nif [ -f \"$1/custom.marker\" ]; then\n  echo '{\"port\": 1234}'\n  exit 0\nfi\nexit 1\n")
@@ -227,6 +260,14 @@ def reference_plans(out_dir):
 
 def main():
     out_dir = HERE
+    if len(sys.argv) > 2 and sys.argv[1] == "--only":  # python make_golden.py --only pairwise[,nasty,userscript]
+        tmp = tempfile.mkdtemp(prefix="m2kgold-")
+        try:
+            for name in sys.argv[2].split(","):
+                fixture({"pairwise": pairwise_spec, "nasty": nasty_spec, "userscript": userscript_spec}[name](), out_dir, tmp)
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+        return
     reference_plans(out_dir)
     tmp = tempfile.mkdtemp(prefix="m2kgold-")
     try:
@@ -252,6 +293,7 @@ def main():
         fixture({"name": "nonexistent", "entries": [], "nonexistent": True}, out_dir, tmp)
         fixture(nasty_spec(), out_dir, tmp)
         fixture(userscript_spec(), out_dir, tmp)
+        fixture(pairwise_spec(), out_dir, tmp)
         for seed in range(1, 41):
             fixture(treespec.random_spec(seed, n_dirs=6 + seed % 9, n_files=14 + (seed * 7) % 30,
                                          ignore_files=seed % 4), out_dir, tmp)
