@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""isDockerFile three ways, and the road to pinning it on a machine that has Go.
+"""TEST INFRASTRUCTURE (it runs the oracle): isDockerFile three ways, and the road to pinning it on a machine that has Go.
 
 The parser behind isDockerFile (moby/buildkit v0.7.2) is not in the reference tree and the reference has no test for the
 function, so its parity is "unpinned": the oracle (C), the kernel source (CUDA, here built for the host) and
@@ -22,7 +22,7 @@ import random
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))  # this directory
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 sys.path.insert(0, ROOT)
 
