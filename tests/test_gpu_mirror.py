@@ -257,3 +257,45 @@ def test_a_result_may_outlive_its_context(tmp_path):
     c2.result_free(r2)
     c2.tree_free(t2)
     c2.close()
+
+
+@pytest.mark.parametrize("name", ["samples", "pairwise", "nasty"])
+def test_the_c_example_prints_what_the_binding_sees(tmp_path, name):
+    """examples/detect.c drives the C ABI from plain C (m2k_pack_detect, m2k_option_json): its lines must be the ones
+    the ctypes binding gets from the same calls -- which the other tests hold against the goldens."""
+    import subprocess
+    from test_host import _build_c_example
+    from move2kube_b200 import _abi, lib
+    root = str(tmp_path / "tree")
+    treespec.materialize(GOLDENS[name], root)
+    exe = _build_c_example(tmp_path)
+    p = subprocess.run([exe, root], capture_output=True)
+    assert p.returncode == 0, p.stderr
+    got = p.stdout.split(b"\n")[:-1]
+    ctx = lib.Context(0)
+    tp, rp = ctx.pack_detect(os.fsencode(root))
+    t, r = tp.contents, rp.contents
+    names = bytes(t.names[0:t.entry_name_off[t.n_entries]])
+
+    def rel(d):
+        parts = []
+        while t.dir_parent[d] != _abi.NONE:
+            e = t.dir_entry[d]
+            parts.append(names[t.entry_name_off[e]:t.entry_name_off[e + 1]])
+            d = t.dir_parent[d]
+        return b"/".join(reversed(parts)) or b"."
+    want = []
+    for k in range(r.n_services):
+        d = r.service_dirs[k]
+        for opt in range(18):
+            if r.dir_opts[d] >> opt & 1:
+                want.append(rel(d) + b"\t%d\t" % opt + lib.option_json(tp, rp, d, opt).rstrip(b"\n"))
+    for f in range(r.n_files):
+        if r.file_flags[f] & _abi.FILE_DOCKERFILE:
+            e = t.file_entry[f]
+            want.append(b"dockerfile\t" + rel(t.entry_dir[e]) + b"/" + names[t.entry_name_off[e]:t.entry_name_off[e + 1]])
+    assert got == want
+    assert len(want) >= (3 if name == "samples" else 20)
+    ctx.result_free(rp)
+    ctx.tree_free(tp)
+    ctx.close()

@@ -4,6 +4,7 @@ well formed and deterministic, path helpers follow Go.  No compute entry point i
 import ctypes as C
 import os
 import re
+import subprocess
 
 import pytest
 
@@ -337,3 +338,21 @@ def test_host_thread_team_is_shared_safely_between_caller_threads():
         assert len(out) == 4 and len(set(out.values())) == 1 and out[0][0] == 0 and out[0][2] > 4000
     finally:
         lib.tree_free_host(tp)
+
+
+def _build_c_example(out_dir):
+    """examples/detect.c against include/m2kdetect.h and libm2kdetect.so: the C ABI used from C, no binding layer"""
+    exe = os.path.join(str(out_dir), "detect")
+    libdir = os.path.join(REPO, "move2kube_b200")
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(REPO, "include"), os.path.join(REPO, "examples", "detect.c"),
+                           "-L", libdir, "-lm2kdetect", "-Wl,-rpath," + libdir, "-o", exe])
+    return exe
+
+
+def test_c_example_builds_links_and_fails_loudly_without_a_device(tmp_path):
+    import torch
+    exe = _build_c_example(tmp_path)
+    if torch.cuda.is_available():
+        pytest.skip("a device is present: tests/test_gpu_mirror.py runs the example")
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    assert p.returncode == 1 and p.stdout == "" and "no CPU path" in p.stderr
