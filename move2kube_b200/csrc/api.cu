@@ -39,7 +39,8 @@ static bool ctx_alive(Ctx* C) {  // caller holds g_live_mu
 // pinned host blocks from the context's pool (Ctx::pinned_pool); a NULL context means plain cudaHostAlloc
 static void* pinned_take(Ctx* C, size_t bytes) {
   if (!bytes) bytes = 16;
-  if (C) {
+  if (C) {  // the pool's book-keeping under the registry's lock: a result may be released from another thread meanwhile
+    std::lock_guard<std::mutex> lk(g_live_mu);
     Ctx::PinnedBlock* best = nullptr;
     for (auto& b : C->pinned_pool)
       if (!b.in_use && b.cap >= bytes && (!best || b.cap < best->cap)) best = &b;
@@ -47,7 +48,7 @@ static void* pinned_take(Ctx* C, size_t bytes) {
   }
   void* p = nullptr;
   if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-  if (C) C->pinned_pool.push_back({p, bytes, true});
+  if (C) { std::lock_guard<std::mutex> lk(g_live_mu); C->pinned_pool.push_back({p, bytes, true}); }
   return p;
 }
 static void pinned_give(Ctx* C, void* p) {
@@ -301,11 +302,17 @@ extern "C" int m2k_ctx_trim(m2k_ctx* ctx) {
   if (!ctx) return fail(nullptr, M2K_ERR_ARG, "ctx is NULL");
   Ctx* C = &ctx->c;
   CU(cudaSetDevice(C->device));
-  for (auto& A : C->arena) if (A.p && !A.in_use) { cudaFree(A.p); A.p = nullptr; A.cap = 0; }
-  for (size_t i = 0; i < C->pinned_pool.size();) {
-    if (!C->pinned_pool[i].in_use) { cudaFreeHost(C->pinned_pool[i].p); C->pinned_pool.erase(C->pinned_pool.begin() + i); }
-    else i++;
+  std::vector<void*> dev, host;  // taken out of the books under the lock, given back to the driver outside it
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    for (auto& A : C->arena) if (A.p && !A.in_use) { dev.push_back(A.p); A.p = nullptr; A.cap = 0; }
+    for (size_t i = 0; i < C->pinned_pool.size();) {
+      if (!C->pinned_pool[i].in_use) { host.push_back(C->pinned_pool[i].p); C->pinned_pool.erase(C->pinned_pool.begin() + i); }
+      else i++;
+    }
   }
+  for (void* p : dev) cudaFree(p);
+  for (void* p : host) cudaFreeHost(p);
   return M2K_OK;
 }
 
@@ -421,15 +428,20 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 static cudaError_t arena_alloc(Ctx* C, DevTree* t, int k, void** out, size_t bytes) {
   Ctx::Arena& A = C->arena[k];
   if (!bytes) bytes = 1;
-  if (A.in_use) return cudaMalloc(out, bytes);
+  bool busy;
+  {  // claim the arena under the registry's lock (a device tree may hand it back from another thread)
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    busy = A.in_use;
+    if (!busy) A.in_use = true;
+  }
+  if (busy) return cudaMalloc(out, bytes);
   if (A.cap < bytes) {
     if (A.p) cudaFree(A.p);
     A.p = nullptr; A.cap = 0;
     cudaError_t e = cudaMalloc(&A.p, bytes);
-    if (e != cudaSuccess) return e;
+    if (e != cudaSuccess) { std::lock_guard<std::mutex> lk(g_live_mu); A.in_use = false; return e; }
     A.cap = bytes;
   }
-  A.in_use = true;
   t->arena_ctx = C;
   t->from_arena |= 1u << k;
   *out = A.p;
