@@ -152,11 +152,24 @@ def gen_file(r):
     return data
 
 
+def _third():
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dockerfile_re
+    return dockerfile_re
+
+
+_checked = [0]
+
+
 def check(dfhost, data, stripe):
     want = oracle_lib.dockerfile_flags(data) & MASK
     got = dfhost.dfhost_flags(data, len(data), stripe)
     assert not (got >> 31), ("map composition is not associative on", data)
     assert got == want, (data, stripe, "host build of the device code", got, "oracle", want)
+    _checked[0] += 1
+    if _checked[0] % 3 == 0:  # every third case also through the regex-engine derivation (it is the slow one)
+        assert _third().is_dockerfile(data) == bool(want & F_DF), (data, "regex-engine derivation vs oracle", want)
 
 
 def test_flag_values_match_the_header():
@@ -259,13 +272,6 @@ def test_newline_runs_fold_the_same_in_any_grouping(dfhost):
 
 
 # ---- arguments in JSON form: three derivations ----------------------------------------------------------------------
-def _third():
-    import sys
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import dockerfile_re
-    return dockerfile_re
-
-
 from dockerfile_kats import JSON_KATS  # noqa: E402
 
 
